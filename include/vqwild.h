@@ -1,0 +1,171 @@
+/*
+ * vqwild.h -- C ABI of the B200-native (sm_100a) query->gallery matching path.
+ *
+ * The reference (dongzhuoyao/video-query-in-the-wild) is pure Python and has no FFI of its
+ * own; its hot path sits behind four library call surfaces.  Every entry
+ * point below names the reference call site (file:line relative to the reference tree) it
+ * replaces.  INTEGRATION.md shows the ctypes binding a maintainer adds on the reference side.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no torch / C++ types in any signature.
+ *   - every function returns 0 on success and a negative vq_status otherwise;
+ *     vq_last_error() returns a thread-local message for the last failure.
+ *   - a pointer argument documented "host or device" is classified with
+ *     cudaPointerGetAttributes: device pointers are used in place (zero copy), host
+ *     pointers are staged through pinned memory on `stream` (this is the e2e path).
+ *   - `stream` is a cudaStream_t passed as void* (0 = default stream).  Calls are
+ *     asynchronous for device outputs and synchronise `stream` before returning when an
+ *     output pointer is host memory.
+ *   - there is NO CPU fallback: without an sm_100 device every compute entry fails with
+ *     VQ_ERR_NO_DEVICE / VQ_ERR_ARCH.
+ *   - deterministic: no floating-point atomics in any result-bearing reduction.
+ *   - canonical score (the parity target): d2(q,g) = fl32(sum_i (q_i-g_i)^2) accumulated
+ *     sequentially in i with fmaf; ranking = d2 ascending, ties -> lowest gallery index.
+ */
+#ifndef VQWILD_H_
+#define VQWILD_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VQ_API __attribute__((visibility("default")))
+
+typedef enum {
+    VQ_OK = 0,
+    VQ_ERR_INVALID = -1,   /* bad argument (dimension mismatch, k out of range, ...) */
+    VQ_ERR_NO_DEVICE = -2, /* no CUDA device / driver */
+    VQ_ERR_ARCH = -3,      /* device is not sm_100 */
+    VQ_ERR_CUDA = -4,      /* a CUDA call failed; see vq_last_error() */
+    VQ_ERR_NOMEM = -5,
+    VQ_ERR_CAPACITY = -6,  /* a documented internal capacity was exceeded */
+    VQ_ERR_STATE = -7      /* call order (search before add, meta missing, ...) */
+} vq_status;
+
+/* element types of embedding inputs */
+#define VQ_F32 0
+#define VQ_BF16 1
+
+/* tensor-core pre-filter precision (how the coarse scores are formed; results are always
+ * the canonical fp32 scores, verified -- see DESIGN.md "Exactness") */
+#define VQ_PREC_AUTO 0   /* fp32 input -> SPLIT3, bf16 input -> BF16 */
+#define VQ_PREC_BF16 1   /* one bf16 MMA pass */
+#define VQ_PREC_SPLIT3 2 /* hi*hi + hi*lo + lo*hi bf16 passes (~2^-16 relative) */
+#define VQ_PREC_EXACT 3  /* no tensor-core pre-filter: canonical CUDA-core scores for all pairs */
+
+VQ_API int vq_version(void);
+VQ_API const char *vq_last_error(void);
+/* 0 if device `dev` exists and is sm_100; else VQ_ERR_NO_DEVICE / VQ_ERR_ARCH. */
+VQ_API int vq_device_check(int dev);
+
+/* ------------------------------------------------------------------------------------
+ * b1. faiss.IndexFlatL2 replacement.
+ *   ctor   dataloader_baseline.py:1502 (:872, :1196)  faiss.IndexFlatL2(d)
+ *   add    :1507 (:877, :1201)                        index.add(xb float32[N,d])
+ *   ntotal :1508
+ *   search :1592-1595 (:935-938, :1268-1271)          index.search(xq float32[nq,d], k)
+ * ---------------------------------------------------------------------------------- */
+typedef struct vq_index vq_index;
+
+VQ_API int vq_index_create(int d, vq_index **out);
+VQ_API int vq_index_destroy(vq_index *ix);
+/* Append n rows (host or device, C-contiguous [n,d], dtype VQ_F32 or VQ_BF16; all adds to one
+ * index must use the same dtype).  Builds the bf16 operand planes and row norms. */
+VQ_API int vq_index_add(vq_index *ix, const void *xb, int64_t n, int dtype, void *stream);
+VQ_API int64_t vq_index_ntotal(const vq_index *ix);
+VQ_API int vq_index_dim(const vq_index *ix);
+VQ_API int vq_index_set_precision(vq_index *ix, int prec);
+/* Per-row metadata used by the fused labelling (a4): label id and video id per gallery row
+ * (dataloader_baseline.py:1540-1556 candidate["label"], candidate["video_id"]).  host or device,
+ * int32[ntotal].  video may be NULL (no ignore rule). */
+VQ_API int vq_index_set_meta(vq_index *ix, const int32_t *label, const int32_t *video, void *stream);
+/* Untrimmed-video segments: seg_start int64[nseg+1] (host), rows [seg_start[v], seg_start[v+1])
+ * are the moments/windows of video v (dataloader_baseline.py:1091-1151 builds them video by
+ * video, so they are contiguous).  Enables vq_index_search_segmax. */
+VQ_API int vq_index_set_segments(vq_index *ix, const int64_t *seg_start, int64_t nseg, void *stream);
+
+/* faiss-shaped search.  xq [nq,d] (host or device, dtype as given); outputs D float32[nq,k]
+ * (canonical squared L2, ascending) and I int64[nq,k] (host or device; -1 / +inf padding when
+ * fewer than k rows qualify).  k <= ntotal.  k <= 1024 takes the tensor-core streaming top-k
+ * path; larger k (the reference's k = ntotal, :1594) takes the full-sort path.
+ * ignore_video: optional int32[nq, n_ignore] (host or device) -- rows whose video id matches
+ * any entry are skipped (the reference's ignore rule, :1548); requires vq_index_set_meta. */
+VQ_API int vq_index_search(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k,
+                           const int32_t *ignore_video, int n_ignore, float *D, int64_t *I,
+                           void *stream);
+
+/* configs[2]: per (query, video) best moment (segment max-pool) and the top-k videos.
+ * Outputs [nq,k]: video id (int64), arg-best gallery row (int64), its canonical d2. */
+VQ_API int vq_index_search_segmax(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k,
+                                  int64_t *video, int64_t *row, float *D, void *stream);
+
+/* Statistics of the last search on this index (host ints): [0] queries that needed the exact
+ * fallback, [1] tensor-core tiles issued, [2] candidate slots per query, [3] work units,
+ * [4] gallery chunks, [5] kernels launched by the call. */
+VQ_API int vq_index_last_stats(const vq_index *ix, int64_t *out6);
+
+/* ------------------------------------------------------------------------------------
+ * b2. Evaluation: ARV_Retrieval.ranking's per-query loop (dataloader_baseline.py:1526-1610)
+ * = labelling (a4) + scoring/ranking (a3) + evaluation_metric.add2dict (a6, :431-496).
+ *   q_label int32[nq], ignore_video int32[nq,n_ignore] (host or device)
+ *   ap float64[nq]; recall float64[nq,3] (R@30/50/100, :332); top_idx int64[nq,100] (the first
+ *   100 survivors in rank order -- the rows behind cm_dict["label"], :441-442); may be NULL.
+ * Requires vq_index_set_meta.  Full-list semantics (k = ntotal): AP over all survivors with
+ * the last one forced positive (:434).
+ * ---------------------------------------------------------------------------------- */
+VQ_API int vq_index_eval_trimmed(vq_index *ix, const void *xq, int64_t nq, int dtype,
+                                 const int32_t *q_label, const int32_t *ignore_video,
+                                 int n_ignore, double *ap, double *recall, int64_t *top_idx,
+                                 void *stream);
+
+/* sklearn.metrics.average_precision_score for a batch of lists (dataloader_baseline.py:391,
+ * :461): lists are concatenated, list s = [offsets[s], offsets[s+1]).  y_true int32, y_score
+ * float64 (any order; sorted internally, ties grouped).  host or device; ap float64[nlists]. */
+VQ_API int vq_average_precision(const int32_t *y_true, const double *y_score,
+                                const int64_t *offsets, int64_t nlists, double *ap, void *stream);
+
+/* ------------------------------------------------------------------------------------
+ * b3. nms_cpu (misc_utils/utils_models.py:153-174), segmented: dets float64[total,3] =
+ * (x1,x2,score); segment s = rows [offsets[s], offsets[s+1]).  keep uint8[total] (1 = kept).
+ * Visiting order inside a segment: score descending, ties lowest row.
+ * ---------------------------------------------------------------------------------- */
+VQ_API int vq_nms1d_segmented(const double *dets, const int64_t *offsets, int64_t nseg,
+                              double thresh, uint8_t *keep, void *stream);
+
+/* ------------------------------------------------------------------------------------
+ * b4. Metric-learning loss (misc_utils/metric_learning_loss.py).
+ *   vq_pdist            Sampler.pdist :276-289          A f32[B,d] -> dist f32[B,B]
+ *   vq_triplet_batchhard  TripletLoss.forward :357-379 with in-kernel batch-hard mining
+ *                       (extension; masks as :173-176) + backward.  G independent groups of B
+ *                       rows: emb f32[G,B,d], labels int32[G,B] -> loss f32[G], grad f32[G,B,d],
+ *                       trip int32[G,B,3] (a,p,n; -1 rows for skipped anchors), may be NULL.
+ *   vq_triplet_given    same loss/backward for caller-sampled triplets int32[T,3] (the
+ *                       reference's random/semihard/distance samplers run on the host).
+ * All pointers host or device.
+ * ---------------------------------------------------------------------------------- */
+VQ_API int vq_pdist(const float *A, int64_t B, int d, float eps, float *dist, void *stream);
+VQ_API int vq_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int64_t B,
+                                int d, float margin, float *loss, float *grad, int32_t *trip,
+                                void *stream);
+VQ_API int vq_triplet_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T,
+                            float margin, float *loss, float *grad, void *stream);
+
+/* a1. Pre-match pooling: F.normalize(p=2, dim=1) per time step (main.py:232) + temporal mean
+ * (dataloader_baseline.py:1481).  x f32[B,C,T] -> out f32[B,C]. */
+VQ_API int vq_pool_normalize(const float *x, int64_t B, int C, int T, float *out, void *stream);
+
+/* 8e. Merge per-shard top-k lists after the all-gather: d2 f32[G,nq,k], idx int64[G,nq,k]
+ * (global row ids, -1 = empty) -> out [nq,k] by (d2 asc, idx asc). */
+VQ_API int vq_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k,
+                         float *out_d2, int64_t *out_idx, void *stream);
+
+/* Canonical all-pairs squared L2 (CUDA cores), out f32[nq,n]; test / small-problem utility. */
+VQ_API int vq_l2sq(const float *q, const float *g, int64_t nq, int64_t n, int d, float *out,
+                   void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VQWILD_H_ */

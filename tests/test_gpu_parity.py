@@ -1,0 +1,355 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via the Python mirror) against the CPU
+oracle on the same seeded inputs and against the golden fixtures minted from the reference.
+Bar: indices / ranks / mined triplets bit-exact; canonical fp32 distances bit-exact; float64
+metrics 1e-9 (north_star: 1e-6); loss / grad bit-exact vs oracle and 1e-6 vs the reference."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+from oracle import oracle as orc  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def vq():
+    import vqwild_b200
+    return vqwild_b200
+
+
+def _emb(rng, n, d, ncls=0, labels=None, scale=True):
+    x = rng.standard_normal((n, d)).astype(np.float32)
+    if ncls:
+        c = rng.standard_normal((ncls, d)).astype(np.float32)
+        x += 1.0 * c[labels]
+    x /= np.linalg.norm(x, axis=1, keepdims=True)
+    if scale:
+        x *= rng.uniform(0.6, 1.0, (n, 1)).astype(np.float32)
+    return np.ascontiguousarray(x, np.float32)
+
+
+def test_l2sq_bit_exact(vq):
+    rng = np.random.default_rng(0)
+    for nq, n, d in [(5, 77, 32), (70, 130, 512), (3, 9, 100)]:
+        q, g = _emb(rng, nq, d), _emb(rng, n, d)
+        got = vq.l2sq(q, g)
+        assert np.array_equal(got.view(np.uint32), orc.l2sq(q, g).view(np.uint32))
+
+
+@pytest.mark.parametrize("prec", ["EXACT", "SPLIT3", "BF16"])
+def test_search_matches_oracle(vq, prec):
+    rng = np.random.default_rng(1)
+    nq, n, d, k = 200, 6000, 512, 100
+    g = _emb(rng, n, d)
+    g[123] = g[45]  # duplicate rows: exact score ties -> lowest index first
+    q = _emb(rng, nq, d)
+    q[0] = g[45]
+    ix = vq.IndexFlatL2(d)
+    ix.set_precision(getattr(vq, "PREC_" + prec))
+    ix.add(g)
+    D, I = ix.search(q, k)
+    Do, Io = orc.search(q, g, k)
+    st = ix.last_stats()
+    print(prec, st)
+    assert np.array_equal(I, Io)
+    assert np.array_equal(D.view(np.uint32), Do.view(np.uint32))
+    assert I[0, 0] == 45 and I[0, 1] == 123 and D[0, 0] == 0.0
+
+
+def test_search_scores_within_fp64_tolerance(vq):
+    rng = np.random.default_rng(11)
+    q, g = _emb(rng, 64, 512), _emb(rng, 3000, 512)
+    ix = vq.IndexFlatL2(512)
+    ix.add(g)
+    D, I = ix.search(q, 50)
+    ref = ((q[:, None, :].astype(np.float64) - g[I].astype(np.float64)) ** 2).sum(-1)
+    assert np.max(np.abs(D - ref) / np.maximum(ref, 1e-30)) < 1e-5  # north_star fp32 tolerance
+
+
+def test_search_small_and_ragged_shapes(vq):
+    rng = np.random.default_rng(2)
+    for nq, n, d, k in [(1, 1, 8, 1), (3, 50, 20, 50), (130, 257, 64, 7), (129, 1025, 100, 33)]:
+        q, g = _emb(rng, nq, d), _emb(rng, n, d)
+        ix = vq.IndexFlatL2(d)
+        ix.add(g[: n // 2])
+        ix.add(g[n // 2:])  # two adds
+        assert ix.ntotal == n
+        D, I = ix.search(q, k)
+        Do, Io = orc.search(q, g, k)
+        assert np.array_equal(I, Io), (nq, n, d, k)
+        assert np.array_equal(D.view(np.uint32), Do.view(np.uint32))
+
+
+def test_search_with_ignore_and_device_tensors(vq):
+    import torch
+    rng = np.random.default_rng(3)
+    nq, n, d, k = 150, 4000, 512, 100
+    g, q = _emb(rng, n, d), _emb(rng, nq, d)
+    video = (np.arange(n) // 3).astype(np.int32)
+    label = rng.integers(0, 20, n).astype(np.int32)
+    ign = rng.integers(0, n // 3, (nq, 5)).astype(np.int32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(torch.from_numpy(g).cuda())
+    ix.set_meta(label, video)
+    D, I = ix.search(torch.from_numpy(q).cuda(), k, ignore_video=torch.from_numpy(ign).cuda())
+    D, I = D.cpu().numpy(), I.cpu().numpy()
+    Do, Io = orc.search(q, g, n)
+    for a in range(nq):
+        keep = ~np.isin(video[Io[a]], ign[a])
+        assert np.array_equal(I[a], Io[a][keep][:k])
+        assert np.array_equal(D[a].view(np.uint32), Do[a][keep][:k].view(np.uint32))
+
+
+def test_search_forced_fallback_path(vq):
+    rng = np.random.default_rng(4)
+    q, g = _emb(rng, 40, 128), _emb(rng, 3000, 128)
+    os.environ["VQ_DEBUG_FORCE_FALLBACK"] = "1"
+    try:
+        ix = vq.IndexFlatL2(128)
+        ix.add(g)
+        D, I = ix.search(q, 100)
+        st = ix.last_stats()
+    finally:
+        del os.environ["VQ_DEBUG_FORCE_FALLBACK"]
+    assert st["fallback_queries"] == 40
+    Do, Io = orc.search(q, g, 100)
+    assert np.array_equal(I, Io) and np.array_equal(D.view(np.uint32), Do.view(np.uint32))
+
+
+def test_search_bf16_input_mode(vq):
+    import torch
+    rng = np.random.default_rng(5)
+    q, g = _emb(rng, 100, 512, scale=False), _emb(rng, 5000, 512, scale=False)
+    qb, gb = torch.from_numpy(q).cuda().bfloat16(), torch.from_numpy(g).cuda().bfloat16()
+    ix = vq.IndexFlatL2(512)
+    ix.add(gb)
+    D, I = ix.search(qb, 100)
+    qr, gr = qb.float().cpu().numpy(), gb.float().cpu().numpy()  # the bf16 values, widened
+    Do, Io = orc.search(qr, gr, 100)
+    assert np.array_equal(I.cpu().numpy(), Io)
+    assert np.array_equal(D.cpu().numpy().view(np.uint32), Do.view(np.uint32))
+    # bf16-input scores vs the fp32 originals: 2e-3 relative (north_star, stated separately)
+    ref = ((q[:, None, :].astype(np.float64) - g[Io].astype(np.float64)) ** 2).sum(-1)
+    assert np.max(np.abs(Do - ref) / ref) < 2e-2  # distances near 2.0; bf16 rounding of inputs
+
+
+@pytest.mark.parametrize("ragged", [False, True])
+def test_segmax_topk(vq, ragged):
+    rng = np.random.default_rng(6)
+    nseg, d, nq, k = 300, 256, 140, 50
+    lens = rng.integers(1, 90, nseg) if ragged else np.full(nseg, 64)
+    seg_start = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    n = int(seg_start[-1])
+    g, q = _emb(rng, n, d), _emb(rng, nq, d)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    ix.set_segments(seg_start)
+    V, R, D = ix.search_segmax(q, k)
+    Vo, Ro, Do = orc.segmax_topk(q, g, seg_start, k)
+    print(ix.last_stats())
+    assert np.array_equal(V, Vo) and np.array_equal(R, Ro)
+    assert np.array_equal(D.view(np.uint32), Do.view(np.uint32))
+
+
+def _golden_trimmed(golden, query_num=1):
+    feat, rows = golden["tr_feat"], golden["tr_q_list_rows"]
+    acc = np.zeros((rows.shape[0], feat.shape[1]), np.float32)
+    for i in range(query_num):
+        acc = acc + feat[rows[:, i]]
+    q = (acc / np.float32(query_num)).astype(np.float32) if query_num > 1 else acc
+    return q, feat, golden["tr_label"], golden["tr_video"], golden["tr_label"][rows[:, 0]], golden["tr_video"][rows]
+
+
+def test_eval_trimmed_golden(vq, golden):
+    for qn, key in [(1, "tr_ap"), (5, "tr5_ap")]:
+        q, g, gl, gv, ql, ign = _golden_trimmed(golden, qn)
+        ix = vq.IndexFlatL2(g.shape[1])
+        ix.add(g)
+        ix.set_meta(gl, gv)
+        ap, rec, top = ix.eval_trimmed(q, ql, ign, want_top=True)
+        np.testing.assert_allclose(ap, golden[key], rtol=0, atol=1e-9)
+        apo, reco, topo, _ = orc.eval_trimmed(q, g, gl, gv, ql, ign)
+        np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-12)
+        assert np.array_equal(top, topo)
+        if qn == 1:
+            assert (gl[top] == golden["tr_cm_labels_top100"]).all()
+
+
+def test_arv_retrieval_mirror_golden(vq, golden):
+    """The thin caller with the reference's list-of-dict interface reproduces the reference's dict."""
+    names = [str(x) for x in golden["label_names"]]
+    feat, lab, vid = golden["tr_feat"], golden["tr_label"], golden["tr_video"]
+    qrows = set(golden["tr_q_row"].tolist())
+    items = []
+    for i in range(feat.shape[0]):
+        rt = "base" if lab[i] < 6 else ("novel" if lab[i] < 11 else "noise")
+        items.append(dict(label=names[lab[i]], video_id="v_%04d" % vid[i], is_query=int(i in qrows),
+                          retrieval_type=rt, feat=feat[i], frame_info=i))
+
+    class A:
+        query_num = 1
+        eval_split = "testing"
+        metric_feat_dim = feat.shape[1]
+
+    ev = vq.ARV_Retrieval(A(), query_list=[it for it in items if lab[it["frame_info"]] < 11], gallery_list=items)
+    res = ev.ranking()
+    # generate_multi_query must reproduce the reference's random.seed(620) draws
+    assert [[x["frame_info"] for x in ql] for ql in ev.query_list] == golden["tr_q_list_rows"].tolist()
+    np.testing.assert_allclose([res["ap"], res["base_map"], res["novel_map"]], golden["tr_result"], rtol=0, atol=1e-9)
+    got = np.array([[res[k][str(n)] for n in (30, 50, 100)] for k in ("recall", "base_recall", "novel_recall")])
+    np.testing.assert_allclose(got, golden["tr_recall"], rtol=0, atol=1e-9)
+
+
+def test_eval_trimmed_random_with_ties(vq):
+    rng = np.random.default_rng(7)
+    n, d, nq = 3000, 512, 300
+    label = rng.integers(0, 25, n).astype(np.int32)
+    g = _emb(rng, n, d, 25, label)
+    g[1000:1040] = g[10]  # a block of exact duplicates (ties inside AP tie groups and at R@N cut-offs)
+    video = (np.arange(n) // 2).astype(np.int32)
+    qrow = rng.choice(n, nq, replace=False)
+    qrow[:3] = [10, 1005, 1039]
+    q = g[qrow]
+    ign = np.stack([video[qrow]] + [video[rng.integers(0, n, nq)] for _ in range(4)], 1).astype(np.int32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    ix.set_meta(label, video)
+    ap, rec, top = ix.eval_trimmed(q, label[qrow], ign, want_top=True)
+    apo, reco, topo, _ = orc.eval_trimmed(q, g, label, video, label[qrow], ign)
+    np.testing.assert_allclose(ap, apo, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-12)
+    assert np.array_equal(top, topo)
+
+
+def test_average_precision_lists_golden(vq, golden):
+    yts, yss, want = [], [], []
+    off = 0
+    for c, n in enumerate(golden["hl_n"]):
+        s = slice(off, off + n)
+        off += n
+        keep = golden["hl_ig"][s] == 0
+        yt = golden["hl_tp"][s][keep].copy()
+        yt[-1] = 1
+        yts.append(yt), yss.append(golden["hl_sc"][s][keep]), want.append(golden["hl_ap"][c])
+    got = vq.average_precision_batch(yts, yss)
+    np.testing.assert_allclose(got, want, rtol=0, atol=1e-12)
+
+
+def test_evaluation_metric_mirror_golden(vq, golden):
+    em = vq.evaluation_metric(None, [])
+    off = 0
+    for c, n in enumerate(golden["hl_n"]):
+        s = slice(off, off + n)
+        off += n
+        hits = [dict(tp=int(t), ignore=bool(i), score=float(x))
+                for t, i, x in zip(golden["hl_tp"][s], golden["hl_ig"][s], golden["hl_sc"][s])]
+        r = em.multiprocess_calculate(hits)
+        assert abs(r["ap"] - golden["hl_ap"][c]) < 1e-12
+        np.testing.assert_allclose(r["recall_list"], golden["hl_rec"][c], rtol=0, atol=1e-12)
+
+
+def test_nms_golden(vq, golden):
+    assert vq.nms_cpu(golden["nms_kat_dets"], 0.5) == [1, 2]
+    off, koff = 0, golden["nms_keep_off"]
+    offs = np.concatenate([[0], np.cumsum(golden["nms_n"])])
+    mask = vq.nms_segmented(golden["nms_dets"], offs, 0.5)
+    for c, n in enumerate(golden["nms_n"]):
+        want = np.zeros(n, np.uint8)
+        want[golden["nms_keep"][koff[c]:koff[c + 1]]] = 1
+        assert np.array_equal(mask[off:off + n], want)
+        assert vq.nms_cpu(golden["nms_dets"][off:off + n], 0.5) == golden["nms_keep"][koff[c]:koff[c + 1]].tolist()
+        off += n
+
+
+def test_triplet_golden_and_oracle(vq, golden):
+    import torch
+    emb, labels, margin = golden["tl_emb"], golden["tl_labels"], float(golden["tl_margin"])
+    x = torch.from_numpy(emb).cuda()
+    d = vq.pdist(x).cpu().numpy()
+    assert np.array_equal(d.view(np.uint32), orc.pdist(emb).view(np.uint32))
+    np.testing.assert_allclose(d, golden["tl_pdist"], rtol=0, atol=2e-6)
+    # reference-sampled (semihard) triplets through the "triplets given" kernel
+    from vqwild_b200.loss import _GivenFn, TripletLoss
+    xg = x.clone().requires_grad_(True)
+    loss = _GivenFn.apply(xg, torch.from_numpy(golden["tl_semihard_trip"].astype(np.int32)), margin)
+    loss.backward()
+    assert abs(loss.item() - float(golden["tl_semihard_loss"])) < 1e-6
+    np.testing.assert_allclose(xg.grad.cpu().numpy(), golden["tl_semihard_grad"], rtol=0, atol=1e-6)
+    lo, go, _, _ = orc.triplet_fwd_bwd(emb, golden["tl_semihard_trip"], margin)
+    assert loss.item() == lo and np.array_equal(xg.grad.cpu().numpy().view(np.uint32), go.view(np.uint32))
+    # batch-hard, mined in the kernel
+    crit = TripletLoss(margin=margin, sampling_method="batchhard")
+    xb = x.clone().requires_grad_(True)
+    loss = crit(xb, labels)
+    loss.backward()
+    assert abs(loss.item() - float(golden["tl_bh_loss"])) < 1e-6
+    np.testing.assert_allclose(xb.grad.cpu().numpy(), golden["tl_bh_grad"], rtol=0, atol=1e-6)
+    assert crit.sampler.give(x, labels) == golden["tl_bh_trip"].tolist()
+
+
+def test_triplet_cfg2_shape_bit_exact_vs_oracle(vq):
+    import torch
+    from vqwild_b200.loss import _BatchHardFn
+    rng = np.random.default_rng(8)
+    B, d = 256, 512
+    labels = np.repeat(np.arange(64), 4)
+    emb = _emb(rng, B, d, 64, labels, scale=False)
+    x = torch.from_numpy(emb).cuda().requires_grad_(True)
+    loss, trip = _BatchHardFn.apply(x, torch.from_numpy(labels), 1.0)
+    loss.backward()
+    lo, go, to = orc.batchhard_triplet(emb, labels, 1.0)
+    assert np.array_equal(trip.cpu().numpy(), to)
+    assert loss.item() == lo
+    assert np.array_equal(x.grad.cpu().numpy().view(np.uint32), go.view(np.uint32))
+    # grouped variant: G independent batches in one call, incl. a singleton class (skipped anchor)
+    G = 3
+    embs = np.stack([_emb(rng, 64, 96, 16, np.repeat(np.arange(16), 4)) for _ in range(G)])
+    labs = np.stack([np.repeat(np.arange(16), 4) for _ in range(G)])
+    labs[1, 0] = 99
+    xs = torch.from_numpy(embs).cuda().requires_grad_(True)
+    loss, trip = _BatchHardFn.apply(xs, torch.from_numpy(labs), 0.3)
+    loss.sum().backward()
+    for gi in range(G):
+        lo, go, to = orc.batchhard_triplet(embs[gi], labs[gi], 0.3)
+        t = trip[gi].cpu().numpy()
+        assert np.array_equal(t[t[:, 0] >= 0], to)
+        assert loss[gi].item() == lo
+        assert np.array_equal(xs.grad[gi].cpu().numpy().view(np.uint32), go.view(np.uint32))
+
+
+def test_pool_normalize(vq, golden):
+    out = vq.pool_normalize(golden["pool_in"])
+    np.testing.assert_allclose(out, golden["pool_out"], rtol=0, atol=1e-6)
+    assert np.array_equal(out.view(np.uint32), orc.pool_normalize(golden["pool_in"]).view(np.uint32))
+
+
+def test_topk_merge(vq):
+    rng = np.random.default_rng(9)
+    G, nq, k = 4, 33, 100
+    d2 = np.sort(rng.random((G, nq, k)).astype(np.float32), axis=2)
+    idx = rng.permutation(G * nq * k).reshape(G, nq, k).astype(np.int64)
+    idx[2, :, 90:] = -1
+    d2[1, 0, :5] = d2[0, 0, :5]  # cross-shard ties
+    od, oi = vq.topk_merge(d2, idx)
+    wd, wi = orc.topk_merge(d2, idx)
+    assert np.array_equal(oi, wi) and np.array_equal(od.view(np.uint32), wd.view(np.uint32))
+
+
+def test_full_size_cfg1_properties(vq):
+    """BASELINE configs[0] shape (4096 x 20480 x 512): oracle on a query subsample + properties."""
+    rng = np.random.default_rng(10)
+    nq, n, d, k = 4096, 20480, 512, 100
+    label = rng.integers(0, 180, n).astype(np.int32)
+    g = _emb(rng, n, d, 180, label)
+    q = g[rng.choice(n, nq, replace=False)] + 0.05 * _emb(rng, nq, d)
+    q = np.ascontiguousarray(q, np.float32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    D, I = ix.search(q, k)
+    print(ix.last_stats())
+    assert (np.diff(D, axis=1) >= 0).all()                       # sorted
+    assert (np.sort(I, axis=1)[:, 1:] != np.sort(I, axis=1)[:, :-1]).all()  # no duplicates
+    sub = rng.choice(nq, 48, replace=False)
+    Do, Io = orc.search(q[sub], g, k)
+    assert np.array_equal(I[sub], Io) and np.array_equal(D[sub].view(np.uint32), Do.view(np.uint32))

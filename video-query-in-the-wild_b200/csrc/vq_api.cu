@@ -1,0 +1,369 @@
+// vq_api.cu -- the C ABI (include/vqwild.h): argument checking, host<->device staging, the
+// index object and the orchestration of the kernels.  Host logic only; every number a caller
+// sees is produced by the kernels in this directory.
+#include <stdarg.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "vq_common.cuh"
+#include "vq_kernels.h"
+
+namespace vq {
+
+static thread_local char g_err[512] = "";
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static int check_device() {
+    int dev = 0, n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        set_error("no CUDA device (%s); this library has no CPU fallback", cudaGetErrorString(e));
+        return VQ_ERR_NO_DEVICE;
+    }
+    VQ_CUDA(cudaGetDevice(&dev));
+    int major = 0;
+    VQ_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    if (major != 10) {
+        set_error("device %d is sm_%d0; this library is built for sm_100a only", dev, major);
+        return VQ_ERR_ARCH;
+    }
+    return VQ_OK;
+}
+
+static int sm_count() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
+static bool is_device_ptr(const void *p) {
+    if (!p) return false;
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// Stream-ordered temporary device buffer.
+struct Tmp {
+    void *p = nullptr;
+    cudaStream_t st = nullptr;
+    int alloc(size_t bytes, cudaStream_t s) {
+        st = s;
+        VQ_CUDA(cudaMallocAsync(&p, bytes ? bytes : 16, s));
+        return VQ_OK;
+    }
+    ~Tmp() {
+        if (p) cudaFreeAsync(p, st);
+    }
+    Tmp() = default;
+    Tmp(const Tmp &) = delete;
+    Tmp &operator=(const Tmp &) = delete;
+};
+
+// Input argument: device pointers pass through, host pointers are copied to a temporary.
+struct In {
+    Tmp tmp;
+    const void *dev = nullptr;
+    int bind(const void *src, size_t bytes, cudaStream_t s) {
+        if (!src) {
+            dev = nullptr;
+            return VQ_OK;
+        }
+        if (is_device_ptr(src)) {
+            dev = src;
+            return VQ_OK;
+        }
+        VQ_TRY(tmp.alloc(bytes, s));
+        VQ_CUDA(cudaMemcpyAsync(tmp.p, src, bytes, cudaMemcpyHostToDevice, s));
+        dev = tmp.p;
+        return VQ_OK;
+    }
+    template <typename T>
+    const T *as() const { return (const T *)dev; }
+};
+
+// Output argument: device pointers are written in place, host pointers get a temporary that
+// finish() copies back.
+struct Out {
+    Tmp tmp;
+    void *dev = nullptr, *host = nullptr;
+    size_t bytes = 0;
+    int bind(void *dst, size_t nbytes, cudaStream_t s) {
+        bytes = nbytes;
+        if (!dst) return VQ_OK;
+        if (is_device_ptr(dst)) {
+            dev = dst;
+            return VQ_OK;
+        }
+        host = dst;
+        VQ_TRY(tmp.alloc(nbytes, s));
+        dev = tmp.p;
+        return VQ_OK;
+    }
+    int finish(cudaStream_t s) {
+        if (host && bytes) VQ_CUDA(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, s));
+        return VQ_OK;
+    }
+    template <typename T>
+    T *as() const { return (T *)dev; }
+};
+
+// ---------------------------------------------------------------------------------------
+// TMA descriptors (driver entry point fetched at run time: no link-time libcuda dependency)
+// ---------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+    }
+    return fn;
+}
+
+// bf16 plane [rows, dp] row-major -> boxes of 64 columns x box_rows rows, 128-byte swizzle
+static int make_map(CUtensorMap *m, const void *base, int64_t rows, int dp, int box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    VQ_CHECK(fn, VQ_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    cuuint64_t dims[2] = {(cuuint64_t)dp, (cuuint64_t)(rows > 0 ? rows : 1)};
+    cuuint64_t strides[1] = {(cuuint64_t)dp * 2};
+    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    VQ_CHECK(r == CUDA_SUCCESS, VQ_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return VQ_OK;
+}
+
+}  // namespace vq
+
+using namespace vq;
+
+// ---------------------------------------------------------------------------------------
+// index object
+// ---------------------------------------------------------------------------------------
+struct vq_index {
+    int d = 0, dp = 0, dtype = -1, prec = VQ_PREC_AUTO;
+    int64_t n = 0, cap = 0;
+    void *raw = nullptr;            // [cap, d] f32 or bf16: the rows as given (canonical re-scoring)
+    __nv_bfloat16 *hi = nullptr;    // [cap, dp]
+    __nv_bfloat16 *lo = nullptr;    // [cap, dp] (f32 input only)
+    float2 *colparam = nullptr;     // [cap]
+    float *norm2 = nullptr;         // [cap]
+    uint32_t *gmax_bits = nullptr;  // [1]
+    int32_t *label = nullptr, *video = nullptr;  // [n]
+    int32_t *seg_of_row = nullptr;  // [n]
+    int64_t *seg_start_dev = nullptr;
+    std::vector<int64_t> seg_start;  // host copy
+    // search workspace (grown on demand)
+    uint64_t *cand = nullptr;
+    size_t cand_bytes = 0;
+    int32_t *cand_cnt = nullptr;
+    float *cand_tau = nullptr;
+    size_t cand_units = 0;
+    int64_t *chunk_start_dev = nullptr;
+    size_t chunk_cap = 0;
+    int32_t *unproven = nullptr;
+    size_t unproven_cap = 0;
+    int32_t *unproven_count = nullptr;
+    int32_t *stat_pinned = nullptr;  // pinned host mirror of unproven_count
+    int64_t stats[6] = {0, 0, 0, 0, 0, 0};
+};
+
+static size_t esize(int dtype) { return dtype == VQ_F32 ? 4 : 2; }
+
+extern "C" {
+
+int vq_version(void) { return 100; }
+const char *vq_last_error(void) { return g_err; }
+
+int vq_device_check(int dev) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0 || dev >= n) {
+        set_error("no CUDA device %d (%s)", dev, cudaGetErrorString(e));
+        return VQ_ERR_NO_DEVICE;
+    }
+    int major = 0;
+    VQ_CUDA(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev));
+    VQ_CHECK(major == 10, VQ_ERR_ARCH, "device %d is sm_%d0, need sm_100", dev, major);
+    return VQ_OK;
+}
+
+int vq_index_create(int d, vq_index **out) {
+    VQ_CHECK(out, VQ_ERR_INVALID, "vq_index_create: out is NULL");
+    VQ_CHECK(d >= 1 && d <= 4096, VQ_ERR_INVALID, "vq_index_create: d=%d out of range [1,4096]", d);
+    VQ_TRY(check_device());
+    vq_index *ix = new vq_index();
+    ix->d = d;
+    ix->dp = (d + 63) / 64 * 64;
+    if (cudaMalloc(&ix->gmax_bits, 4) != cudaSuccess || cudaMalloc(&ix->unproven_count, 4) != cudaSuccess ||
+        cudaMallocHost(&ix->stat_pinned, 4) != cudaSuccess) {
+        set_error("vq_index_create: allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
+        delete ix;
+        return VQ_ERR_NOMEM;
+    }
+    cudaMemset(ix->gmax_bits, 0, 4);
+    cudaMemset(ix->unproven_count, 0, 4);
+    *ix->stat_pinned = 0;
+    *out = ix;
+    return VQ_OK;
+}
+
+int vq_index_destroy(vq_index *ix) {
+    if (!ix) return VQ_OK;
+    cudaDeviceSynchronize();
+    void *ptrs[] = {ix->raw,   ix->hi,         ix->lo,           ix->colparam,     ix->norm2,    ix->gmax_bits,
+                    ix->label, ix->video,      ix->seg_of_row,   ix->seg_start_dev, ix->cand,     ix->cand_cnt,
+                    ix->cand_tau, ix->chunk_start_dev, ix->unproven, ix->unproven_count};
+    for (void *p : ptrs)
+        if (p) cudaFree(p);
+    if (ix->stat_pinned) cudaFreeHost(ix->stat_pinned);
+    delete ix;
+    return VQ_OK;
+}
+
+int64_t vq_index_ntotal(const vq_index *ix) { return ix ? ix->n : 0; }
+int vq_index_dim(const vq_index *ix) { return ix ? ix->d : 0; }
+
+int vq_index_set_precision(vq_index *ix, int prec) {
+    VQ_CHECK(ix, VQ_ERR_INVALID, "index is NULL");
+    VQ_CHECK(prec >= VQ_PREC_AUTO && prec <= VQ_PREC_EXACT, VQ_ERR_INVALID, "bad precision %d", prec);
+    ix->prec = prec;
+    return VQ_OK;
+}
+
+}  // extern "C"
+
+template <typename T>
+static int grow(T **p, int64_t old_elems, int64_t new_elems, cudaStream_t st) {
+    T *np_ = nullptr;
+    if (cudaMalloc(&np_, (size_t)new_elems * sizeof(T)) != cudaSuccess) {
+        set_error("out of device memory growing a buffer to %lld bytes", (long long)(new_elems * sizeof(T)));
+        cudaGetLastError();
+        return VQ_ERR_NOMEM;
+    }
+    if (*p && old_elems) VQ_CUDA(cudaMemcpyAsync(np_, *p, (size_t)old_elems * sizeof(T), cudaMemcpyDeviceToDevice, st));
+    if (*p) {
+        VQ_CUDA(cudaStreamSynchronize(st));
+        cudaFree(*p);
+    }
+    *p = np_;
+    return VQ_OK;
+}
+
+extern "C" {
+
+int vq_index_add(vq_index *ix, const void *xb, int64_t n, int dtype, void *stream) {
+    VQ_CHECK(ix && (xb || n == 0), VQ_ERR_INVALID, "vq_index_add: NULL argument");
+    VQ_CHECK(n >= 0, VQ_ERR_INVALID, "vq_index_add: n=%lld", (long long)n);
+    VQ_CHECK(dtype == VQ_F32 || dtype == VQ_BF16, VQ_ERR_INVALID, "vq_index_add: dtype %d", dtype);
+    VQ_CHECK(ix->dtype < 0 || ix->dtype == dtype, VQ_ERR_INVALID, "vq_index_add: dtype differs from earlier adds");
+    VQ_CHECK(ix->n + n < (1ll << 31), VQ_ERR_CAPACITY, "index limited to 2^31-1 rows");
+    if (n == 0) return VQ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    ix->dtype = dtype;
+    const int64_t nn = ix->n + n;
+    if (nn > ix->cap) {
+        const int64_t ncap = std::max<int64_t>(nn, ix->cap + ix->cap / 2);
+        const size_t es = esize(dtype);
+        char *raw = (char *)ix->raw;
+        VQ_TRY(grow<char>(&raw, ix->n * ix->d * es, ncap * ix->d * es, st));
+        ix->raw = raw;
+        VQ_TRY(grow<__nv_bfloat16>(&ix->hi, ix->n * ix->dp, ncap * ix->dp, st));
+        if (dtype == VQ_F32) VQ_TRY(grow<__nv_bfloat16>(&ix->lo, ix->n * ix->dp, ncap * ix->dp, st));
+        VQ_TRY(grow<float2>(&ix->colparam, ix->n, ncap, st));
+        VQ_TRY(grow<float>(&ix->norm2, ix->n, ncap, st));
+        ix->cap = ncap;
+    }
+    const size_t es = esize(dtype);
+    char *dst = (char *)ix->raw + (size_t)ix->n * ix->d * es;
+    VQ_CUDA(cudaMemcpyAsync(dst, xb, (size_t)n * ix->d * es, cudaMemcpyDefault, st));
+    VQ_TRY(launch_prepare_rows(dst, dtype, n, ix->d, ix->dp, ix->hi + ix->n * ix->dp,
+                               ix->lo ? ix->lo + ix->n * ix->dp : nullptr, ix->colparam + ix->n, ix->norm2 + ix->n,
+                               ix->gmax_bits, st));
+    ix->n = nn;
+    // metadata no longer covers all rows
+    if (ix->label) { cudaFree(ix->label); ix->label = nullptr; }
+    if (ix->video) { cudaFree(ix->video); ix->video = nullptr; }
+    if (ix->seg_of_row) { cudaFree(ix->seg_of_row); ix->seg_of_row = nullptr; }
+    ix->seg_start.clear();
+    return VQ_OK;
+}
+
+int vq_index_set_meta(vq_index *ix, const int32_t *label, const int32_t *video, void *stream) {
+    VQ_CHECK(ix, VQ_ERR_INVALID, "index is NULL");
+    VQ_CHECK(ix->n > 0, VQ_ERR_STATE, "vq_index_set_meta before vq_index_add");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t bytes = (size_t)ix->n * 4;
+    if (ix->label) { cudaFree(ix->label); ix->label = nullptr; }
+    if (ix->video) { cudaFree(ix->video); ix->video = nullptr; }
+    if (label) {
+        VQ_CUDA(cudaMalloc(&ix->label, bytes));
+        VQ_CUDA(cudaMemcpyAsync(ix->label, label, bytes, cudaMemcpyDefault, st));
+    }
+    if (video) {
+        VQ_CUDA(cudaMalloc(&ix->video, bytes));
+        VQ_CUDA(cudaMemcpyAsync(ix->video, video, bytes, cudaMemcpyDefault, st));
+    }
+    return VQ_OK;
+}
+
+int vq_index_set_segments(vq_index *ix, const int64_t *seg_start, int64_t nseg, void *stream) {
+    VQ_CHECK(ix && seg_start, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(nseg >= 1, VQ_ERR_INVALID, "nseg=%lld", (long long)nseg);
+    VQ_CHECK(!is_device_ptr(seg_start), VQ_ERR_INVALID, "seg_start must be host memory");
+    VQ_CHECK(seg_start[0] == 0 && seg_start[nseg] == ix->n, VQ_ERR_INVALID,
+             "segments must cover rows [0,%lld)", (long long)ix->n);
+    for (int64_t v = 0; v < nseg; ++v)
+        VQ_CHECK(seg_start[v] <= seg_start[v + 1], VQ_ERR_INVALID, "seg_start not monotone at %lld", (long long)v);
+    cudaStream_t st = (cudaStream_t)stream;
+    ix->seg_start.assign(seg_start, seg_start + nseg + 1);
+    std::vector<int32_t> sor((size_t)ix->n);
+    for (int64_t v = 0; v < nseg; ++v)
+        for (int64_t r = seg_start[v]; r < seg_start[v + 1]; ++r) sor[(size_t)r] = (int32_t)v;
+    if (ix->seg_of_row) cudaFree(ix->seg_of_row);
+    if (ix->seg_start_dev) cudaFree(ix->seg_start_dev);
+    VQ_CUDA(cudaMalloc(&ix->seg_of_row, (size_t)ix->n * 4));
+    VQ_CUDA(cudaMalloc(&ix->seg_start_dev, (size_t)(nseg + 1) * 8));
+    VQ_CUDA(cudaMemcpyAsync(ix->seg_of_row, sor.data(), (size_t)ix->n * 4, cudaMemcpyHostToDevice, st));
+    VQ_CUDA(cudaMemcpyAsync(ix->seg_start_dev, seg_start, (size_t)(nseg + 1) * 8, cudaMemcpyHostToDevice, st));
+    VQ_CUDA(cudaStreamSynchronize(st));  // sor is a stack-lifetime staging buffer
+    return VQ_OK;
+}
+
+int vq_index_last_stats(const vq_index *ix, int64_t *out6) {
+    VQ_CHECK(ix && out6, VQ_ERR_INVALID, "NULL argument");
+    VQ_CUDA(cudaDeviceSynchronize());
+    int32_t c = 0;
+    VQ_CUDA(cudaMemcpy(&c, ix->unproven_count, 4, cudaMemcpyDeviceToHost));
+    for (int i = 0; i < 6; ++i) out6[i] = ix->stats[i];
+    out6[0] = c;
+    return VQ_OK;
+}
+
+}  // extern "C"
+
+#include "vq_api_search.inl"

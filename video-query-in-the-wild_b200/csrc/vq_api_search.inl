@@ -1,0 +1,475 @@
+// vq_api_search.inl -- search / evaluation orchestration (included by vq_api.cu).
+#include <stdlib.h>
+
+namespace vq {
+
+static int resolve_prec(const vq_index *ix) {
+    if (ix->prec != VQ_PREC_AUTO) return ix->prec;
+    return ix->dtype == VQ_F32 ? VQ_PREC_SPLIT3 : VQ_PREC_BF16;
+}
+
+static int choose_kprime(int k, int prec, int dtype) {
+    int base = k + std::max(16, k / 4);
+    if (dtype == VQ_F32 && prec == VQ_PREC_BF16) base = k * 5 / 2 + 32;  // single bf16 pass on fp32 data: wide band
+    base = (base + 31) / 32 * 32;
+    return std::min(kMaxKPrime, std::max(64, base));
+}
+
+// worst-case |coarse - (|q|^2 - d2_canonical)| <= eps_rel*|q|*|g|max + eps_abs*(|q|^2+|g|max^2)
+static void error_model(int prec, int dtype, int dp, float *eps_rel, float *eps_abs) {
+    const float u = 5.9604645e-8f;                          // 2^-24
+    const int npass = prec == VQ_PREC_SPLIT3 ? 3 : 1;
+    float rel = 2.0f * npass * 2.0f * dp * u;               // fp32 accumulation inside the tensor core, x2 (score = 2*dot)
+    if (dtype == VQ_F32) rel += prec == VQ_PREC_SPLIT3 ? 2.4e-5f : 8.0e-3f;  // operand rounding to bf16 (split / single)
+    *eps_rel = rel;
+    *eps_abs = 4.0f * dp * u;                               // |g|^2 reduction + the canonical chain's own rounding
+    if (getenv("VQ_DEBUG_FORCE_FALLBACK")) *eps_abs = 1e30f;  // test hook: no query can be proven
+}
+
+// Split the gallery into chunks so that (query blocks x chunks) fills the SMs evenly.
+static void plan_chunks(const vq_index *ix, int64_t nq, int kprime, bool segmax, std::vector<int64_t> *cs) {
+    const int sms = sm_count();
+    const int64_t n = ix->n;
+    const int64_t ntiles = (n + kTileN - 1) / kTileN;
+    const int64_t nqb = (nq + kTileM - 1) / kTileM;
+    int64_t max_chunks = std::min<int64_t>(ntiles, (int64_t)(128 * 64) / kprime);
+    max_chunks = std::min<int64_t>(max_chunks, std::max<int64_t>(1, ntiles / 8));  // >= 8 tiles per chunk
+    max_chunks = std::max<int64_t>(1, std::min<int64_t>(max_chunks, 64));
+    int64_t best = 1;
+    double best_eff = -1.0;
+    for (int64_t c = 1; c <= max_chunks; ++c) {
+        const int64_t units = nqb * c;
+        const double eff = (double)units / (double)(((units + sms - 1) / sms) * sms);
+        if (eff > best_eff + 0.02) {
+            best_eff = eff;
+            best = c;
+        }
+    }
+    cs->clear();
+    cs->push_back(0);
+    for (int64_t c = 1; c < best; ++c) {
+        int64_t target = (ntiles * c / best) * kTileN;
+        if (segmax) {  // move to the next video boundary
+            auto it = std::lower_bound(ix->seg_start.begin(), ix->seg_start.end(), target);
+            target = it == ix->seg_start.end() ? n : *it;
+        }
+        if (target > cs->back() && target < n) cs->push_back(target);
+    }
+    cs->push_back(n);
+}
+
+template <typename T>
+static int ensure(T **p, size_t *cap, size_t need) {
+    if (*cap >= need) return VQ_OK;
+    if (*p) {
+        VQ_CUDA(cudaDeviceSynchronize());
+        cudaFree(*p);
+        *p = nullptr;
+        *cap = 0;
+    }
+    if (cudaMalloc(p, need * sizeof(T)) != cudaSuccess) {
+        cudaGetLastError();
+        set_error("out of device memory for a %zu-byte workspace", need * sizeof(T));
+        return VQ_ERR_NOMEM;
+    }
+    *cap = need;
+    return VQ_OK;
+}
+
+// All pointers are device pointers here.
+static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int k, bool segmax, const int32_t *ign,
+                       int n_ign, float *D, int64_t *I, int64_t *seg_out, cudaStream_t st) {
+    const int prec = resolve_prec(ix);
+    int launches = 0;
+    VQ_CUDA(cudaMemsetAsync(ix->unproven_count, 0, 4, st));
+    if (prec == VQ_PREC_EXACT) {
+        FallbackParams f{};
+        f.nq = nq; f.n = ix->n; f.d = ix->d; f.dtype = dtype; f.q = xq; f.g = ix->raw;
+        f.col_video = ix->video; f.q_ignore = ign; f.n_ign = n_ign;
+        f.seg_of_row = segmax ? ix->seg_of_row : nullptr;
+        f.seg_start = segmax ? ix->seg_start_dev : nullptr;
+        f.nseg = segmax ? (int64_t)ix->seg_start.size() - 1 : 0;
+        f.k = k; f.out_d2 = D; f.out_idx = I; f.out_seg = seg_out;
+        VQ_TRY(launch_exact_topk(f, (int)std::min<int64_t>(nq, 4 * sm_count()), st));
+        ix->stats[1] = 0; ix->stats[2] = 0; ix->stats[3] = 0; ix->stats[4] = 0; ix->stats[5] = 1;
+        return VQ_OK;
+    }
+    const int kprime = choose_kprime(k, prec, dtype);
+    VQ_CHECK(k <= kprime, VQ_ERR_CAPACITY, "k=%d exceeds the streaming top-k limit %d", k, kMaxKPrime);
+    // query operand planes
+    Tmp qhi, qlo;
+    VQ_TRY(qhi.alloc((size_t)nq * ix->dp * 2, st));
+    const bool split = prec == VQ_PREC_SPLIT3;
+    if (split) VQ_TRY(qlo.alloc((size_t)nq * ix->dp * 2, st));
+    VQ_TRY(launch_prepare_rows(xq, dtype, nq, ix->d, ix->dp, (__nv_bfloat16 *)qhi.p,
+                               split ? (__nv_bfloat16 *)qlo.p : nullptr, nullptr, nullptr, nullptr, st));
+    ++launches;
+    CUtensorMap maps[4];
+    VQ_TRY(make_map(&maps[0], qhi.p, nq, ix->dp, kTileM));
+    VQ_TRY(make_map(&maps[1], split ? qlo.p : qhi.p, nq, ix->dp, kTileM));
+    VQ_TRY(make_map(&maps[2], ix->hi, ix->n, ix->dp, kTileN));
+    VQ_TRY(make_map(&maps[3], split ? (void *)ix->lo : (void *)ix->hi, ix->n, ix->dp, kTileN));
+    // work decomposition
+    std::vector<int64_t> cs;
+    plan_chunks(ix, nq, kprime, segmax, &cs);
+    const int n_chunks = (int)cs.size() - 1;
+    const int n_qblocks = (int)((nq + kTileM - 1) / kTileM);
+    const size_t units = (size_t)n_chunks * n_qblocks;
+    VQ_TRY(ensure(&ix->chunk_start_dev, &ix->chunk_cap, cs.size()));
+    VQ_CUDA(cudaMemcpyAsync(ix->chunk_start_dev, cs.data(), cs.size() * 8, cudaMemcpyHostToDevice, st));
+    VQ_TRY(ensure(&ix->cand, &ix->cand_bytes, units * kTileM * kCandCap));
+    if (ix->cand_units < units) {
+        if (ix->cand_cnt) { VQ_CUDA(cudaDeviceSynchronize()); cudaFree(ix->cand_cnt); cudaFree(ix->cand_tau); }
+        VQ_CUDA(cudaMalloc(&ix->cand_cnt, units * kTileM * 4));
+        VQ_CUDA(cudaMalloc(&ix->cand_tau, units * kTileM * 4));
+        ix->cand_units = units;
+    }
+    VQ_TRY(ensure(&ix->unproven, &ix->unproven_cap, (size_t)nq));
+
+    GemmTopkParams gp{};
+    gp.nq = nq; gp.n = ix->n; gp.kb_count = ix->dp / 64; gp.n_qblocks = n_qblocks; gp.n_chunks = n_chunks;
+    gp.chunk_start = ix->chunk_start_dev; gp.colparam = ix->colparam;
+    gp.col_video = n_ign > 0 ? ix->video : nullptr;
+    gp.col_seg = segmax ? ix->seg_of_row : nullptr;
+    gp.q_ignore = n_ign > 0 ? ign : nullptr; gp.n_ign = n_ign; gp.kprime = kprime;
+    gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau;
+    const int grid = (int)std::min<size_t>(units, (size_t)sm_count());
+    VQ_TRY(launch_gemm_topk(maps, gp, split ? 3 : 1, segmax, grid, st));
+    ++launches;
+
+    SelectParams sp{};
+    sp.nq = nq; sp.n = ix->n; sp.d = ix->d; sp.dtype = dtype; sp.q = xq; sp.g = ix->raw;
+    sp.n_qblocks = n_qblocks; sp.n_chunks = n_chunks; sp.cand = ix->cand; sp.cand_cnt = ix->cand_cnt;
+    sp.cand_tau = ix->cand_tau; sp.kprime = kprime; sp.k = k;
+    error_model(prec, ix->dtype, ix->dp, &sp.eps_rel, &sp.eps_abs);
+    sp.gmax_norm2_bits = ix->gmax_bits;
+    sp.seg_of_row = segmax ? ix->seg_of_row : nullptr;
+    sp.seg_start = segmax ? ix->seg_start_dev : nullptr;
+    sp.out_d2 = D; sp.out_idx = I; sp.out_seg = seg_out;
+    sp.unproven = ix->unproven; sp.unproven_count = ix->unproven_count;
+    VQ_TRY(launch_select(sp, st));
+    ++launches;
+
+    FallbackParams f{};
+    f.nq = nq; f.n = ix->n; f.d = ix->d; f.dtype = dtype; f.q = xq; f.g = ix->raw;
+    f.col_video = ix->video; f.q_ignore = n_ign > 0 ? ign : nullptr; f.n_ign = n_ign;
+    f.seg_of_row = segmax ? ix->seg_of_row : nullptr;
+    f.seg_start = segmax ? ix->seg_start_dev : nullptr;
+    f.nseg = segmax ? (int64_t)ix->seg_start.size() - 1 : 0;
+    f.k = k; f.out_d2 = D; f.out_idx = I; f.out_seg = seg_out;
+    f.unproven = ix->unproven; f.unproven_count = ix->unproven_count;
+    VQ_TRY(launch_exact_topk(f, (int)std::min<int64_t>(nq, 2 * sm_count()), st));
+    ++launches;
+
+    int64_t tiles = 0;
+    for (int c = 0; c < n_chunks; ++c) tiles += (cs[c + 1] - cs[c] + kTileN - 1) / kTileN;
+    ix->stats[1] = tiles * n_qblocks;
+    ix->stats[2] = kprime;
+    ix->stats[3] = (int64_t)units;
+    ix->stats[4] = n_chunks;
+    ix->stats[5] = launches;
+    return VQ_OK;
+}
+
+static int check_search_args(const vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k) {
+    VQ_CHECK(ix && xq, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(ix->n > 0, VQ_ERR_STATE, "search on an empty index");
+    VQ_CHECK(dtype == ix->dtype, VQ_ERR_INVALID, "query dtype %d differs from the index dtype %d", dtype, ix->dtype);
+    VQ_CHECK(nq >= 0 && nq < (1ll << 31), VQ_ERR_INVALID, "nq=%lld", (long long)nq);
+    VQ_CHECK(k >= 1, VQ_ERR_INVALID, "k=%lld", (long long)k);
+    return VQ_OK;
+}
+
+}  // namespace vq
+
+extern "C" {
+
+int vq_index_search(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k, const int32_t *ignore_video,
+                    int n_ignore, float *D, int64_t *I, void *stream) {
+    VQ_TRY(check_search_args(ix, xq, nq, dtype, k));
+    VQ_CHECK(D && I, VQ_ERR_INVALID, "NULL output");
+    VQ_CHECK(k <= ix->n, VQ_ERR_INVALID, "k=%lld exceeds ntotal=%lld", (long long)k, (long long)ix->n);
+    VQ_CHECK(n_ignore >= 0 && n_ignore <= kMaxIgnore, VQ_ERR_INVALID, "n_ignore=%d (max %d)", n_ignore, kMaxIgnore);
+    VQ_CHECK(!(ignore_video && n_ignore > 0) || ix->video, VQ_ERR_STATE, "ignore list given but no video ids set");
+    VQ_CHECK(k <= kMaxKPrime, VQ_ERR_CAPACITY,
+             "k=%lld: the streaming top-k path serves k <= %d; use vq_index_eval_trimmed for full-list metrics",
+             (long long)k, kMaxKPrime);
+    if (nq == 0) return VQ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int n_ign = ignore_video ? n_ignore : 0;
+    In q, ig;
+    Out oD, oI;
+    VQ_TRY(q.bind(xq, (size_t)nq * ix->d * esize(dtype), st));
+    VQ_TRY(ig.bind(ignore_video, (size_t)nq * n_ign * 4, st));
+    VQ_TRY(oD.bind(D, (size_t)nq * k * 4, st));
+    VQ_TRY(oI.bind(I, (size_t)nq * k * 8, st));
+    VQ_TRY(search_core(ix, q.dev, nq, dtype, (int)k, false, ig.as<int32_t>(), n_ign, oD.as<float>(), oI.as<int64_t>(),
+                       nullptr, st));
+    VQ_TRY(oD.finish(st));
+    VQ_TRY(oI.finish(st));
+    if (oD.host || oI.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_index_search_segmax(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k, int64_t *video,
+                           int64_t *row, float *D, void *stream) {
+    VQ_TRY(check_search_args(ix, xq, nq, dtype, k));
+    VQ_CHECK(video && row && D, VQ_ERR_INVALID, "NULL output");
+    VQ_CHECK(!ix->seg_start.empty(), VQ_ERR_STATE, "vq_index_set_segments has not been called");
+    const int64_t nseg = (int64_t)ix->seg_start.size() - 1;
+    VQ_CHECK(k <= nseg, VQ_ERR_INVALID, "k=%lld exceeds the number of videos %lld", (long long)k, (long long)nseg);
+    VQ_CHECK(k <= kMaxKPrime, VQ_ERR_CAPACITY, "k=%lld exceeds %d", (long long)k, kMaxKPrime);
+    if (nq == 0) return VQ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    In q;
+    Out oV, oR, oD;
+    VQ_TRY(q.bind(xq, (size_t)nq * ix->d * esize(dtype), st));
+    VQ_TRY(oV.bind(video, (size_t)nq * k * 8, st));
+    VQ_TRY(oR.bind(row, (size_t)nq * k * 8, st));
+    VQ_TRY(oD.bind(D, (size_t)nq * k * 4, st));
+    VQ_TRY(search_core(ix, q.dev, nq, dtype, (int)k, true, nullptr, 0, oD.as<float>(), oR.as<int64_t>(),
+                       oV.as<int64_t>(), st));
+    VQ_TRY(oV.finish(st));
+    VQ_TRY(oR.finish(st));
+    VQ_TRY(oD.finish(st));
+    if (oV.host || oR.host || oD.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_index_eval_trimmed(vq_index *ix, const void *xq, int64_t nq, int dtype, const int32_t *q_label,
+                          const int32_t *ignore_video, int n_ignore, double *ap, double *recall, int64_t *top_idx,
+                          void *stream) {
+    VQ_TRY(check_search_args(ix, xq, nq, dtype, 1));
+    VQ_CHECK(q_label && ap && recall, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(ix->label, VQ_ERR_STATE, "vq_index_set_meta (labels) has not been called");
+    VQ_CHECK(n_ignore >= 0 && n_ignore <= kMaxIgnore, VQ_ERR_INVALID, "n_ignore=%d (max %d)", n_ignore, kMaxIgnore);
+    const int n_ign = ignore_video ? n_ignore : 0;
+    VQ_CHECK(n_ign == 0 || ix->video, VQ_ERR_STATE, "ignore list given but no video ids set");
+    if (nq == 0) return VQ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    In q, ql, ig;
+    Out oA, oR, oT;
+    VQ_TRY(q.bind(xq, (size_t)nq * ix->d * esize(dtype), st));
+    VQ_TRY(ql.bind(q_label, (size_t)nq * 4, st));
+    VQ_TRY(ig.bind(ignore_video, (size_t)nq * n_ign * 4, st));
+    VQ_TRY(oA.bind(ap, (size_t)nq * 8, st));
+    VQ_TRY(oR.bind(recall, (size_t)nq * 3 * 8, st));
+    VQ_TRY(oT.bind(top_idx, (size_t)nq * 100 * 8, st));
+    // full-list AP / R@N: canonical scores for a tile of queries, then the rank-count reduction
+    const int64_t tile_q = std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(1ll << 31) / std::max<int64_t>(1, ix->n * 4)));
+    Tmp d2, ovf;
+    VQ_TRY(d2.alloc((size_t)tile_q * ix->n * 4, st));
+    VQ_TRY(ovf.alloc(4, st));
+    int launches = 0;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        const int pcap2 = attempt == 0 ? 1024 : kMaxPositives;
+        VQ_CUDA(cudaMemsetAsync(ovf.p, 0, 4, st));
+        for (int64_t q0 = 0; q0 < nq; q0 += tile_q) {
+            const int64_t tq = std::min(tile_q, nq - q0);
+            const char *qt = (const char *)q.dev + (size_t)q0 * ix->d * esize(dtype);
+            VQ_TRY(launch_l2sq_all(qt, ix->raw, dtype, tq, ix->n, ix->d, (float *)d2.p, st));
+            ApRowsParams a{};
+            a.nq_tile = tq; a.n = ix->n; a.d2 = (const float *)d2.p; a.g_label = ix->label; a.g_video = ix->video;
+            a.q_label = ql.as<int32_t>() + q0;
+            a.q_ignore = n_ign ? ig.as<int32_t>() + q0 * n_ign : nullptr;
+            a.n_ign = n_ign; a.ap = oA.as<double>() + q0; a.recall = oR.as<double>() + q0 * 3;
+            a.top_idx = nullptr; a.overflow = (int32_t *)ovf.p;
+            VQ_TRY(launch_ap_rows(a, pcap2, st));
+            launches += 2;
+        }
+        int32_t h = 0;
+        VQ_CUDA(cudaMemcpyAsync(&h, ovf.p, 4, cudaMemcpyDeviceToHost, st));
+        VQ_CUDA(cudaStreamSynchronize(st));
+        if (!h) break;
+        VQ_CHECK(attempt == 0, VQ_ERR_CAPACITY, "a query has more than %d positives in the gallery", kMaxPositives - 1);
+    }
+    if (top_idx) {  // the first 100 survivors in rank order (cm_dict side data, :437-442)
+        const int64_t k = std::min<int64_t>(100, ix->n);
+        Tmp tD, tI;
+        VQ_TRY(tD.alloc((size_t)nq * k * 4, st));
+        VQ_TRY(tI.alloc((size_t)nq * k * 8, st));
+        VQ_TRY(search_core(ix, q.dev, nq, dtype, (int)k, false, ig.as<int32_t>(), n_ign, (float *)tD.p, (int64_t *)tI.p,
+                           nullptr, st));
+        launches += (int)ix->stats[5];
+        if (k == 100) {
+            VQ_CUDA(cudaMemcpyAsync(oT.dev, tI.p, (size_t)nq * 100 * 8, cudaMemcpyDeviceToDevice, st));
+        } else {
+            VQ_CUDA(cudaMemsetAsync(oT.dev, 0xff, (size_t)nq * 100 * 8, st));
+            VQ_CUDA(cudaMemcpy2DAsync(oT.dev, 100 * 8, tI.p, (size_t)k * 8, (size_t)k * 8, (size_t)nq,
+                                      cudaMemcpyDeviceToDevice, st));
+        }
+    }
+    ix->stats[5] = launches;
+    VQ_TRY(oA.finish(st));
+    VQ_TRY(oR.finish(st));
+    VQ_TRY(oT.finish(st));
+    VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_average_precision(const int32_t *y_true, const double *y_score, const int64_t *offsets, int64_t nlists,
+                         double *ap, void *stream) {
+    VQ_CHECK(y_true && y_score && offsets && ap, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(!is_device_ptr(offsets), VQ_ERR_INVALID, "offsets must be host memory");
+    VQ_TRY(check_device());
+    if (nlists == 0) return VQ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t total = offsets[nlists];
+    In yt, ys, of;
+    Out oA;
+    Tmp ovf;
+    VQ_TRY(yt.bind(y_true, (size_t)total * 4, st));
+    VQ_TRY(ys.bind(y_score, (size_t)total * 8, st));
+    VQ_TRY(of.bind(offsets, (size_t)(nlists + 1) * 8, st));
+    VQ_TRY(oA.bind(ap, (size_t)nlists * 8, st));
+    VQ_TRY(ovf.alloc(4, st));
+    VQ_CUDA(cudaMemsetAsync(ovf.p, 0, 4, st));
+    VQ_TRY(launch_average_precision(yt.as<int32_t>(), ys.as<double>(), of.as<int64_t>(), nlists, 0, oA.as<double>(),
+                                    (int32_t *)ovf.p, st));
+    int32_t h = 0;
+    VQ_CUDA(cudaMemcpyAsync(&h, ovf.p, 4, cudaMemcpyDeviceToHost, st));
+    VQ_TRY(oA.finish(st));
+    VQ_CUDA(cudaStreamSynchronize(st));
+    VQ_CHECK(!h, VQ_ERR_CAPACITY, "a list has more than %d positives", kMaxPositives);
+    return VQ_OK;
+}
+
+int vq_nms1d_segmented(const double *dets, const int64_t *offsets, int64_t nseg, double thresh, uint8_t *keep,
+                       void *stream) {
+    VQ_CHECK(dets && offsets && keep, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(!is_device_ptr(offsets), VQ_ERR_INVALID, "offsets must be host memory");
+    VQ_TRY(check_device());
+    if (nseg == 0) return VQ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t total = offsets[nseg];
+    In dd, of;
+    Out oK;
+    Tmp dead;
+    VQ_TRY(dd.bind(dets, (size_t)total * 3 * 8, st));
+    VQ_TRY(of.bind(offsets, (size_t)(nseg + 1) * 8, st));
+    VQ_TRY(oK.bind(keep, (size_t)total, st));
+    VQ_TRY(dead.alloc((size_t)total, st));
+    VQ_TRY(launch_nms1d(dd.as<double>(), of.as<int64_t>(), nseg, thresh, oK.as<uint8_t>(), (uint8_t *)dead.p, st));
+    VQ_TRY(oK.finish(st));
+    if (oK.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_pdist(const float *A, int64_t B, int d, float eps, float *dist, void *stream) {
+    VQ_CHECK(A && dist, VQ_ERR_INVALID, "NULL argument");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In a;
+    Out o;
+    VQ_TRY(a.bind(A, (size_t)B * d * 4, st));
+    VQ_TRY(o.bind(dist, (size_t)B * B * 4, st));
+    VQ_TRY(launch_pdist(a.as<float>(), B, d, eps, o.as<float>(), st));
+    VQ_TRY(o.finish(st));
+    if (o.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int64_t B, int d, float margin,
+                         float *loss, float *grad, int32_t *trip, void *stream) {
+    VQ_CHECK(emb && labels && loss, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(G >= 1 && B >= 1 && d >= 1, VQ_ERR_INVALID, "bad shape G=%lld B=%lld d=%d", (long long)G, (long long)B, d);
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In e, l;
+    Out oL, oG, oT;
+    Tmp lt, tr;
+    VQ_TRY(e.bind(emb, (size_t)G * B * d * 4, st));
+    VQ_TRY(l.bind(labels, (size_t)G * B * 4, st));
+    VQ_TRY(oL.bind(loss, (size_t)G * 4, st));
+    VQ_TRY(oG.bind(grad, (size_t)G * B * d * 4, st));
+    VQ_TRY(oT.bind(trip, (size_t)G * B * 3 * 4, st));
+    VQ_TRY(lt.alloc((size_t)G * B * 4, st));
+    int32_t *tdev = oT.as<int32_t>();
+    if (!tdev) {
+        VQ_TRY(tr.alloc((size_t)G * B * 3 * 4, st));
+        tdev = (int32_t *)tr.p;
+    }
+    VQ_TRY(launch_triplet_batchhard(e.as<float>(), l.as<int32_t>(), G, B, d, margin, oL.as<float>(), oG.as<float>(),
+                                    tdev, (float *)lt.p, st));
+    VQ_TRY(oL.finish(st));
+    VQ_TRY(oG.finish(st));
+    VQ_TRY(oT.finish(st));
+    if (oL.host || oG.host || oT.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_triplet_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T, float margin, float *loss,
+                     float *grad, void *stream) {
+    VQ_CHECK(emb && loss && (trip || T == 0), VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(B >= 1 && d >= 1 && T >= 0, VQ_ERR_INVALID, "bad shape");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!is_device_ptr(trip))
+        for (int64_t i = 0; i < T * 3; ++i)
+            VQ_CHECK(trip[i] >= 0 && trip[i] < B, VQ_ERR_INVALID, "triplet index %d out of range", trip[i]);
+    In e, t;
+    Out oL, oG;
+    Tmp lt;
+    VQ_TRY(e.bind(emb, (size_t)B * d * 4, st));
+    VQ_TRY(t.bind(trip, (size_t)T * 3 * 4, st));
+    VQ_TRY(oL.bind(loss, 4, st));
+    VQ_TRY(oG.bind(grad, (size_t)B * d * 4, st));
+    VQ_TRY(lt.alloc((size_t)std::max<int64_t>(T, 1) * 4, st));
+    VQ_TRY(launch_triplet_given(e.as<float>(), B, d, t.as<int32_t>(), T, margin, oL.as<float>(), oG.as<float>(),
+                                (float *)lt.p, st));
+    VQ_TRY(oL.finish(st));
+    VQ_TRY(oG.finish(st));
+    if (oL.host || oG.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_pool_normalize(const float *x, int64_t B, int C, int T, float *out, void *stream) {
+    VQ_CHECK(x && out, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(B >= 0 && C >= 1 && T >= 1 && T <= 8192, VQ_ERR_INVALID, "bad shape");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In a;
+    Out o;
+    VQ_TRY(a.bind(x, (size_t)B * C * T * 4, st));
+    VQ_TRY(o.bind(out, (size_t)B * C * 4, st));
+    VQ_TRY(launch_pool_normalize(a.as<float>(), B, C, T, o.as<float>(), st));
+    VQ_TRY(o.finish(st));
+    if (o.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k, float *out_d2, int64_t *out_idx,
+                  void *stream) {
+    VQ_CHECK(d2 && idx && out_d2 && out_idx, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(G >= 1 && nq >= 0 && k >= 1, VQ_ERR_INVALID, "bad shape");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In a, b;
+    Out oD, oI;
+    VQ_TRY(a.bind(d2, (size_t)G * nq * k * 4, st));
+    VQ_TRY(b.bind(idx, (size_t)G * nq * k * 8, st));
+    VQ_TRY(oD.bind(out_d2, (size_t)nq * k * 4, st));
+    VQ_TRY(oI.bind(out_idx, (size_t)nq * k * 8, st));
+    VQ_TRY(launch_topk_merge(a.as<float>(), b.as<int64_t>(), G, nq, k, oD.as<float>(), oI.as<int64_t>(), st));
+    VQ_TRY(oD.finish(st));
+    VQ_TRY(oI.finish(st));
+    if (oD.host || oI.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_l2sq(const float *q, const float *g, int64_t nq, int64_t n, int d, float *out, void *stream) {
+    VQ_CHECK(q && g && out, VQ_ERR_INVALID, "NULL argument");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In a, b;
+    Out o;
+    VQ_TRY(a.bind(q, (size_t)nq * d * 4, st));
+    VQ_TRY(b.bind(g, (size_t)n * d * 4, st));
+    VQ_TRY(o.bind(out, (size_t)nq * n * 4, st));
+    VQ_TRY(launch_l2sq_all(a.dev, b.dev, VQ_F32, nq, n, d, o.as<float>(), st));
+    VQ_TRY(o.finish(st));
+    if (o.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,123 @@
+// vq_blocksel.cuh -- block-wide selection / sorting utilities on u64 keys held in shared memory.
+// All functions must be called by every thread of the block (they contain __syncthreads()).
+#pragma once
+#include "vq_common.cuh"
+
+namespace vq {
+
+// block-wide sum of a per-thread int; result returned to all threads.  scratch: int[34] smem.
+__device__ __forceinline__ int block_sum(int v, int *scratch) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    v = __reduce_add_sync(0xffffffffu, v);
+    __syncthreads();  // scratch free
+    if (lane == 0) scratch[warp] = v;
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    int t = (lane < nw) ? scratch[lane] : 0;
+    t = __reduce_add_sync(0xffffffffu, t);
+    return t;
+}
+
+// K-th smallest key (1-based K) among keys[0..n).  Requires 1 <= K <= n.  Bit-by-bit bisection:
+// 64 rounds of a block-wide count.
+__device__ __forceinline__ uint64_t block_kth_smallest(const uint64_t *keys, int n, int K, int *scratch) {
+    uint64_t P = 0;
+    for (int bit = 63; bit >= 0; --bit) {
+        const uint64_t c = P | (1ull << bit);
+        int cnt = 0;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) cnt += keys[i] < c ? 1 : 0;
+        cnt = block_sum(cnt, scratch);
+        if (cnt < K) P = c;  // fewer than K keys below c: the K-th smallest has this bit set
+    }
+    return P;
+}
+
+// K-th largest value of the HIGH 32-bit words (1-based), requires 1 <= K <= n.
+__device__ __forceinline__ uint32_t block_kth_largest_hi(const uint64_t *keys, int n, int K, int *scratch) {
+    uint32_t T = 0;
+    for (int bit = 31; bit >= 0; --bit) {
+        const uint32_t c = T | (1u << bit);
+        int cnt = 0;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) cnt += (uint32_t)(keys[i] >> 32) >= c ? 1 : 0;
+        cnt = block_sum(cnt, scratch);
+        if (cnt >= K) T = c;
+    }
+    return T;
+}
+
+// In-place bitonic sort, ascending, of keys[0..n2) where n2 is a power of two.
+__device__ __forceinline__ void block_bitonic_sort(uint64_t *keys, int n2) {
+    for (int k = 2; k <= n2; k <<= 1) {
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            __syncthreads();
+            for (int i = threadIdx.x; i < n2; i += blockDim.x) {
+                int ixj = i ^ j;
+                if (ixj > i) {
+                    uint64_t a = keys[i], b = keys[ixj];
+                    bool up = (i & k) == 0;
+                    if ((a > b) == up) {
+                        keys[i] = b;
+                        keys[ixj] = a;
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+}
+
+__host__ __device__ __forceinline__ int next_pow2(int v) {
+    int p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+// canonical d2 between a query held in shared memory (fp32) and one gallery row in global
+// memory; T = float or __nv_bfloat16.  Sequential in i, bit-identical to the oracle.
+template <typename T>
+__device__ __forceinline__ float canon_d2_row(const float *qs, const T *g, int d);
+
+template <>
+__device__ __forceinline__ float canon_d2_row<float>(const float *qs, const float *g, int d) {
+    float acc = 0.f;
+    int i = 0;
+    if ((((uintptr_t)g) & 15) == 0) {
+        for (; i + 4 <= d; i += 4) {
+            const float4 v = *reinterpret_cast<const float4 *>(g + i);
+            acc = canon_step(acc, qs[i], v.x);
+            acc = canon_step(acc, qs[i + 1], v.y);
+            acc = canon_step(acc, qs[i + 2], v.z);
+            acc = canon_step(acc, qs[i + 3], v.w);
+        }
+    }
+    for (; i < d; ++i) acc = canon_step(acc, qs[i], g[i]);
+    return acc;
+}
+
+template <>
+__device__ __forceinline__ float canon_d2_row<__nv_bfloat16>(const float *qs, const __nv_bfloat16 *g, int d) {
+    float acc = 0.f;
+    int i = 0;
+    if ((((uintptr_t)g) & 15) == 0) {
+        for (; i + 8 <= d; i += 8) {
+            const uint4 v = *reinterpret_cast<const uint4 *>(g + i);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                acc = canon_step(acc, qs[i + 2 * t], __uint_as_float(w[t] << 16));
+                acc = canon_step(acc, qs[i + 2 * t + 1], __uint_as_float(w[t] & 0xffff0000u));
+            }
+        }
+    }
+    for (; i < d; ++i) acc = canon_step(acc, qs[i], __bfloat162float(g[i]));
+    return acc;
+}
+
+template <typename T>
+__device__ __forceinline__ float to_f32(T v);
+template <>
+__device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+
+}  // namespace vq

@@ -1,0 +1,217 @@
+// vq_exact.cu -- canonical (oracle-identical) CUDA-core scoring.
+//   l2sq_all    : all-pairs d2 tile kernel, out[nq,n]; feeds the full-list AP reduction
+//                 (vq_metrics.cu) and the k > kMaxKPrime search path.
+//   exact_topk  : per-query exact streaming top-k over the whole gallery -- the fallback for
+//                 queries the tensor-core pre-filter could not prove, and VQ_PREC_EXACT mode.
+// Arithmetic: d2 = sequential fmaf chain over i (vq_common.cuh:canon_step), the restatement of
+// faiss.IndexFlatL2.search's squared L2 (dataloader_baseline.py:1592-1597).
+#include "vq_blocksel.cuh"
+#include "vq_kernels.h"
+
+namespace vq {
+
+// ---------------------------------------------------------------------------------------
+// all-pairs: 64 x 64 output tile per 256-thread block, 4 x 4 per thread, k staged 32 at a time
+// ---------------------------------------------------------------------------------------
+static constexpr int AT = 64, AK = 32, APAD = 4;
+
+template <typename T>
+__global__ void __launch_bounds__(256) l2sq_all_kernel(const T *__restrict__ q, const T *__restrict__ g,
+                                                       int64_t nq, int64_t n, int d, float *__restrict__ out) {
+    __shared__ __align__(16) float sQ[AK][AT + APAD];
+    __shared__ __align__(16) float sG[AK][AT + APAD];
+    const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int64_t q0 = (int64_t)blockIdx.y * AT, g0 = (int64_t)blockIdx.x * AT;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    const int lr = tid >> 2, lk = (tid & 3) * 8;  // loader: row lr, 8 consecutive k
+    for (int k0 = 0; k0 < d; k0 += AK) {
+        __syncthreads();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int k = k0 + lk + e;
+            float vq_ = 0.f, vg_ = 0.f;
+            if (k < d) {
+                if (q0 + lr < nq) vq_ = to_f32<T>(q[(q0 + lr) * d + k]);
+                if (g0 + lr < n) vg_ = to_f32<T>(g[(g0 + lr) * d + k]);
+            }
+            sQ[lk + e][lr] = vq_;
+            sG[lk + e][lr] = vg_;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < AK; ++kk) {
+            const float4 a4 = *reinterpret_cast<const float4 *>(&sQ[kk][ty * 4]);
+            const float4 b4 = *reinterpret_cast<const float4 *>(&sG[kk][tx * 4]);
+            const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = canon_step(acc[a][b], av[a], bv[b]);
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+        const int64_t qi = q0 + ty * 4 + a;
+        if (qi >= nq) continue;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const int64_t gi = g0 + tx * 4 + b;
+            if (gi < n) out[qi * n + gi] = acc[a][b];
+        }
+    }
+}
+
+int launch_l2sq_all(const void *q, const void *g, int dtype, int64_t nq, int64_t n, int d, float *out,
+                    cudaStream_t st) {
+    if (nq == 0 || n == 0) return VQ_OK;
+    dim3 grid((unsigned)((n + AT - 1) / AT), (unsigned)((nq + AT - 1) / AT));
+    VQ_CHECK(grid.y <= 65535, VQ_ERR_INVALID, "l2sq_all: too many query tiles in one launch");
+    if (dtype == VQ_F32)
+        l2sq_all_kernel<float><<<grid, 256, 0, st>>>((const float *)q, (const float *)g, nq, n, d, out);
+    else
+        l2sq_all_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)q, (const __nv_bfloat16 *)g,
+                                                              nq, n, d, out);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// exact streaming top-k, one block per query (grid-stride over the query list)
+// ---------------------------------------------------------------------------------------
+static constexpr int kExThreads = 256;
+static constexpr int kExCap = 4096;  // key buffer; must be >= 2*k and leave kExThreads of headroom
+
+template <typename T, bool SEGMAX>
+__global__ void __launch_bounds__(kExThreads) exact_topk_kernel(const FallbackParams p) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint64_t *keys = (uint64_t *)sm;          // [kExCap]
+    float *qs = (float *)(keys + kExCap);     // [d]
+    int *scratch = (int *)(qs + p.d);         // [40]; [36] = count, [37] = ignore list base
+    int *ign = scratch + 40;                  // [kMaxIgnore]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nlist = p.unproven_count ? *p.unproven_count : (int)p.nq;
+    const int ksort = next_pow2(p.k);
+
+    for (int li = blockIdx.x; li < nlist; li += gridDim.x) {
+        const int64_t q = p.unproven ? p.unproven[li] : li;
+        __syncthreads();
+        const T *qrow = (const T *)p.q + q * p.d;
+        for (int i = tid; i < p.d; i += kExThreads) qs[i] = to_f32<T>(qrow[i]);
+        if (tid < kMaxIgnore) ign[tid] = (tid < p.n_ign) ? p.q_ignore[q * p.n_ign + tid] : -1;
+        if (tid == 0) scratch[36] = 0;
+        __syncthreads();
+        uint64_t thr = ~0ull;  // keep keys < thr
+        const int64_t nitems = SEGMAX ? p.nseg : p.n;
+        const int per_round = SEGMAX ? kExThreads / 32 : kExThreads;
+        for (int64_t base = 0; base < nitems; base += per_round) {
+            uint64_t key = ~0ull;
+            if (!SEGMAX) {
+                const int64_t j = base + tid;
+                if (j < p.n) {
+                    bool masked = false;
+                    if (p.n_ign > 0) {
+                        const int v = p.col_video[j];
+                        for (int z = 0; z < p.n_ign; ++z) masked |= (v == ign[z]);
+                    }
+                    if (!masked) key = make_key_asc(canon_d2_row<T>(qs, (const T *)p.g + j * p.d, p.d), (uint32_t)j);
+                }
+            } else {
+                const int64_t v = base + warp;
+                if (v < p.nseg) {
+                    const int64_t s0 = p.seg_start[v], s1 = p.seg_start[v + 1];
+                    bool masked = false;
+                    if (p.n_ign > 0 && s0 < s1) {
+                        const int vid = p.col_video[s0];
+                        for (int z = 0; z < p.n_ign; ++z) masked |= (vid == ign[z]);
+                    }
+                    uint64_t best = ~0ull;
+                    if (!masked)
+                        for (int64_t rr = s0 + lane; rr < s1; rr += 32) {
+                            const uint64_t kk =
+                                make_key_asc(canon_d2_row<T>(qs, (const T *)p.g + rr * p.d, p.d), (uint32_t)rr);
+                            best = kk < best ? kk : best;
+                        }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) {
+                        const uint64_t other = __shfl_xor_sync(0xffffffffu, best, o);
+                        best = other < best ? other : best;
+                    }
+                    if (lane == 0) key = best;
+                }
+            }
+            if (key < thr) keys[atomicAdd(&scratch[36], 1)] = key;
+            __syncthreads();
+            const int cnt = scratch[36];
+            if (cnt > kExCap - kExThreads) {  // uniform
+                const uint64_t X = block_kth_smallest(keys, cnt, p.k, scratch);
+                // keep keys <= X (exactly k: keys are unique)
+                uint64_t mine[kExCap / kExThreads];
+                int nm = 0;
+                for (int i = tid; i < cnt; i += kExThreads) {
+                    const uint64_t kk = keys[i];
+                    if (kk <= X) mine[nm++] = kk;
+                }
+                __syncthreads();
+                if (tid == 0) scratch[36] = 0;
+                __syncthreads();
+                const int b = atomicAdd(&scratch[36], nm);
+                for (int i = 0; i < nm; ++i) keys[b + i] = mine[i];
+                __syncthreads();
+                thr = X + 1;  // strictly better than the current k-th, or it cannot enter the top-k
+            }
+        }
+        __syncthreads();
+        int cnt = scratch[36];
+        if (cnt > p.k) {
+            const uint64_t X = block_kth_smallest(keys, cnt, p.k, scratch);
+            uint64_t mine[kExCap / kExThreads];
+            int nm = 0;
+            for (int i = tid; i < cnt; i += kExThreads) {
+                const uint64_t kk = keys[i];
+                if (kk <= X) mine[nm++] = kk;
+            }
+            __syncthreads();
+            if (tid == 0) scratch[36] = 0;
+            __syncthreads();
+            const int b = atomicAdd(&scratch[36], nm);
+            for (int i = 0; i < nm; ++i) keys[b + i] = mine[i];
+            __syncthreads();
+            cnt = scratch[36];
+        }
+        for (int i = cnt + tid; i < ksort; i += kExThreads) keys[i] = ~0ull;
+        __syncthreads();
+        block_bitonic_sort(keys, ksort);
+        for (int i = tid; i < p.k; i += kExThreads) {
+            const uint64_t kk = keys[i];
+            const bool ok = i < cnt;
+            const uint32_t row = (uint32_t)kk;
+            p.out_d2[q * p.k + i] = ok ? ordered_to_f32((uint32_t)(kk >> 32)) : INFINITY;
+            p.out_idx[q * p.k + i] = ok ? (int64_t)row : -1;
+            if (SEGMAX && p.out_seg) p.out_seg[q * p.k + i] = ok ? (int64_t)p.seg_of_row[row] : -1;
+        }
+    }
+}
+
+template <typename T, bool SEGMAX>
+static int launch_ex(const FallbackParams &p, int grid, cudaStream_t st) {
+    const size_t smem = (size_t)kExCap * 8 + (size_t)p.d * 4 + 40 * 4 + kMaxIgnore * 4 + 16;
+    auto kern = exact_topk_kernel<T, SEGMAX>;
+    VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<grid, kExThreads, smem, st>>>(p);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+int launch_exact_topk(const FallbackParams &p, int grid, cudaStream_t st) {
+    if (p.nq == 0) return VQ_OK;
+    VQ_CHECK(p.k >= 1 && 2 * p.k <= kExCap - kExThreads, VQ_ERR_CAPACITY, "exact_topk: k=%d too large", p.k);
+    const bool seg = p.seg_start != nullptr;
+    if (p.dtype == VQ_F32) return seg ? launch_ex<float, true>(p, grid, st) : launch_ex<float, false>(p, grid, st);
+    return seg ? launch_ex<__nv_bfloat16, true>(p, grid, st) : launch_ex<__nv_bfloat16, false>(p, grid, st);
+}
+
+}  // namespace vq

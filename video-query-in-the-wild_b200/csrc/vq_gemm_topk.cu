@@ -1,0 +1,412 @@
+// vq_gemm_topk.cu -- kernels (1)+(2): query x gallery similarity GEMM on tcgen05/TMEM tiles fed
+// by TMA, with a fused epilogue that turns each accumulator tile into coarse scores
+// (c = scale_j * <q,g_j> + bias_j; l2sq: 2<q,g> - |g|^2) and streams them into a per-query
+// candidate list (threshold filter + warp-cooperative select), optionally max-pooling over the
+// moments of one untrimmed video first.  The Q x N score matrix never exists in HBM.
+//
+// Replaces the arithmetic of faiss.IndexFlatL2.search (dataloader_baseline.py:1592-1597,
+// :935-940, :1268-1273) and the labelling "ignore" rule (:1548) for the candidates it emits.
+// The candidates are only a PRE-FILTER: vq_select.cu re-scores them with the canonical fp32
+// chain, proves the top-k complete against the discard threshold tau emitted here, and sends
+// unproven queries to the exact fallback.
+//
+// Structure (one CTA per SM, persistent over work units = (gallery chunk, 128-query block)):
+//   warp 0     TMA producer: A (queries) and B (gallery) k-blocks of 64 bf16 -> 128B-swizzled smem
+//   warp 1     MMA issuer: tcgen05.mma kind::f16, M=128 N=256 K=16, fp32 accumulators in TMEM
+//              (2 x 256 columns, double buffered against the epilogue)
+//   warps 2-5  epilogue: tcgen05.ld 32 lanes x 32 columns, one query row per thread
+#include "vq_common.cuh"
+#include "vq_kernels.h"
+
+namespace vq {
+
+static constexpr int BM = kTileM, BN = kTileN, BK = 64;
+static constexpr int kEpiThreads = 128;
+static constexpr int kThreads = 64 + kEpiThreads;
+static constexpr int A_BYTES = BM * BK * 2;  // 16 KB
+static constexpr int B_BYTES = BN * BK * 2;  // 32 KB
+
+template <int NPASS>
+struct SmemLayout {
+    static constexpr int NPLANE = NPASS == 1 ? 1 : 2;
+    static constexpr int STAGE_BYTES = NPLANE * (A_BYTES + B_BYTES);
+    static constexpr int STAGES = NPASS == 1 ? 4 : 2;
+    static constexpr int OFF_COLP = STAGES * STAGE_BYTES;          // float2[2][BN]
+    static constexpr int OFF_COLV = OFF_COLP + 2 * BN * 8;         // int[2][BN]
+    static constexpr int OFF_COLS = OFF_COLV + 2 * BN * 4;         // int[2][BN]
+    static constexpr int OFF_IGN = OFF_COLS + 2 * BN * 4;          // int[BM][kMaxIgnore]
+    static constexpr int OFF_BAR = OFF_IGN + BM * kMaxIgnore * 4;  // mbarriers
+    static constexpr int NBAR = 2 * STAGES + 4;
+    static constexpr int OFF_TMEM = OFF_BAR + NBAR * 8;
+    static constexpr int TOTAL = OFF_TMEM + 16 + 1024;  // + alignment slack
+};
+
+// Warp-cooperative compaction of one query row's candidate buffer to its k' best coarse keys.
+// Returns the new count; *tau_out = coarse score of the k'-th best (everything discarded is
+// <= tau).  Ties at the threshold are kept in buffer (= column) order, so the result is
+// deterministic.
+__device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, int lane,
+                                           float *tau_out) {
+    constexpr int E = kCandCap / 32;
+    uint64_t e[E];
+    __syncwarp();  // the lanes' appends to this row are visible to the whole warp
+#pragma unroll
+    for (int i = 0; i < E; ++i) {
+        int idx = i * 32 + lane;
+        e[i] = idx < cnt ? buf[idx] : 0ull;
+    }
+    __syncwarp();
+    // bisection on the ordered score word: T = k'-th largest
+    uint32_t T = 0;
+#pragma unroll 1
+    for (int bit = 31; bit >= 0; --bit) {
+        uint32_t cand = T | (1u << bit);
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < E; ++i) c += ((uint32_t)(e[i] >> 32) >= cand) ? 1 : 0;
+        c = __reduce_add_sync(0xffffffffu, c);
+        if (c >= kprime) T = cand;
+    }
+    int gt = 0;
+#pragma unroll
+    for (int i = 0; i < E; ++i) gt += ((uint32_t)(e[i] >> 32) > T) ? 1 : 0;
+    gt = __reduce_add_sync(0xffffffffu, gt);
+    const int quota_eq = kprime - gt;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    int pos = 0, eqseen = 0;
+#pragma unroll
+    for (int i = 0; i < E; ++i) {
+        uint32_t hi = (uint32_t)(e[i] >> 32);
+        bool valid = (i * 32 + lane) < cnt;
+        bool isgt = valid && hi > T;
+        bool iseq = valid && hi == T;
+        uint32_t eqm = __ballot_sync(0xffffffffu, iseq);
+        bool keep = isgt || (iseq && (eqseen + __popc(eqm & lt_mask)) < quota_eq);
+        uint32_t km = __ballot_sync(0xffffffffu, keep);
+        if (keep) buf[pos + __popc(km & lt_mask)] = e[i];
+        pos += __popc(km);
+        eqseen += __popc(eqm);
+    }
+    __syncwarp();
+    *tau_out = ordered_to_f32(T);
+    return pos;
+}
+
+template <int NPASS, bool SEGMAX>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_constant__ CUtensorMap tm_a_lo,
+                 const __grid_constant__ CUtensorMap tm_b_hi, const __grid_constant__ CUtensorMap tm_b_lo,
+                 const GemmTopkParams p) {
+    using L = SmemLayout<NPASS>;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    float2 *colp = (float2 *)(smem + L::OFF_COLP);
+    int *colv = (int *)(smem + L::OFF_COLV);
+    int *cols = (int *)(smem + L::OFF_COLS);
+    int *ign = (int *)(smem + L::OFF_IGN);
+    uint64_t *full_bar = (uint64_t *)(smem + L::OFF_BAR);
+    uint64_t *empty_bar = full_bar + L::STAGES;
+    uint64_t *tfull_bar = empty_bar + L::STAGES;
+    uint64_t *tempty_bar = tfull_bar + 2;
+    uint32_t *tmem_slot = (uint32_t *)(smem + L::OFF_TMEM);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int n_units = p.n_chunks * p.n_qblocks;
+    const int KB = p.kb_count;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_a_hi);
+        tma_prefetch_desc(&tm_b_hi);
+        if (NPASS > 1) {
+            tma_prefetch_desc(&tm_a_lo);
+            tma_prefetch_desc(&tm_b_lo);
+        }
+        for (int s = 0; s < L::STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tfull_bar[s], 1);
+            mbar_init(&tempty_bar[s], kEpiThreads);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================ TMA producer =================================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+                const int chunk = u / p.n_qblocks, qb = u % p.n_qblocks;
+                const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+                const int ntiles = (int)((ce - cs + BN - 1) / BN);
+                const int q0 = qb * BM;
+                for (int t = 0; t < ntiles; ++t) {
+                    const int row0 = (int)(cs + (int64_t)t * BN);
+                    for (int kb = 0; kb < KB; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1u);
+                        uint8_t *sa = smem + stage * L::STAGE_BYTES;
+                        mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
+                        tma_load_2d(&tm_a_hi, &full_bar[stage], sa, kb * BK, q0, kEvictLast);
+                        if (NPASS > 1) {
+                            tma_load_2d(&tm_a_lo, &full_bar[stage], sa + A_BYTES, kb * BK, q0, kEvictLast);
+                            tma_load_2d(&tm_b_hi, &full_bar[stage], sa + 2 * A_BYTES, kb * BK, row0, kEvictNormal);
+                            tma_load_2d(&tm_b_lo, &full_bar[stage], sa + 2 * A_BYTES + B_BYTES, kb * BK, row0, kEvictNormal);
+                        } else {
+                            tma_load_2d(&tm_b_hi, &full_bar[stage], sa + A_BYTES, kb * BK, row0, kEvictNormal);
+                        }
+                        if (++stage == L::STAGES) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ===================================
+        constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+        int stage = 0;
+        uint32_t phase = 0;
+        int as = 0;
+        uint32_t aphase = 0;
+        for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+            const int chunk = u / p.n_qblocks;
+            const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+            const int ntiles = (int)((ce - cs + BN - 1) / BN);
+            for (int t = 0; t < ntiles; ++t) {
+                mbar_wait(&tempty_bar[as], aphase ^ 1u);
+                tc_fence_after();
+                const uint32_t tacc = tmem_base + (uint32_t)(as * BN);
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    if (lane == 0) {
+                        const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
+                        if (NPASS == 1) {
+                            const uint64_t ad = umma_desc_sw128(sa), bd = umma_desc_sw128(sa + A_BYTES);
+#pragma unroll
+                            for (int k = 0; k < BK / 16; ++k)
+                                umma_bf16(tacc, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                        } else {
+                            const uint64_t ah = umma_desc_sw128(sa), al = umma_desc_sw128(sa + A_BYTES);
+                            const uint64_t bh = umma_desc_sw128(sa + 2 * A_BYTES);
+                            const uint64_t bl = umma_desc_sw128(sa + 2 * A_BYTES + B_BYTES);
+#pragma unroll
+                            for (int k = 0; k < BK / 16; ++k) {
+                                umma_bf16(tacc, al + 2 * k, bh + 2 * k, idesc, (kb | k) != 0);
+                                umma_bf16(tacc, ah + 2 * k, bl + 2 * k, idesc, 1);
+                                umma_bf16(tacc, ah + 2 * k, bh + 2 * k, idesc, 1);
+                            }
+                        }
+                        umma_commit(&empty_bar[stage]);  // frees the smem stage when the MMAs retire
+                        if (kb == KB - 1) umma_commit(&tfull_bar[as]);
+                    }
+                    __syncwarp();
+                    if (++stage == L::STAGES) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+                if (++as == 2) {
+                    as = 0;
+                    aphase ^= 1u;
+                }
+            }
+        }
+    } else {
+        // ================================ epilogue =====================================
+        const int et = threadIdx.x - 64;         // 0..127
+        const int quarter = warp & 3;            // TMEM lane quarter this warp may read
+        const int row = quarter * 32 + lane;     // accumulator row == query row in the block
+        const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+        int as = 0;
+        uint32_t aphase = 0;
+        for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+            const int chunk = u / p.n_qblocks, qb = u % p.n_qblocks;
+            const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+            const int ntiles = (int)((ce - cs + BN - 1) / BN);
+            const int64_t q = (int64_t)qb * BM + row;
+            const bool qvalid = q < p.nq;
+            uint64_t *buf = p.cand + ((int64_t)u * BM + row) * kCandCap;
+            uint64_t *wbuf = p.cand + ((int64_t)u * BM + quarter * 32) * kCandCap;
+            float tau = qvalid ? -INFINITY : INFINITY;
+            int cnt = 0;
+            // group-max state (SEGMAX)
+            int cur_seg = -2;
+            float cur_max = -INFINITY;
+            uint32_t cur_arg = 0;
+            bool grp_masked = false;
+            if (p.n_ign > 0) {  // each thread only ever reads its own row's ignore list
+                for (int t = 0; t < p.n_ign; ++t)
+                    ign[row * kMaxIgnore + t] = qvalid ? p.q_ignore[q * p.n_ign + t] : -1;
+            }
+            // column parameters of tile 0 (2 columns per thread)
+            float2 np0, np1;
+            int nv0 = -1, nv1 = -1, ns0 = -1, ns1 = -1;
+            auto fetch_cols = [&](int t) {
+                int64_t j0 = cs + (int64_t)t * BN + et * 2;
+                np0 = make_float2(0.f, -INFINITY);
+                np1 = np0;
+                nv0 = nv1 = -1;
+                ns0 = ns1 = -1;
+                if (j0 < ce) {
+                    np0 = p.colparam[j0];
+                    if (p.col_video) nv0 = p.col_video[j0];
+                    if (SEGMAX) ns0 = p.col_seg[j0];
+                }
+                if (j0 + 1 < ce) {
+                    np1 = p.colparam[j0 + 1];
+                    if (p.col_video) nv1 = p.col_video[j0 + 1];
+                    if (SEGMAX) ns1 = p.col_seg[j0 + 1];
+                }
+            };
+            fetch_cols(0);
+            for (int t = 0; t < ntiles; ++t) {
+                // stage this tile's column parameters (buffer `as`), then prefetch the next tile's
+                colp[as * BN + et * 2] = np0;
+                colp[as * BN + et * 2 + 1] = np1;
+                colv[as * BN + et * 2] = nv0;
+                colv[as * BN + et * 2 + 1] = nv1;
+                if (SEGMAX) {
+                    cols[as * BN + et * 2] = ns0;
+                    cols[as * BN + et * 2 + 1] = ns1;
+                }
+                named_bar_sync(1, kEpiThreads);
+                if (t + 1 < ntiles) fetch_cols(t + 1);
+                // make room: a tile can add at most BN entries
+                if (__any_sync(0xffffffffu, cnt > kCandCap - BN)) {
+                    uint32_t need = __ballot_sync(0xffffffffu, cnt > kCandCap - BN);
+                    while (need) {
+                        int src = __ffs(need) - 1;
+                        need &= need - 1;
+                        int c_r = __shfl_sync(0xffffffffu, cnt, src);
+                        float t_r;
+                        int nc = compact_row(wbuf + (int64_t)src * kCandCap, c_r, p.kprime, lane, &t_r);
+                        if (lane == src) {
+                            cnt = nc;
+                            tau = fmaxf(tau, t_r);
+                        }
+                    }
+                }
+                mbar_wait(&tfull_bar[as], aphase);
+                tc_fence_after();
+                const uint32_t tacc = tmem_base + lane_addr + (uint32_t)(as * BN);
+                const uint32_t jbase = (uint32_t)(cs + (int64_t)t * BN);
+                const float2 *cp = colp + as * BN;
+                const int *cv = colv + as * BN;
+                const int *csg = cols + as * BN;
+#pragma unroll 1
+                for (int ch = 0; ch < BN / 32; ++ch) {
+                    uint32_t r[32];
+                    tmem_ld32(tacc + ch * 32, r);
+                    tmem_wait_ld();
+                    if (ch == BN / 32 - 1) {  // accumulator fully read: hand TMEM back to the MMA warp
+                        tc_fence_before();
+                        mbar_arrive(&tempty_bar[as]);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int col = ch * 32 + i;
+                        const float2 sp = cp[col];
+                        const float c = __fmaf_rn(__uint_as_float(r[i]), sp.x, sp.y);
+                        if (SEGMAX) {
+                            const int sg = csg[col];
+                            if (sg != cur_seg) {  // warp-uniform
+                                if (cur_max > tau && !grp_masked) {
+                                    buf[cnt] = make_key_desc(cur_max, cur_arg);
+                                    ++cnt;
+                                }
+                                cur_seg = sg;
+                                cur_max = -INFINITY;
+                                grp_masked = false;
+                                if (p.n_ign > 0) {
+                                    const int v = cv[col];
+                                    for (int z = 0; z < p.n_ign; ++z) grp_masked |= (v == ign[row * kMaxIgnore + z]);
+                                }
+                            }
+                            if (c > cur_max) {
+                                cur_max = c;
+                                cur_arg = jbase + col;
+                            }
+                        } else {
+                            if (c > tau) {
+                                bool masked = false;
+                                if (p.n_ign > 0) {
+                                    const int v = cv[col];
+                                    for (int z = 0; z < p.n_ign; ++z) masked |= (v == ign[row * kMaxIgnore + z]);
+                                }
+                                if (!masked) {
+                                    buf[cnt] = make_key_desc(c, jbase + col);
+                                    ++cnt;
+                                }
+                            }
+                        }
+                    }
+                }
+                if (++as == 2) {
+                    as = 0;
+                    aphase ^= 1u;
+                }
+            }
+            if (SEGMAX) {
+                if (cur_max > tau && !grp_masked) {
+                    buf[cnt] = make_key_desc(cur_max, cur_arg);
+                    ++cnt;
+                }
+            }
+            __syncwarp();
+            // final compaction of this unit to <= k' entries per row
+            {
+                uint32_t need = __ballot_sync(0xffffffffu, cnt > p.kprime);
+                while (need) {
+                    int src = __ffs(need) - 1;
+                    need &= need - 1;
+                    int c_r = __shfl_sync(0xffffffffu, cnt, src);
+                    float t_r;
+                    int nc = compact_row(wbuf + (int64_t)src * kCandCap, c_r, p.kprime, lane, &t_r);
+                    if (lane == src) {
+                        cnt = nc;
+                        tau = fmaxf(tau, t_r);
+                    }
+                }
+            }
+            p.cand_cnt[(int64_t)u * BM + row] = qvalid ? cnt : 0;
+            p.cand_tau[(int64_t)u * BM + row] = tau;
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+template <int NPASS, bool SEGMAX>
+static int launch_t(const CUtensorMap *maps, const GemmTopkParams &p, int grid, cudaStream_t st) {
+    using L = SmemLayout<NPASS>;
+    auto kern = gemm_topk_kernel<NPASS, SEGMAX>;
+    VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL));
+    kern<<<grid, kThreads, L::TOTAL, st>>>(maps[0], maps[1], maps[2], maps[3], p);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+int launch_gemm_topk(const CUtensorMap *maps, const GemmTopkParams &p, int npass, bool segmax, int grid,
+                     cudaStream_t st) {
+    if (npass == 1) return segmax ? launch_t<1, true>(maps, p, grid, st) : launch_t<1, false>(maps, p, grid, st);
+    return segmax ? launch_t<3, true>(maps, p, grid, st) : launch_t<3, false>(maps, p, grid, st);
+}
+
+}  // namespace vq

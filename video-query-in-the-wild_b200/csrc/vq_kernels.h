@@ -1,0 +1,121 @@
+// vq_kernels.h -- internal launch interfaces between the C-ABI layer (vq_api.cu) and the kernels.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace vq {
+
+static constexpr int kTileM = 128;      // queries per work unit (UMMA M)
+static constexpr int kTileN = 256;      // gallery rows per tile (UMMA N)
+static constexpr int kCandCap = 1024;   // candidate slots per (work unit, query)
+static constexpr int kMaxIgnore = 8;    // ignore-list length per query (the reference uses 5)
+static constexpr int kMaxKPrime = 512;  // largest pre-filter list (must be <= kCandCap - kTileN)
+
+struct GemmTopkParams {
+    int64_t nq, n;
+    int kb_count;              // padded dim / 64
+    int n_qblocks, n_chunks;
+    const int64_t *chunk_start;  // device [n_chunks+1], gallery row ranges of the chunks
+    const float2 *colparam;      // device [n]: (scale, bias) of the coarse score
+    const int32_t *col_video;    // device [n] or null
+    const int32_t *col_seg;      // device [n] or null (segment id per row, SEGMAX)
+    const int32_t *q_ignore;     // device [nq, n_ign] or null
+    int n_ign;
+    int kprime;
+    uint64_t *cand;   // [units][kTileM][kCandCap] keys (ordered coarse score << 32 | ~row)
+    int32_t *cand_cnt;  // [units][kTileM]
+    float *cand_tau;    // [units][kTileM] everything not listed has coarse score <= tau
+};
+
+int launch_gemm_topk(const CUtensorMap *maps4, const GemmTopkParams &p, int npass, bool segmax,
+                     int grid, cudaStream_t st);
+
+// ---- vq_prepare.cu ----
+// fp32 or bf16 rows [n,d] -> bf16 planes hi/lo [n,dp] (zero padded), colparam (2, -|x|^2),
+// norm2 [n]; max_norm2 (ordered-uint atomicMax target, may be null).
+int launch_prepare_rows(const void *x, int dtype, int64_t n, int d, int dp, __nv_bfloat16 *hi,
+                        __nv_bfloat16 *lo, float2 *colparam, float *norm2, uint32_t *max_norm2_bits,
+                        cudaStream_t st);
+int launch_pool_normalize(const float *x, int64_t B, int C, int T, float *out, cudaStream_t st);
+
+// ---- vq_exact.cu ----
+// canonical all-pairs d2 for queries [q_begin, q_begin+nq_tile) -> out[nq_tile, n]
+int launch_l2sq_all(const void *q, const void *g, int dtype, int64_t nq_tile, int64_t n, int d,
+                    float *out, cudaStream_t st);
+
+struct SelectParams {
+    int64_t nq, n;
+    int d;
+    int dtype;           // element type of q/g (VQ_F32 / VQ_BF16)
+    const void *q, *g;   // original rows (canonical re-scoring reads these)
+    int n_qblocks, n_chunks;
+    const uint64_t *cand;
+    const int32_t *cand_cnt;
+    const float *cand_tau;
+    int kprime, k;
+    float eps_rel, eps_abs;      // |coarse - (|q|^2 - d2)| <= eps_rel*|q|*gmax + eps_abs
+    const uint32_t *gmax_norm2_bits;
+    // segmax
+    const int32_t *seg_of_row;   // [n] or null
+    const int64_t *seg_start;    // [nseg+1] or null
+    // outputs
+    float *out_d2;     // [nq,k]
+    int64_t *out_idx;  // [nq,k] gallery row (segmax: arg-best row)
+    int64_t *out_seg;  // [nq,k] or null (segmax: video id)
+    int32_t *unproven;       // [nq] list of query ids that need the exact fallback
+    int32_t *unproven_count; // [1]
+};
+int launch_select(const SelectParams &p, cudaStream_t st);
+
+struct FallbackParams {
+    int64_t nq, n;
+    int d, dtype;
+    const void *q, *g;
+    const int32_t *col_video, *q_ignore;
+    int n_ign;
+    const int32_t *seg_of_row;
+    const int64_t *seg_start;
+    int64_t nseg;
+    int k;
+    float *out_d2;
+    int64_t *out_idx;
+    int64_t *out_seg;
+    const int32_t *unproven;        // null => all queries
+    const int32_t *unproven_count;  // null => nq
+};
+int launch_exact_topk(const FallbackParams &p, int grid, cudaStream_t st);
+
+// ---- vq_metrics.cu ----
+struct ApRowsParams {
+    int64_t nq_tile, n;
+    const float *d2;           // [nq_tile, n] canonical
+    const int32_t *g_label, *g_video;
+    const int32_t *q_label;    // [nq_tile]
+    const int32_t *q_ignore;   // [nq_tile, n_ign] or null
+    int n_ign;
+    double *ap;        // [nq_tile]
+    double *recall;    // [nq_tile,3]
+    int64_t *top_idx;  // [nq_tile,100] or null
+    int32_t *overflow; // [1] set when a query has more positives than kMaxPositives
+};
+static constexpr int kMaxPositives = 8192;
+// pcap2: power-of-two capacity of the per-query positive list (<= kMaxPositives)
+int launch_ap_rows(const ApRowsParams &p, int pcap2, cudaStream_t st);
+int launch_average_precision(const int32_t *y_true, const double *y_score, const int64_t *offsets,
+                             int64_t nlists, int64_t max_len, double *ap, int32_t *overflow,
+                             cudaStream_t st);
+int launch_nms1d(const double *dets, const int64_t *offsets, int64_t nseg, double thresh,
+                 uint8_t *keep, uint8_t *dead_scratch, cudaStream_t st);
+int launch_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k, float *od,
+                      int64_t *oi, cudaStream_t st);
+
+// ---- vq_triplet.cu ----
+int launch_pdist(const float *A, int64_t B, int d, float eps, float *dist, cudaStream_t st);
+int launch_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int64_t B, int d,
+                             float margin, float *loss, float *grad, int32_t *trip, float *scratch,
+                             cudaStream_t st);
+int launch_triplet_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T,
+                         float margin, float *loss, float *grad, float *scratch, cudaStream_t st);
+
+}  // namespace vq

@@ -1,0 +1,416 @@
+// vq_metrics.cu -- kernel (4): segmented AP / R@N reduction in rank-count form, plus temporal
+// NMS and the multi-GPU top-k merge.
+//
+// ap_rows   one block per query over its canonical d2 row: the reference's per-candidate
+//           labelling loop (dataloader_baseline.py:1537-1586: tp = label match :1553, ignore =
+//           shared video id :1548) becomes two integer compares per element; AP
+//           (evaluation_metric.add2dict :431-461 -> sklearn average_precision_score) and
+//           R@30/50/100 (:475-481) are computed WITHOUT sorting the row:
+//             rank(p) = #{survivors ahead of p};  for each tie group of positive scores
+//             AP += (tps/P - prev_recall) * (tps / #{survivors with d2 <= t})      (float64)
+//           with the last-ranked survivor forced positive (:434, AP only).
+// ap_lists  sklearn.metrics.average_precision_score on a batch of (y_true, y_score) lists.
+// nms1d     misc_utils/utils_models.py:nms_cpu, one warp per segment.
+// topk_merge  k-way merge of per-shard top-k lists.
+#include "vq_blocksel.cuh"
+#include "vq_kernels.h"
+
+namespace vq {
+
+static constexpr int kApThreads = 256;
+
+// exclusive prefix sum of a[0..n) in shared memory, in place; returns the total.  part: int[kApThreads+1]
+__device__ __forceinline__ int block_exclusive_scan(int *a, int n, int *part) {
+    const int tid = threadIdx.x;
+    const int per = (n + kApThreads - 1) / kApThreads;
+    const int b = tid * per, e = min(n, b + per);
+    int s = 0;
+    for (int i = b; i < e; ++i) s += a[i];
+    __syncthreads();
+    part[tid] = s;
+    __syncthreads();
+    if (tid == 0) {
+        int run = 0;
+        for (int i = 0; i < kApThreads; ++i) {
+            int v = part[i];
+            part[i] = run;
+            run += v;
+        }
+        part[kApThreads] = run;
+    }
+    __syncthreads();
+    int run = part[tid];
+    for (int i = b; i < e; ++i) {
+        int v = a[i];
+        a[i] = run;
+        run += v;
+    }
+    __syncthreads();
+    return part[kApThreads];
+}
+
+__device__ __forceinline__ bool is_ignored(int v, const int *ign, int n_ign) {
+    bool m = false;
+    for (int z = 0; z < n_ign; ++z) m |= (v == ign[z]);
+    return m;
+}
+
+// dynamic smem: u64 pos[pcap2] | int cntA[pcap2+1] | int cntE[pcap2] | int gstart[pcap2] | int part[257] | misc
+__global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams p, int pcap2) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint64_t *pos = (uint64_t *)sm;
+    int *cntA = (int *)(pos + pcap2);
+    int *cntE = cntA + pcap2 + 1;
+    int *gstart = cntE + pcap2;
+    int *part = gstart + pcap2;
+    int *misc = part + kApThreads + 1;  // [0]=npos [1]=nvalid, [8..16)=ignore list
+    unsigned long long *last_key = (unsigned long long *)(misc + 16);
+    double *res = (double *)(last_key + 1);  // [0]=ap
+    int *topn = (int *)(res + 1);            // [3] true positives within rank 30/50/100
+    const int tid = threadIdx.x;
+    const int64_t q = blockIdx.x;
+    const float *row = p.d2 + q * p.n;
+    const int ql = p.q_label[q];
+
+    if (tid < kMaxIgnore) misc[8 + tid] = (p.q_ignore && tid < p.n_ign) ? p.q_ignore[q * p.n_ign + tid] : -1;
+    if (tid == 0) {
+        misc[0] = 0;
+        misc[1] = 0;
+        *last_key = 0ull;
+        topn[0] = topn[1] = topn[2] = 0;
+    }
+    for (int i = tid; i < pcap2; i += kApThreads) {
+        pos[i] = ~0ull;
+        cntA[i] = 0;
+        cntE[i] = 0;
+    }
+    if (tid == 0) cntA[pcap2] = 0;
+    __syncthreads();
+    const int *ign = misc + 8;
+    const int n_ign = p.q_ignore ? p.n_ign : 0;
+
+    // ---- pass 1: positives, survivor count, last-ranked survivor ----
+    int nvalid_t = 0;
+    unsigned long long lk = 0ull;
+    for (int64_t j = tid; j < p.n; j += kApThreads) {
+        if (n_ign && is_ignored(p.g_video[j], ign, n_ign)) continue;
+        ++nvalid_t;
+        const unsigned long long key = make_key_asc(row[j], (uint32_t)j);
+        lk = key > lk ? key : lk;
+        if (p.g_label[j] == ql) {
+            const int slot = atomicAdd(&misc[0], 1);
+            if (slot < pcap2) pos[slot] = key;
+        }
+    }
+    atomicAdd(&misc[1], nvalid_t);
+    atomicMax(last_key, lk);
+    __syncthreads();
+    const int ntrue = misc[0];
+    const int nvalid = misc[1];
+    if (ntrue + 1 > pcap2) {  // uniform
+        if (tid == 0) {
+            atomicExch(p.overflow, 1);
+            p.ap[q] = 0.0;
+            p.recall[q * 3] = p.recall[q * 3 + 1] = p.recall[q * 3 + 2] = 0.0;
+        }
+        return;
+    }
+    if (nvalid == 0) {  // the reference would raise on y_true[-1] of an empty list
+        if (tid == 0) {
+            p.ap[q] = 0.0;
+            p.recall[q * 3] = p.recall[q * 3 + 1] = p.recall[q * 3 + 2] = 0.0;
+        }
+        return;
+    }
+    // forced positive: the last survivor in ranked order (dataloader_baseline.py:434), AP only
+    const uint64_t lastk = *last_key;
+    const bool last_is_true = p.g_label[(uint32_t)lastk] == ql;
+    int npos = ntrue;
+    if (!last_is_true) {
+        if (tid == 0) pos[ntrue] = lastk;
+        npos = ntrue + 1;
+    }
+    __syncthreads();
+    const int n2 = next_pow2(npos);
+    block_bitonic_sort(pos, n2);  // ascending (d2, row): best first
+
+    // ---- pass 2: bucket every survivor against the sorted positive d2 values ----
+    for (int64_t j = tid; j < p.n; j += kApThreads) {
+        if (n_ign && is_ignored(p.g_video[j], ign, n_ign)) continue;
+        const uint32_t s = f32_to_ordered(row[j]);
+        int lo = 0, hi = npos;  // lower bound: first i with pos_d2[i] >= s
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if ((uint32_t)(pos[mid] >> 32) < s) lo = mid + 1; else hi = mid;
+        }
+        atomicAdd(&cntA[lo], 1);
+        if (lo < npos && (uint32_t)(pos[lo] >> 32) == s) atomicAdd(&cntE[lo], 1);
+    }
+    __syncthreads();
+    block_exclusive_scan(cntA, npos + 1, part);  // cntA[i] = #{survivors with lower bound < i}
+    // inclusive count LE(g) = cntA[g+1] = #{survivors with d2 <= pos_d2[g]} for a group start g
+
+    // ---- AP: sequential over tie groups (float64, sklearn's order of operations) ----
+    if (tid == 0) {
+        const double P = (double)npos;
+        double ap = 0.0, tps = 0.0, prev = 0.0;
+        int i = 0;
+        while (i < npos) {
+            const int g = i;
+            const uint32_t t = (uint32_t)(pos[g] >> 32);
+            while (i < npos && (uint32_t)(pos[i] >> 32) == t) {
+                gstart[i] = g;
+                tps += 1.0;
+                ++i;
+            }
+            const double jcount = (double)cntA[g + 1];
+            const double recall = tps / P;
+            const double precision = tps / jcount;
+            ap += (recall - prev) * precision;
+            prev = recall;
+        }
+        res[0] = ap;
+    }
+    __syncthreads();
+
+    // ---- R@N: exact rank of every TRUE positive under the (d2, row) order ----
+    for (int i = tid; i < npos; i += kApThreads) {
+        const uint64_t key = pos[i];
+        if (!last_is_true && key == lastk) continue;  // the forced one is not a true positive
+        const int g = gstart[i];
+        const int lt = cntA[g + 1] - cntE[g];  // survivors strictly ahead by d2
+        int rank;
+        if (cntE[g] == 1) {
+            rank = lt + 1;
+        } else {  // exact ties: count survivors with equal d2 and row <= mine (rare)
+            const uint32_t s = (uint32_t)(key >> 32), myrow = (uint32_t)key;
+            int c = 0;
+            for (int64_t j = 0; j <= myrow; ++j) {
+                if (f32_to_ordered(row[j]) != s) continue;
+                if (n_ign && is_ignored(p.g_video[j], ign, n_ign)) continue;
+                ++c;
+            }
+            rank = lt + c;
+        }
+        if (rank <= 30) atomicAdd(&topn[0], 1);
+        if (rank <= 50) atomicAdd(&topn[1], 1);
+        if (rank <= 100) atomicAdd(&topn[2], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        p.ap[q] = res[0];
+        const double npos_true = (double)ntrue + 1e-10;  // :476
+        for (int r = 0; r < 3; ++r) p.recall[q * 3 + r] = (double)topn[r] * 1.0 / npos_true;
+    }
+}
+
+static size_t ap_rows_smem(int pcap2) {
+    return (size_t)pcap2 * 8 + (size_t)(pcap2 + 1) * 4 + (size_t)pcap2 * 4 * 2 + (kApThreads + 1) * 4 + 16 * 4 + 8 +
+           8 + 16 + 64;
+}
+
+int launch_ap_rows(const ApRowsParams &p, int pcap2, cudaStream_t st) {
+    if (p.nq_tile == 0) return VQ_OK;
+    const size_t smem = ap_rows_smem(pcap2);
+    VQ_CUDA(cudaFuncSetAttribute(ap_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ap_rows_kernel<<<(unsigned)p.nq_tile, kApThreads, smem, st>>>(p, pcap2);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// sklearn average_precision_score on a batch of lists (any order in, ties grouped).
+// One block per list; positives' scores sorted in shared memory, every element bucketed.
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t f64_to_ordered_desc(double s) {
+    // larger score -> SMALLER key (so ascending key order = descending score)
+    uint64_t u = (uint64_t)__double_as_longlong(s);
+    u = (u & 0x8000000000000000ull) ? ~u : (u | 0x8000000000000000ull);  // ascending in s
+    return ~u;
+}
+
+__global__ void __launch_bounds__(kApThreads) ap_lists_kernel(const int32_t *__restrict__ y_true,
+                                                             const double *__restrict__ y_score,
+                                                             const int64_t *__restrict__ offsets, double *ap,
+                                                             int pcap2, int32_t *overflow) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint64_t *pos = (uint64_t *)sm;
+    int *cntA = (int *)(pos + pcap2);
+    int *part = cntA + pcap2 + 1;
+    int *misc = part + kApThreads + 1;
+    const int tid = threadIdx.x;
+    const int64_t b = offsets[blockIdx.x], e = offsets[blockIdx.x + 1];
+    if (tid == 0) misc[0] = 0;
+    for (int i = tid; i < pcap2; i += kApThreads) {
+        pos[i] = ~0ull;
+        cntA[i] = 0;
+    }
+    if (tid == 0) cntA[pcap2] = 0;
+    __syncthreads();
+    for (int64_t j = b + tid; j < e; j += kApThreads)
+        if (y_true[j] != 0) {
+            const int slot = atomicAdd(&misc[0], 1);
+            if (slot < pcap2) pos[slot] = f64_to_ordered_desc(y_score[j]);
+        }
+    __syncthreads();
+    const int npos = misc[0];
+    if (npos > pcap2) {
+        if (tid == 0) {
+            atomicExch(overflow, 1);
+            ap[blockIdx.x] = 0.0;
+        }
+        return;
+    }
+    if (npos == 0) {
+        if (tid == 0) ap[blockIdx.x] = 0.0;
+        return;
+    }
+    block_bitonic_sort(pos, next_pow2(npos));
+    for (int64_t j = b + tid; j < e; j += kApThreads) {
+        const uint64_t s = f64_to_ordered_desc(y_score[j]);
+        int lo = 0, hi = npos;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (pos[mid] < s) lo = mid + 1; else hi = mid;
+        }
+        atomicAdd(&cntA[lo], 1);
+    }
+    __syncthreads();
+    block_exclusive_scan(cntA, npos + 1, part);
+    if (tid == 0) {
+        const double P = (double)npos;
+        double a = 0.0, tps = 0.0, prev = 0.0;
+        int i = 0;
+        while (i < npos) {
+            const int g = i;
+            while (i < npos && pos[i] == pos[g]) {
+                tps += 1.0;
+                ++i;
+            }
+            const double recall = tps / P, precision = tps / (double)cntA[g + 1];
+            a += (recall - prev) * precision;
+            prev = recall;
+        }
+        ap[blockIdx.x] = a;
+    }
+}
+
+int launch_average_precision(const int32_t *y_true, const double *y_score, const int64_t *offsets,
+                             int64_t nlists, int64_t max_len, double *ap, int32_t *overflow, cudaStream_t st) {
+    (void)max_len;
+    if (nlists == 0) return VQ_OK;
+    const int pcap2 = kMaxPositives;
+    const size_t smem = (size_t)pcap2 * 8 + (size_t)(pcap2 + 1) * 4 + (kApThreads + 1) * 4 + 64;
+    VQ_CUDA(cudaFuncSetAttribute(ap_lists_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ap_lists_kernel<<<(unsigned)nlists, kApThreads, smem, st>>>(y_true, y_score, offsets, ap, pcap2, overflow);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// nms_cpu, one warp per segment.  The warp walks the segment in (score desc, row asc) order;
+// lanes test the remaining candidates against each newly kept one.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) nms1d_kernel(const double *__restrict__ dets,
+                                                    const int64_t *__restrict__ offsets, int64_t nseg,
+                                                    double thresh, uint8_t *__restrict__ keep,
+                                                    uint8_t *__restrict__ dead) {
+    const int lane = threadIdx.x & 31;
+    const int64_t seg = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (seg >= nseg) return;
+    const int64_t b = offsets[seg], e = offsets[seg + 1];
+    const int64_t n = e - b;
+    for (int64_t i = lane; i < n; i += 32) {
+        keep[b + i] = 0;
+        dead[b + i] = 0;
+    }
+    __syncwarp();
+    // repeatedly pick the best not-yet-dead row: (score desc, row asc)
+    for (;;) {
+        double bs = -INFINITY;
+        int64_t bi = -1;
+        for (int64_t i = lane; i < n; i += 32) {
+            if (dead[b + i]) continue;
+            const double s = dets[(b + i) * 3 + 2];
+            if (bi < 0 || s > bs) {  // rows visited ascending per lane: first max wins
+                bs = s;
+                bi = i;
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            const double os = __shfl_xor_sync(0xffffffffu, bs, o);
+            const int64_t oi = __shfl_xor_sync(0xffffffffu, bi, o);
+            if (oi >= 0 && (bi < 0 || os > bs || (os == bs && oi < bi))) {
+                bs = os;
+                bi = oi;
+            }
+        }
+        if (bi < 0) break;
+        const double x1 = dets[(b + bi) * 3], x2 = dets[(b + bi) * 3 + 1], li = x2 - x1 + 1.0;
+        if (lane == 0) {
+            keep[b + bi] = 1;
+            dead[b + bi] = 1;
+        }
+        for (int64_t i = lane; i < n; i += 32) {
+            if (dead[b + i] || i == bi) continue;
+            const double y1 = dets[(b + i) * 3], y2 = dets[(b + i) * 3 + 1], lj = y2 - y1 + 1.0;
+            const double xx1 = fmax(x1, y1), xx2 = fmin(x2, y2);
+            const double inter = fmax(0.0, xx2 - xx1 + 1.0);
+            const double ovr = inter / (li + lj - inter);
+            if (!(ovr < thresh)) dead[b + i] = 1;
+        }
+        __syncwarp();
+    }
+}
+
+int launch_nms1d(const double *dets, const int64_t *offsets, int64_t nseg, double thresh, uint8_t *keep,
+                         uint8_t *dead, cudaStream_t st) {
+    if (nseg == 0) return VQ_OK;
+    nms1d_kernel<<<(unsigned)((nseg + 7) / 8), 256, 0, st>>>(dets, offsets, nseg, thresh, keep, dead);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+// ---------------------------------------------------------------------------------------
+// k-way merge of per-shard lists: one block per query, bitonic sort of G*k keys in smem.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) topk_merge_kernel(const float *__restrict__ d2, const int64_t *__restrict__ idx,
+                                                         int G, int64_t nq, int64_t k, float *__restrict__ od,
+                                                         int64_t *__restrict__ oi, int n2) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint64_t *keys = (uint64_t *)sm;
+    const int64_t q = blockIdx.x;
+    const int total = (int)(G * k);
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) {
+        uint64_t kk = ~0ull;
+        if (i < total) {
+            const int g = i / (int)k, j = i % (int)k;
+            const int64_t o = ((int64_t)g * nq + q) * k + j;
+            if (idx[o] >= 0) kk = make_key_asc(d2[o], (uint32_t)idx[o]);
+        }
+        keys[i] = kk;
+    }
+    __syncthreads();
+    block_bitonic_sort(keys, n2);
+    for (int i = threadIdx.x; i < k; i += blockDim.x) {
+        const uint64_t kk = keys[i];
+        const bool ok = kk != ~0ull;
+        od[q * k + i] = ok ? ordered_to_f32((uint32_t)(kk >> 32)) : INFINITY;
+        oi[q * k + i] = ok ? (int64_t)(uint32_t)kk : -1;
+    }
+}
+
+int launch_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k, float *od, int64_t *oi,
+                      cudaStream_t st) {
+    if (nq == 0) return VQ_OK;
+    const int n2 = next_pow2((int)(G * k));
+    const size_t smem = (size_t)n2 * 8;
+    VQ_CHECK(smem <= 200 * 1024, VQ_ERR_CAPACITY, "topk_merge: G*k=%lld too large", (long long)(G * k));
+    VQ_CUDA(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    topk_merge_kernel<<<(unsigned)nq, 128, smem, st>>>(d2, idx, G, nq, k, od, oi, n2);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+}  // namespace vq

@@ -1,0 +1,100 @@
+// vq_prepare.cu -- index-build side kernels (a1, a2).
+//   prepare_rows : embedding rows -> bf16 operand planes for the tensor-core pre-filter
+//                  (hi = bf16(x), lo = bf16(x - hi), zero padded to a multiple of 64 columns),
+//                  per-row |x|^2 and the coarse-score column parameters (2, -|x|^2).
+//                  Replaces the list->concat->index.add of dataloader_baseline.py:1502-1510.
+//   pool_normalize: F.normalize(p=2,dim=1) per time step (main.py:232) + temporal mean
+//                  (dataloader_baseline.py:1481), canonical arithmetic (see oracle).
+#include "vq_common.cuh"
+#include "vq_kernels.h"
+
+namespace vq {
+
+template <typename T>
+__device__ __forceinline__ float ldf(const T *p);
+template <>
+__device__ __forceinline__ float ldf<float>(const float *p) { return *p; }
+template <>
+__device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16 *p) { return __bfloat162float(*p); }
+
+// one warp per row; 8 rows per 256-thread block
+template <typename T>
+__global__ void __launch_bounds__(256) prepare_rows_kernel(const T *__restrict__ x, int64_t n, int d, int dp,
+                                                           __nv_bfloat16 *__restrict__ hi,
+                                                           __nv_bfloat16 *__restrict__ lo,
+                                                           float2 *__restrict__ colparam,
+                                                           float *__restrict__ norm2,
+                                                           uint32_t *max_bits) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= n) return;
+    const T *xr = x + row * d;
+    __nv_bfloat16 *hr = hi + row * dp;
+    __nv_bfloat16 *lr = lo ? lo + row * dp : nullptr;
+    float acc = 0.f;
+    for (int c = lane * 2; c < dp; c += 64) {
+        float v0 = c < d ? ldf(xr + c) : 0.f;
+        float v1 = c + 1 < d ? ldf(xr + c + 1) : 0.f;
+        __nv_bfloat16 h0 = __float2bfloat16_rn(v0), h1 = __float2bfloat16_rn(v1);
+        *reinterpret_cast<__nv_bfloat162 *>(hr + c) = __nv_bfloat162(h0, h1);
+        if (lr) {
+            __nv_bfloat16 l0 = __float2bfloat16_rn(v0 - __bfloat162float(h0));
+            __nv_bfloat16 l1 = __float2bfloat16_rn(v1 - __bfloat162float(h1));
+            *reinterpret_cast<__nv_bfloat162 *>(lr + c) = __nv_bfloat162(l0, l1);
+        }
+        acc = fmaf(v0, v0, acc);
+        acc = fmaf(v1, v1, acc);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+        if (norm2) norm2[row] = acc;
+        if (colparam) colparam[row] = make_float2(2.0f, -acc);
+        if (max_bits) atomicMax(max_bits, __float_as_uint(acc));  // acc >= 0: bit order == value order
+    }
+}
+
+int launch_prepare_rows(const void *x, int dtype, int64_t n, int d, int dp, __nv_bfloat16 *hi,
+                        __nv_bfloat16 *lo, float2 *colparam, float *norm2, uint32_t *max_bits,
+                        cudaStream_t st) {
+    if (n == 0) return VQ_OK;
+    unsigned grid = (unsigned)((n + 7) / 8);
+    if (dtype == VQ_F32)
+        prepare_rows_kernel<float><<<grid, 256, 0, st>>>((const float *)x, n, d, dp, hi, lo, colparam, norm2, max_bits);
+    else
+        prepare_rows_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)x, n, d, dp, hi, lo,
+                                                                  colparam, norm2, max_bits);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+// block per batch item; x[b] is [C][T] with T contiguous
+__global__ void __launch_bounds__(256) pool_normalize_kernel(const float *__restrict__ x, int C, int T,
+                                                             float *__restrict__ out) {
+    extern __shared__ float nr[];  // [T]
+    const float *xb = x + (int64_t)blockIdx.x * C * T;
+    for (int t = threadIdx.x; t < T; t += blockDim.x) {
+        float acc = 0.f;
+        for (int c = 0; c < C; ++c) {
+            float v = xb[(int64_t)c * T + t];
+            acc = __fmaf_rn(v, v, acc);
+        }
+        float nrm = __fsqrt_rn(acc);
+        nr[t] = nrm > 1e-12f ? nrm : 1e-12f;
+    }
+    __syncthreads();
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+        float acc = 0.f;
+        for (int t = 0; t < T; ++t) acc = __fadd_rn(acc, __fdiv_rn(xb[(int64_t)c * T + t], nr[t]));
+        out[(int64_t)blockIdx.x * C + c] = __fdiv_rn(acc, (float)T);
+    }
+}
+
+int launch_pool_normalize(const float *x, int64_t B, int C, int T, float *out, cudaStream_t st) {
+    if (B == 0) return VQ_OK;
+    pool_normalize_kernel<<<(unsigned)B, 256, T * sizeof(float), st>>>(x, C, T, out);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+}  // namespace vq

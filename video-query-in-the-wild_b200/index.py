@@ -1,0 +1,102 @@
+"""`faiss.IndexFlatL2`-compatible index over the sm_100a kernels.
+
+Reference call sites replaced: dataloader_baseline.py:1502 (ctor), :1507 (add), :1508 (ntotal),
+:1592-1595 (search); same for the clip (:872-881, :935-938) and moment (:1196-1204, :1268-1271)
+evaluators.  Inject with ``sys.modules["faiss"] = vqwild_b200.faiss_module()``.
+"""
+import ctypes as C
+import types
+
+import numpy as np
+
+from . import _lib as L
+
+
+class IndexFlatL2:
+    """Squared-L2 brute-force index.  ``search`` returns (D ascending float32[nq,k], I int64[nq,k]),
+    D holding the canonical fp32 squared distances, ties broken by lowest gallery index."""
+
+    def __init__(self, d):
+        self.d = int(d)
+        self._h = C.c_void_p()
+        L.check(L.lib().vq_index_create(C.c_int(self.d), C.byref(self._h)))
+        self._keep = []
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h and L._lib is not None:
+            L._lib.vq_index_destroy(h)
+
+    # ---- faiss surface ----
+    @property
+    def ntotal(self):
+        return int(L.lib().vq_index_ntotal(self._h))
+
+    def add(self, xb):
+        xb, dt = L.emb_dtype(xb)
+        if xb.ndim != 2 or xb.shape[1] != self.d:
+            raise ValueError("add: expected [n, %d], got %s" % (self.d, tuple(xb.shape)))
+        L.check(L.lib().vq_index_add(self._h, L.ptr(xb), C.c_int64(xb.shape[0]), C.c_int(dt), L.stream_of(xb)))
+
+    def search(self, xq, k, ignore_video=None):
+        xq, dt = L.emb_dtype(xq)
+        if xq.ndim != 2 or xq.shape[1] != self.d:
+            raise ValueError("search: expected [nq, %d], got %s" % (self.d, tuple(xq.shape)))
+        nq, k = xq.shape[0], int(k)
+        ign = L.as_i32(ignore_video)
+        n_ign = 0 if ign is None else int(ign.shape[1])
+        D = L.empty_like_kind(xq, (nq, k), np.float32)
+        I = L.empty_like_kind(xq, (nq, k), np.int64)
+        L.check(L.lib().vq_index_search(self._h, L.ptr(xq), C.c_int64(nq), C.c_int(dt), C.c_int64(k), L.ptr(ign),
+                                        C.c_int(n_ign), L.ptr(D), L.ptr(I), L.stream_of(xq)))
+        return D, I
+
+    # ---- extensions used by the evaluators ----
+    def set_precision(self, prec):
+        L.check(L.lib().vq_index_set_precision(self._h, C.c_int(int(prec))))
+
+    def set_meta(self, label, video=None):
+        label, video = L.as_i32(label), L.as_i32(video)
+        L.check(L.lib().vq_index_set_meta(self._h, L.ptr(label), L.ptr(video), L.stream_of(label)))
+
+    def set_segments(self, seg_start):
+        ss = np.ascontiguousarray(seg_start, dtype=np.int64)
+        L.check(L.lib().vq_index_set_segments(self._h, L.ptr(ss), C.c_int64(ss.shape[0] - 1), C.c_void_p(0)))
+
+    def search_segmax(self, xq, k):
+        """Per (query, video) best moment and the top-k videos: (video, row, D) each [nq,k]."""
+        xq, dt = L.emb_dtype(xq)
+        nq, k = xq.shape[0], int(k)
+        V = L.empty_like_kind(xq, (nq, k), np.int64)
+        R = L.empty_like_kind(xq, (nq, k), np.int64)
+        D = L.empty_like_kind(xq, (nq, k), np.float32)
+        L.check(L.lib().vq_index_search_segmax(self._h, L.ptr(xq), C.c_int64(nq), C.c_int(dt), C.c_int64(k),
+                                               L.ptr(V), L.ptr(R), L.ptr(D), L.stream_of(xq)))
+        return V, R, D
+
+    def eval_trimmed(self, xq, q_label, ignore_video=None, want_top=False):
+        """ARV_Retrieval.ranking's per-query numbers (dataloader_baseline.py:1526-1610):
+        ap float64[nq], recall float64[nq,3] (R@30/50/100), top_idx int64[nq,100] or None."""
+        xq, dt = L.emb_dtype(xq)
+        nq = xq.shape[0]
+        ql, ign = L.as_i32(q_label), L.as_i32(ignore_video)
+        n_ign = 0 if ign is None else int(ign.shape[1])
+        ap = L.empty_like_kind(xq, (nq,), np.float64)
+        rec = L.empty_like_kind(xq, (nq, 3), np.float64)
+        top = L.empty_like_kind(xq, (nq, 100), np.int64) if want_top else None
+        L.check(L.lib().vq_index_eval_trimmed(self._h, L.ptr(xq), C.c_int64(nq), C.c_int(dt), L.ptr(ql), L.ptr(ign),
+                                              C.c_int(n_ign), L.ptr(ap), L.ptr(rec), L.ptr(top), L.stream_of(xq)))
+        return ap, rec, top
+
+    def last_stats(self):
+        out = (C.c_int64 * 6)()
+        L.check(L.lib().vq_index_last_stats(self._h, out))
+        keys = ("fallback_queries", "tc_tiles", "kprime", "work_units", "chunks", "launches")
+        return dict(zip(keys, [int(v) for v in out]))
+
+
+def faiss_module():
+    """A module object exposing ``IndexFlatL2`` for ``sys.modules["faiss"]`` injection."""
+    m = types.ModuleType("faiss")
+    m.IndexFlatL2 = IndexFlatL2
+    return m

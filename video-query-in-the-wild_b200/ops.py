@@ -1,0 +1,63 @@
+"""Stateless entry points: pre-match pooling (a1), canonical all-pairs scores, the multi-GPU
+top-k merge (8e) and the sharded search built on it."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib as L
+
+
+def pool_normalize(x):
+    """F.normalize(p=2, dim=1) per time step (main.py:232) + temporal mean
+    (dataloader_baseline.py:1481): [B,C,T] -> [B,C]."""
+    x, _ = L.emb_dtype(x)
+    B, Cc, T = x.shape
+    out = L.empty_like_kind(x, (B, Cc), np.float32)
+    L.check(L.lib().vq_pool_normalize(L.ptr(x), C.c_int64(B), C.c_int(Cc), C.c_int(T), L.ptr(out), L.stream_of(x)))
+    return out
+
+
+def l2sq(q, g):
+    q, _ = L.emb_dtype(q)
+    g, _ = L.emb_dtype(g)
+    out = L.empty_like_kind(q, (q.shape[0], g.shape[0]), np.float32)
+    L.check(L.lib().vq_l2sq(L.ptr(q), L.ptr(g), C.c_int64(q.shape[0]), C.c_int64(g.shape[0]), C.c_int(q.shape[1]),
+                            L.ptr(out), L.stream_of(q)))
+    return out
+
+
+def topk_merge(d2, idx):
+    """[G,nq,k] per-shard lists (global row ids, -1 = empty) -> [nq,k] by (d2 asc, idx asc)."""
+    G, nq, k = d2.shape
+    od = L.empty_like_kind(d2, (nq, k), np.float32)
+    oi = L.empty_like_kind(d2, (nq, k), np.int64)
+    L.check(L.lib().vq_topk_merge(L.ptr(d2), L.ptr(idx), C.c_int(G), C.c_int64(nq), C.c_int64(k), L.ptr(od),
+                                  L.ptr(oi), L.stream_of(d2)))
+    return od, oi
+
+
+def sharded_search(index, xq, k, row_offset, group=None):
+    """Row-sharded gallery: every rank searches its shard (`index` holds rows
+    [row_offset, row_offset + ntotal) of the global gallery), the per-rank top-k lists are
+    exchanged with ONE all-gather and merged on every rank.  xq: CUDA tensor (NCCL) or CPU
+    tensor / numpy (gloo tests call `merge_gathered` with an oracle-made local list)."""
+    import torch
+    import torch.distributed as dist
+    D, I = index.search(xq, k)
+    D = torch.as_tensor(D)
+    I = torch.as_tensor(I)
+    I = torch.where(I >= 0, I + int(row_offset), I)
+    return merge_gathered(D, I, group)
+
+
+def merge_gathered(D, I, group=None, merge=None):
+    """All-gather [nq,k] lists over the process group and merge them (merge defaults to the CUDA
+    kernel; tests on CPU pass the oracle's merge)."""
+    import torch
+    import torch.distributed as dist
+    ws = dist.get_world_size(group)
+    gD = torch.empty((ws,) + tuple(D.shape), dtype=D.dtype, device=D.device)
+    gI = torch.empty((ws,) + tuple(I.shape), dtype=I.dtype, device=I.device)
+    dist.all_gather_into_tensor(gD, D.contiguous(), group=group)
+    dist.all_gather_into_tensor(gI, I.contiguous(), group=group)
+    return (merge or topk_merge)(gD, gI)

@@ -1,0 +1,69 @@
+"""Thin caller mirroring the matching stage of the reference evaluators:
+``ARV_Retrieval.ranking`` (dataloader_baseline.py:1512-1611) over the two lists of dicts that are
+the hand-off from the feature stage (``query_list`` / ``gallery_list``, each item carrying
+``feat``, ``label``, ``video_id``, ``is_query``, ``retrieval_type``).  Everything between the
+lists and the result dict runs in the CUDA extension."""
+import numpy as np
+
+from .index import IndexFlatL2
+from .metrics import evaluation_metric, generate_multi_query
+
+
+def _ids(values, table=None):
+    table = {} if table is None else table
+    out = np.empty(len(values), np.int32)
+    for i, v in enumerate(values):
+        out[i] = table.setdefault(v, len(table))
+    return out, table
+
+
+class ARV_Retrieval:
+    def __init__(self, args, feat_extract_func=None, query_list=None, gallery_list=None):
+        self.args = args
+        self.feat_extract_func = feat_extract_func
+        self.eval_split = getattr(args, "eval_split", "testing")
+        self.feat_dim = getattr(args, "metric_feat_dim", None)
+        self.query_list = query_list
+        self.gallery_list = gallery_list
+        self.faiss_index = None
+
+    def build_index(self):
+        """dataloader_baseline.py:1502-1510: gallery features -> index (one H2D copy)."""
+        xb = np.ascontiguousarray(np.stack([g["feat"].reshape(-1) for g in self.gallery_list]), dtype=np.float32)
+        self.faiss_index = IndexFlatL2(xb.shape[1])
+        self.faiss_index.add(xb)
+        self.faiss_xb = xb
+        self._label_ids, self._label_table = _ids([g["label"] for g in self.gallery_list])
+        self._video_ids, self._video_table = _ids([g["video_id"] for g in self.gallery_list])
+        self.faiss_index.set_meta(self._label_ids, self._video_ids)
+
+    def ranking(self):
+        if self.faiss_index is None:
+            self.build_index()
+        self.original_query_list = self.query_list
+        self.query_list = generate_multi_query(self.query_list)                 # :1520
+        self.query_list = [q for q in self.query_list if q[0]["is_query"] == 1]  # :1521
+        self.class_map_evaluation = evaluation_metric(self.args, self.query_list)
+        nq, qn = len(self.query_list), int(self.args.query_num)
+        xq = np.empty((nq, self.faiss_xb.shape[1]), np.float32)
+        for i, queries in enumerate(self.query_list):                            # :1588-1591
+            acc = 0
+            for j in range(qn):
+                acc = acc + queries[j]["feat"]
+            xq[i] = acc / qn if qn > 1 else acc
+        # ids of labels / videos unseen in the gallery get fresh ids (match nothing)
+        q_label, _ = _ids([q[0]["label"] for q in self.query_list], dict(self._label_table))
+        ign = np.stack([_ids([x["video_id"] for x in q], dict(self._video_table))[0] for q in self.query_list])
+        ap, rec, top = self.faiss_index.eval_trimmed(xq, q_label, ign, want_top=True)
+        cls = [q[0]["label"] for q in self.query_list]
+        typ = [q[0]["retrieval_type"] for q in self.query_list]
+        self.class_map_evaluation.update_arrays(cls, typ, ap, rec)
+        names = {v: k for k, v in self._label_table.items()}
+        for i in range(nq):  # confusion-matrix side data (:437-442)
+            rows = [r for r in top[i].tolist() if r >= 0]
+            self.class_map_evaluation.cm_labels.extend(names[self._label_ids[r]] for r in rows)
+            self.class_map_evaluation.cm_gt_labels.extend([cls[i]] * len(rows))
+        return self.class_map_evaluation.get_result(self.original_query_list)
+
+    def evaluation(self):
+        return self.ranking()
