@@ -1,0 +1,439 @@
+#!/usr/bin/env python
+"""bench.py -- the hot path's headline measurement (BASELINE.json `metric`): query-gallery
+pairs/s on synthetic 512-d embeddings, one process per GPU.
+
+Workload (config.workload): BASELINE.json configs[3] "large-gallery scaling": 100 000 queries x
+10 000 000 clips x 512-d bf16, top-100, gallery row-sharded over the ranks (STRONG scaling: the
+10 M gallery is fixed, each of N ranks holds 10M/N rows), per-rank top-k merged after ONE NCCL
+all-gather.  It fits one B200 (20.5 GB of gallery planes), so it is also the N=1 workload.
+
+A step = one pass of the matching path over all queries: vq_index_search on the local shard
+(query operand preparation -> tcgen05 GEMM + streaming top-k -> canonical re-score / verify ->
+exact fallback for unproven queries) and, for N>1, all-gather + merge.  `value` is timed with the
+queries resident in HBM; `e2e` is the same step through the C-ABI with HOST (pinned) query and
+result buffers, copies inside the timed region.  The gallery is index state (the reference's
+`index.add(xb)`, dataloader_baseline.py:1507, runs once per evaluation); its one-off cost from
+host memory is reported separately as `index_add`.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    torchrun --nproc-per-node N bench.py --gpus N ...
+
+--impl reference: the reference's CPU path for the same metric.  The reference is pure Python
+(nothing compiles into oracle/_ref) and is absent on the GPU box, so this arm times the C port
+of its matching stage (oracle/vq_oracle.c: canonical squared-L2 + full sort per query, OpenMP
+over all host threads) on a bounded sample of the workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SEED = 0
+BLOCK_ROWS = 1 << 20  # synthetic data is generated in blocks seeded by (SEED, block id)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    # the named workload; overriding any of these makes config.workload say "custom"
+    ap.add_argument("--nq", type=int, default=100_000)
+    ap.add_argument("--n", type=int, default=10_000_000)
+    ap.add_argument("--d", type=int, default=512)
+    ap.add_argument("--k", type=int, default=100)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-aux", action="store_true", help="skip the cfg-1 mAP-eval and cfg-2 loss side measurements")
+    return ap.parse_args()
+
+
+def workload_name(a):
+    if (a.nq, a.n, a.d, a.k) == (100_000, 10_000_000, 512, 100):
+        return "configs[3] large-gallery scaling: 100k queries x 10M clips x 512-d bf16, top-100"
+    return "custom: %d queries x %d clips x %d-d bf16, top-%d" % (a.nq, a.n, a.d, a.k)
+
+
+# ---------------------------------------------------------------------------------------------
+# synthetic embeddings: x = normalize(randn) * u, u ~ U(0.6, 1): pooled features
+# have norm <= 1, not 1, so squared-L2 and cosine rankings differ.
+# ---------------------------------------------------------------------------------------------
+def gen_block(torch, kind, block, rows, d, device):
+    g = torch.Generator(device=device)
+    g.manual_seed(SEED * 1_000_003 + (0 if kind == "g" else 500_000) + block)
+    x = torch.randn(rows, d, generator=g, device=device, dtype=torch.float32)
+    x = x / x.norm(dim=1, keepdim=True)
+    u = torch.rand(rows, 1, generator=g, device=device, dtype=torch.float32) * 0.4 + 0.6
+    return (x * u).to(torch.bfloat16)
+
+
+def gen_rows(torch, kind, r0, r1, d, device):
+    """Rows [r0, r1) of the synthetic matrix `kind`; identical whatever the sharding."""
+    out = torch.empty((r1 - r0, d), dtype=torch.bfloat16, device=device)
+    b = r0 // BLOCK_ROWS
+    while b * BLOCK_ROWS < r1:
+        lo, hi = b * BLOCK_ROWS, (b + 1) * BLOCK_ROWS
+        blk = gen_block(torch, kind, b, BLOCK_ROWS, d, device)
+        s, e = max(lo, r0), min(hi, r1)
+        out[s - r0:e - r0] = blk[s - lo:e - lo]
+        del blk
+        b += 1
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks during the timed region (B200_PROFILING.md recipe)
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, dev_index):
+        self.rows, self.proc, self.th = [], None, None
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(dev_index), "--query-gpu=" + self.FIELDS,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._pump, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self, t0, t1):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, pw, reasons = [], None, [], set()
+        names = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+        for ts, line in self.rows:
+            if ts < t0 or ts > t1 + 0.1:
+                continue
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                smax = float(f[1])
+                pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v == "Active":
+                    reasons.add(nm)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": smax,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------
+# the CPU arm: C port of the reference's matching stage on a bounded sample
+# ---------------------------------------------------------------------------------------------
+def cpu_sample(a, steps, warmup):
+    """Returns (pairs/s, cores, sample description, ms/step)."""
+    import numpy as np
+    import torch
+    from oracle import oracle as orc
+    cores = orc.num_threads()
+    n_s = min(a.n, 1 << 18)
+    nq_s = min(a.nq, 4 * cores)
+    g = gen_block(torch, "g", 0, n_s, a.d, "cpu").float().numpy()
+    q = gen_block(torch, "q", 0, nq_s, a.d, "cpu").float().numpy()
+    times = []
+    for it in range(warmup + steps):
+        t0 = time.perf_counter()
+        D, I = orc.search(q, g, a.k)  # canonical d2 to every row + full sort, as faiss k=N (:1592-1597)
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    assert (np.diff(D, axis=1) >= 0).all()
+    dt = sum(times) / len(times)
+    sample = "%d queries x first %d gallery rows x %d-d (bf16 values widened to f32), full sort per query, %d steps" % (
+        nq_s, n_s, a.d, len(times))
+    return nq_s * n_s / dt, cores, sample, dt * 1e3
+
+
+def run_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    v, cores, sample, ms = cpu_sample(a, max(1, a.steps), max(0, min(a.warmup, 1)))
+    print(json.dumps({
+        "impl": "reference", "metric": "query-gallery pairs/sec (512-d)", "value": v, "unit": "pairs/s",
+        "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(a), "nq": a.nq, "n": a.n, "d": a.d, "k": a.k},
+        "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "reference is pure Python and absent on the GPU box; this is the OpenMP C port of its matching stage "
+                "(oracle/vq_oracle.c), a faster baseline than the reference's own per-query Python loop",
+    }))
+
+
+# ---------------------------------------------------------------------------------------------
+# side measurements on rank 0 at N=1 (the second half of BASELINE.json's metric, and configs[1])
+# ---------------------------------------------------------------------------------------------
+def aux_measurements(torch, vq):
+    import numpy as np
+    dev = "cuda"
+    out = {}
+    # configs[0]: trimmed retrieval eval, 4096 x 20480 x 512 f32, full-list AP + R@N
+    rng = np.random.default_rng(0)
+    n, nq, d = 20480, 4096, 512
+    label = rng.integers(0, 180, n).astype(np.int32)
+    centre = rng.standard_normal((180, d)).astype(np.float32)
+    g = rng.standard_normal((n, d)).astype(np.float32) + centre[label]
+    g /= np.linalg.norm(g, axis=1, keepdims=True)
+    g *= rng.uniform(0.6, 1.0, (n, 1)).astype(np.float32)
+    video = np.arange(n, dtype=np.int32)
+    qrow = rng.choice(n, nq, replace=False)
+    ign = video[qrow][:, None].astype(np.int32)
+    ix = vq.IndexFlatL2(d)
+    gd = torch.from_numpy(g).to(dev)
+    ix.add(gd)
+    ix.set_meta(torch.from_numpy(label).to(dev), torch.from_numpy(video).to(dev))
+    qd = gd[torch.from_numpy(qrow).to(dev)].contiguous()
+    ql = torch.from_numpy(label[qrow]).to(dev)
+    igd = torch.from_numpy(ign).to(dev)
+    ts = []
+    for it in range(4):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ap, rec, _ = ix.eval_trimmed(qd, ql, igd)
+        torch.cuda.synchronize()
+        ts.append(time.perf_counter() - t0)
+    out["map_eval_cfg0"] = {"workload": "configs[0]: 4096 queries x 20480 gallery x 512-d f32, full-list AP + R@30/50/100",
+                            "wall_ms": min(ts[1:]) * 1e3, "mAP": float(ap.double().mean().item()),
+                            "pairs_per_s": nq * n / min(ts[1:])}
+    del ix, gd
+    # configs[1]: batch-hard triplet fwd+bwd, B=256 D=512 (latency bound) and 4096 such groups (HBM bound)
+    from vqwild_b200.loss import TripletLoss
+    crit = TripletLoss(margin=1.0, sampling_method="batchhard")
+    for G in (1, 4096):
+        emb = torch.randn(G, 256, 512, device=dev)
+        emb = (emb / emb.norm(dim=2, keepdim=True)).requires_grad_(True)
+        lab = torch.arange(256, device=dev).div(4, rounding_mode="floor").to(torch.int32).repeat(G, 1)
+        x = emb if G > 1 else emb[0].detach().requires_grad_(True)
+        lb = lab if G > 1 else lab[0]
+        for _ in range(3):
+            crit(x, lb)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 20 if G == 1 else 5
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            crit(x, lb)   # forward computes loss AND the gradient (fused); backward only scales it
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        nbytes = G * (2 * 256 * 512 * 4 + 256 * 8 + 4)
+        out["triplet_cfg1_G%d" % G] = {"workload": "configs[1]: batch-hard triplet fwd+bwd, %d x (256 x 512-d f32)" % G,
+                                       "ms": ms, "algorithmic_bytes": nbytes, "GB_per_s": nbytes / ms / 1e6}
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+def run_b200(a):
+    import torch
+    import torch.distributed as dist
+    import vqwild_b200 as vq
+    from vqwild_b200 import ops
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device: the product has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+    G = world
+    if a.gpus != world and rank == 0:
+        print("note: --gpus %d but WORLD_SIZE=%d; using WORLD_SIZE" % (a.gpus, world), file=sys.stderr)
+
+    # ---- data: gallery shard [r0, r1), all queries ----
+    r0, r1 = rank * a.n // G, (rank + 1) * a.n // G
+    xq = gen_rows(torch, "q", 0, a.nq, a.d, dev)
+    shard = gen_rows(torch, "g", r0, r1, a.d, dev)
+    index = vq.IndexFlatL2(a.d)
+    # one-off: index.add from pinned HOST memory (the reference's :1507) -- reported, not part of a step
+    add_info = None
+    if G == 1 and shard.numel() * 2 <= 24 << 30:
+        host = torch.empty(shard.shape, dtype=torch.bfloat16, pin_memory=True)
+        host.copy_(shard)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        index.add(host)
+        torch.cuda.synchronize()
+        add_info = {"ms": (time.perf_counter() - t0) * 1e3, "h2d_bytes": shard.numel() * 2}
+        del host
+    else:
+        index.add(shard)
+    del shard
+    torch.cuda.synchronize()
+
+    k = a.k
+    D = torch.empty((a.nq, k), dtype=torch.float32, device=dev)
+    I = torch.empty((a.nq, k), dtype=torch.int64, device=dev)
+
+    def step_device():
+        index.search(xq, k, out=(D, I))
+        if G == 1:
+            return D, I
+        Ig = torch.where(I >= 0, I + r0, I)
+        return ops.merge_gathered(D, Ig)
+
+    xq_host = torch.empty(xq.shape, dtype=torch.bfloat16, pin_memory=True)
+    xq_host.copy_(xq)
+    Dh = torch.empty((a.nq, k), dtype=torch.float32, pin_memory=True)
+    Ih = torch.empty((a.nq, k), dtype=torch.int64, pin_memory=True)
+
+    def step_e2e():
+        if G == 1:
+            index.search(xq_host, k, out=(Dh, Ih))    # C-ABI stages H2D / D2H on the stream and synchronises
+            return Dh, Ih
+        xd = xq_host.to(dev, non_blocking=True)
+        index.search(xd, k, out=(D, I))
+        Ig = torch.where(I >= 0, I + r0, I)
+        Dm, Im = ops.merge_gathered(D, Ig)
+        Dh.copy_(Dm, non_blocking=True)
+        Ih.copy_(Im, non_blocking=True)
+        torch.cuda.synchronize()
+        return Dh, Ih
+
+    def barrier():
+        if G > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, collect=None):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        t0 = time.time()
+        e0.record()
+        for _ in range(steps):
+            fn()
+            if collect is not None:
+                collect()
+        e1.record()
+        barrier()
+        t1 = time.time()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if G > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), t0, t1
+
+    for _ in range(a.warmup):
+        step_device()
+    gemm_ms, phase_ms = [], []
+
+    def collect():
+        t = index.last_timing()
+        gemm_ms.append(t["gemm_topk_ms"])
+        phase_ms.append(t)
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    total_ms, t0, t1 = timed(step_device, a.steps, collect)
+    clocks = sampler.stop(t0, t1) if sampler else None
+    stats = index.last_stats()
+    out = step_device()
+    checksum = int((out[1].sum() % (1 << 61)).item())
+
+    for _ in range(max(1, min(a.warmup, 2))):
+        step_e2e()
+    e2e_ms, _, _ = timed(step_e2e, a.steps)
+
+    pairs = float(a.nq) * float(a.n)
+    ms_per_step = total_ms / a.steps
+    value = pairs / (ms_per_step * 1e-3)
+    e2e_value = pairs / (e2e_ms / a.steps * 1e-3)
+
+    # roofline of the dominant kernel (gemm_topk_kernel): algorithmic flops 2*Q*N_local*D per launch
+    peaks, which = None, "fallback"
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except (OSError, ValueError):
+        pass
+    g_ms = sum(gemm_ms) / len(gemm_ms)
+    flops = 2.0 * a.nq * (r1 - r0) * a.d
+    achieved = flops / (g_ms * 1e-3) / 1e12
+    if peaks and g_ms > 50.0:
+        peak, which = peaks["bf16_tflops_sustained"], "MEASURED_PEAKS.json bf16_tflops_sustained (kernel runs >50 ms per launch)"
+    elif peaks:
+        peak, which = peaks["bf16_tflops"], "MEASURED_PEAKS.json bf16_tflops (burst)"
+    else:
+        peak, which = 1590.0, "fallback 1.59 PFLOP/s (B200_PROFILING.md)"
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "gemm_topk_traffic.json")) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch")
+    except (OSError, ValueError):
+        pass
+
+    line = {
+        "metric": "query-gallery pairs/sec (512-d)", "value": value, "unit": "pairs/s", "n_gpus": G,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": workload_name(a), "nq": a.nq, "n": a.n, "d": a.d, "k": a.k,
+                   "parallelism": "gallery rows sharded %d-way, queries replicated, 1 all-gather of [Q,k] (d2,idx) + merge" % G
+                   if G > 1 else "single GPU",
+                   "l2_policy": "inputs larger than L2 (gallery shard %.1f GB per rank)" % ((r1 - r0) * a.d * 2 / 1e9),
+                   "tie_break": "d2 ascending, lowest gallery row first", "result": "canonical fp32 d2, verified top-k"},
+        "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": a.nq * a.d * 2,
+                "d2h_bytes_per_step": a.nq * k * 12, "ms_per_step": e2e_ms / a.steps},
+        "gpu_launches": (stats["launches"] + (1 if G > 1 else 0)) * a.steps,
+        "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+                     "traffic": traffic, "kernel": "gemm_topk_kernel<1,false>", "kernel_ms": g_ms,
+                     "algorithmic_flops_per_launch": flops, "peak_source": which},
+        "phases_ms": {kk: sum(p[kk] for p in phase_ms) / len(phase_ms) for kk in phase_ms[0]},
+        "search_stats": stats, "result_checksum": checksum, "clocks": clocks,
+    }
+    if add_info:
+        line["index_add"] = add_info
+
+    if rank == 0 and G == 1:
+        del index
+        torch.cuda.empty_cache()
+        if not a.no_aux:
+            try:
+                line["aux"] = aux_measurements(torch, vq)
+            except Exception as e:  # side numbers must not take the headline line down
+                line["aux"] = {"error": repr(e)}
+        if not a.no_cpu_baseline:
+            v, cores, sample, _ = cpu_sample(a, 1, 1)
+            line["cpu_baseline"] = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port", "sample": sample}
+    if G > 1:
+        dist.barrier()
+    if rank == 0:
+        print(json.dumps(line))
+    if G > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)

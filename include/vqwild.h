@@ -105,6 +105,10 @@ VQ_API int vq_index_search_segmax(vq_index *ix, const void *xq, int64_t nq, int 
  * fallback, [1] tensor-core tiles issued, [2] candidate slots per query, [3] work units,
  * [4] gallery chunks, [5] kernels launched by the call. */
 VQ_API int vq_index_last_stats(const vq_index *ix, int64_t *out6);
+/* Device time (ms, CUDA events on the caller's stream) of the phases of the last tensor-core
+ * search on this index: [0] query operand preparation, [1] the tcgen05 GEMM + streaming
+ * top-k kernel, [2] select/verify, [3] exact fallback.  Waits for that search to finish. */
+VQ_API int vq_index_last_timing(const vq_index *ix, float *out4);
 
 /* ------------------------------------------------------------------------------------
  * b2. Evaluation: ARV_Retrieval.ranking's per-query loop (dataloader_baseline.py:1526-1610)

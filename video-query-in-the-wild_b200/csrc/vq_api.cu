@@ -190,6 +190,8 @@ struct vq_index {
     int32_t *unproven_count = nullptr;
     int32_t *stat_pinned = nullptr;  // pinned host mirror of unproven_count
     int64_t stats[6] = {0, 0, 0, 0, 0, 0};
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // search phases (vq_index_last_timing)
+    bool ev_valid = false;
 };
 
 static size_t esize(int dtype) { return dtype == VQ_F32 ? 4 : 2; }
@@ -225,6 +227,7 @@ int vq_index_create(int d, vq_index **out) {
         delete ix;
         return VQ_ERR_NOMEM;
     }
+    for (int i = 0; i < 5; ++i) cudaEventCreate(&ix->ev[i]);
     cudaMemset(ix->gmax_bits, 0, 4);
     cudaMemset(ix->unproven_count, 0, 4);
     *ix->stat_pinned = 0;
@@ -241,6 +244,8 @@ int vq_index_destroy(vq_index *ix) {
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (ix->stat_pinned) cudaFreeHost(ix->stat_pinned);
+    for (int i = 0; i < 5; ++i)
+        if (ix->ev[i]) cudaEventDestroy(ix->ev[i]);
     delete ix;
     return VQ_OK;
 }
@@ -361,6 +366,14 @@ int vq_index_last_stats(const vq_index *ix, int64_t *out6) {
     VQ_CUDA(cudaMemcpy(&c, ix->unproven_count, 4, cudaMemcpyDeviceToHost));
     for (int i = 0; i < 6; ++i) out6[i] = ix->stats[i];
     out6[0] = c;
+    return VQ_OK;
+}
+
+int vq_index_last_timing(const vq_index *ix, float *out4) {
+    VQ_CHECK(ix && out4, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(ix->ev_valid, VQ_ERR_STATE, "no tensor-core search has run on this index");
+    VQ_CUDA(cudaEventSynchronize(ix->ev[4]));
+    for (int i = 0; i < 4; ++i) VQ_CUDA(cudaEventElapsedTime(&out4[i], ix->ev[i], ix->ev[i + 1]));
     return VQ_OK;
 }
 

@@ -98,6 +98,8 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     VQ_CHECK(k <= kprime, VQ_ERR_CAPACITY, "k=%d exceeds the streaming top-k limit %d", k, kMaxKPrime);
     // query operand planes
     Tmp qhi, qlo;
+    ix->ev_valid = false;
+    VQ_CUDA(cudaEventRecord(ix->ev[0], st));
     VQ_TRY(qhi.alloc((size_t)nq * ix->dp * 2, st));
     const bool split = prec == VQ_PREC_SPLIT3;
     if (split) VQ_TRY(qlo.alloc((size_t)nq * ix->dp * 2, st));
@@ -134,7 +136,9 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     gp.q_ignore = n_ign > 0 ? ign : nullptr; gp.n_ign = n_ign; gp.kprime = kprime;
     gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau;
     const int grid = (int)std::min<size_t>(units, (size_t)sm_count());
+    VQ_CUDA(cudaEventRecord(ix->ev[1], st));
     VQ_TRY(launch_gemm_topk(maps, gp, split ? 3 : 1, segmax, grid, st));
+    VQ_CUDA(cudaEventRecord(ix->ev[2], st));
     ++launches;
 
     SelectParams sp{};
@@ -148,6 +152,7 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     sp.out_d2 = D; sp.out_idx = I; sp.out_seg = seg_out;
     sp.unproven = ix->unproven; sp.unproven_count = ix->unproven_count;
     VQ_TRY(launch_select(sp, st));
+    VQ_CUDA(cudaEventRecord(ix->ev[3], st));
     ++launches;
 
     FallbackParams f{};
@@ -159,6 +164,8 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     f.k = k; f.out_d2 = D; f.out_idx = I; f.out_seg = seg_out;
     f.unproven = ix->unproven; f.unproven_count = ix->unproven_count;
     VQ_TRY(launch_exact_topk(f, (int)std::min<int64_t>(nq, 2 * sm_count()), st));
+    VQ_CUDA(cudaEventRecord(ix->ev[4], st));
+    ix->ev_valid = true;
     ++launches;
 
     int64_t tiles = 0;

@@ -38,15 +38,22 @@ class IndexFlatL2:
             raise ValueError("add: expected [n, %d], got %s" % (self.d, tuple(xb.shape)))
         L.check(L.lib().vq_index_add(self._h, L.ptr(xb), C.c_int64(xb.shape[0]), C.c_int(dt), L.stream_of(xb)))
 
-    def search(self, xq, k, ignore_video=None):
+    def search(self, xq, k, ignore_video=None, out=None):
+        """faiss surface; ``out=(D, I)`` (extension) writes into caller buffers -- host (pinned)
+        or device, float32[nq,k] / int64[nq,k] -- instead of allocating them."""
         xq, dt = L.emb_dtype(xq)
         if xq.ndim != 2 or xq.shape[1] != self.d:
             raise ValueError("search: expected [nq, %d], got %s" % (self.d, tuple(xq.shape)))
         nq, k = xq.shape[0], int(k)
         ign = L.as_i32(ignore_video)
         n_ign = 0 if ign is None else int(ign.shape[1])
-        D = L.empty_like_kind(xq, (nq, k), np.float32)
-        I = L.empty_like_kind(xq, (nq, k), np.int64)
+        if out is not None:
+            D, I = out
+            if tuple(D.shape) != (nq, k) or tuple(I.shape) != (nq, k):
+                raise ValueError("search: out buffers must be [%d, %d]" % (nq, k))
+        else:
+            D = L.empty_like_kind(xq, (nq, k), np.float32)
+            I = L.empty_like_kind(xq, (nq, k), np.int64)
         L.check(L.lib().vq_index_search(self._h, L.ptr(xq), C.c_int64(nq), C.c_int(dt), C.c_int64(k), L.ptr(ign),
                                         C.c_int(n_ign), L.ptr(D), L.ptr(I), L.stream_of(xq)))
         return D, I
@@ -93,6 +100,13 @@ class IndexFlatL2:
         L.check(L.lib().vq_index_last_stats(self._h, out))
         keys = ("fallback_queries", "tc_tiles", "kprime", "work_units", "chunks", "launches")
         return dict(zip(keys, [int(v) for v in out]))
+
+
+    def last_timing(self):
+        """Device ms of the last tensor-core search's phases (CUDA events on its stream)."""
+        out = (C.c_float * 4)()
+        L.check(L.lib().vq_index_last_timing(self._h, out))
+        return dict(zip(("prepare_ms", "gemm_topk_ms", "select_ms", "fallback_ms"), [float(v) for v in out]))
 
 
 def faiss_module():
