@@ -31,8 +31,8 @@ struct SmemLayout {
     static constexpr int NPLANE = NPASS == 1 ? 1 : 2;
     static constexpr int STAGE_BYTES = NPLANE * (A_BYTES + B_BYTES);
     static constexpr int STAGES = NPASS == 1 ? 4 : 2;
-    static constexpr int OFF_COLP = STAGES * STAGE_BYTES;          // float2[2][BN]
-    static constexpr int OFF_COLV = OFF_COLP + 2 * BN * 8;         // int[2][BN]
+    static constexpr int OFF_COLP = STAGES * STAGE_BYTES;          // float[2][BN] column bias (-|g|^2)
+    static constexpr int OFF_COLV = OFF_COLP + 2 * BN * 4;         // int[2][BN]
     static constexpr int OFF_COLS = OFF_COLV + 2 * BN * 4;         // int[2][BN]
     static constexpr int OFF_IGN = OFF_COLS + 2 * BN * 4;          // int[BM][kMaxIgnore]
     static constexpr int OFF_BAR = OFF_IGN + BM * kMaxIgnore * 4;  // mbarriers
@@ -41,51 +41,70 @@ struct SmemLayout {
     static constexpr int TOTAL = OFF_TMEM + 16 + 1024;  // + alignment slack
 };
 
-// Warp-cooperative compaction of one query row's candidate buffer to its k' best coarse keys.
-// Returns the new count; *tau_out = coarse score of the k'-th best (everything discarded is
-// <= tau).  Ties at the threshold are kept in buffer (= column) order, so the result is
-// deterministic.
-__device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, int lane,
+// Warp-cooperative compaction of one query row's candidate buffer.  Finds a threshold word T by
+// bisection on the ordered score bits such that kprime <= #{score >= T}; with keep_max > kprime
+// the bisection stops as soon as the count also fits keep_max (the intermediate compactions only
+// need SOME valid threshold; they run ~3x fewer steps), with keep_max == kprime it runs to the
+// exact k'-th largest and ties at T are kept in buffer (= column) order up to the quota, so the
+// result is deterministic.  Returns the new count; *tau_out = a score such that everything
+// discarded is <= tau.
+__device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, int keep_max, int lane,
                                            float *tau_out) {
     constexpr int E = kCandCap / 32;
-    uint64_t e[E];
+    uint32_t hi[E], lo[E];
     __syncwarp();  // the lanes' appends to this row are visible to the whole warp
 #pragma unroll
     for (int i = 0; i < E; ++i) {
         int idx = i * 32 + lane;
-        e[i] = idx < cnt ? buf[idx] : 0ull;
+        uint64_t e = idx < cnt ? buf[idx] : 0ull;
+        hi[i] = (uint32_t)(e >> 32);
+        lo[i] = (uint32_t)e;
     }
     __syncwarp();
-    // bisection on the ordered score word: T = k'-th largest
     uint32_t T = 0;
+    int cT = cnt;  // #{hi >= T}
 #pragma unroll 1
     for (int bit = 31; bit >= 0; --bit) {
-        uint32_t cand = T | (1u << bit);
+        const uint32_t cand = T | (1u << bit);
         int c = 0;
 #pragma unroll
-        for (int i = 0; i < E; ++i) c += ((uint32_t)(e[i] >> 32) >= cand) ? 1 : 0;
+        for (int i = 0; i < E; ++i) c += (hi[i] >= cand) ? 1 : 0;
         c = __reduce_add_sync(0xffffffffu, c);
-        if (c >= kprime) T = cand;
+        if (c >= kprime) {
+            T = cand;
+            cT = c;
+            if (c <= keep_max) break;
+        }
     }
-    int gt = 0;
-#pragma unroll
-    for (int i = 0; i < E; ++i) gt += ((uint32_t)(e[i] >> 32) > T) ? 1 : 0;
-    gt = __reduce_add_sync(0xffffffffu, gt);
-    const int quota_eq = kprime - gt;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    int pos = 0, eqseen = 0;
+    int pos = 0;
+    if (cT <= keep_max) {  // keep everything >= T
 #pragma unroll
-    for (int i = 0; i < E; ++i) {
-        uint32_t hi = (uint32_t)(e[i] >> 32);
-        bool valid = (i * 32 + lane) < cnt;
-        bool isgt = valid && hi > T;
-        bool iseq = valid && hi == T;
-        uint32_t eqm = __ballot_sync(0xffffffffu, iseq);
-        bool keep = isgt || (iseq && (eqseen + __popc(eqm & lt_mask)) < quota_eq);
-        uint32_t km = __ballot_sync(0xffffffffu, keep);
-        if (keep) buf[pos + __popc(km & lt_mask)] = e[i];
-        pos += __popc(km);
-        eqseen += __popc(eqm);
+        for (int i = 0; i < E; ++i) {
+            const bool keep = (i * 32 + lane) < cnt && hi[i] >= T;
+            const uint32_t km = __ballot_sync(0xffffffffu, keep);
+            if (keep) buf[pos + __popc(km & lt_mask)] = ((uint64_t)hi[i] << 32) | lo[i];
+            pos += __popc(km);
+        }
+    } else {  // exact: T is the k'-th largest; ties at T by buffer order up to the quota
+        int gt = 0;
+#pragma unroll
+        for (int i = 0; i < E; ++i) gt += (hi[i] > T) ? 1 : 0;
+        gt = __reduce_add_sync(0xffffffffu, gt);
+        const int quota_eq = kprime - gt;
+        int eqseen = 0;
+#pragma unroll
+        for (int i = 0; i < E; ++i) {
+            const bool valid = (i * 32 + lane) < cnt;
+            const bool isgt = valid && hi[i] > T;
+            const bool iseq = valid && hi[i] == T;
+            const uint32_t eqm = __ballot_sync(0xffffffffu, iseq);
+            const bool keep = isgt || (iseq && (eqseen + __popc(eqm & lt_mask)) < quota_eq);
+            const uint32_t km = __ballot_sync(0xffffffffu, keep);
+            if (keep) buf[pos + __popc(km & lt_mask)] = ((uint64_t)hi[i] << 32) | lo[i];
+            pos += __popc(km);
+            eqseen += __popc(eqm);
+        }
     }
     __syncwarp();
     *tau_out = ordered_to_f32(T);
@@ -99,8 +118,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                  const GemmTopkParams p) {
     using L = SmemLayout<NPASS>;
     extern __shared__ uint8_t smem_raw[];
-    uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    float2 *colp = (float2 *)(smem + L::OFF_COLP);
+    // 1024-byte alignment (SWIZZLE_128B) by offset arithmetic: keeps the pointer in the shared window (LDS/STS)
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float *colb = (float *)(smem + L::OFF_COLP);
     int *colv = (int *)(smem + L::OFF_COLV);
     int *cols = (int *)(smem + L::OFF_COLS);
     int *ign = (int *)(smem + L::OFF_IGN);
@@ -250,59 +270,69 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                 for (int t = 0; t < p.n_ign; ++t)
                     ign[row * kMaxIgnore + t] = qvalid ? p.q_ignore[q * p.n_ign + t] : -1;
             }
-            // column parameters of tile 0 (2 columns per thread)
-            float2 np0, np1;
+            // column parameters of tile 0 (2 columns per thread); the coarse score is
+            // c = 2 <q,g> - |g|^2 (colparam = (2, -|g|^2), vq_prepare.cu), only the bias is staged
+            float nb0, nb1;
             int nv0 = -1, nv1 = -1, ns0 = -1, ns1 = -1;
             auto fetch_cols = [&](int t) {
                 int64_t j0 = cs + (int64_t)t * BN + et * 2;
-                np0 = make_float2(0.f, -INFINITY);
-                np1 = np0;
+                nb0 = nb1 = -INFINITY;
                 nv0 = nv1 = -1;
                 ns0 = ns1 = -1;
                 if (j0 < ce) {
-                    np0 = p.colparam[j0];
+                    nb0 = p.colparam[j0].y;
                     if (p.col_video) nv0 = p.col_video[j0];
                     if (SEGMAX) ns0 = p.col_seg[j0];
                 }
                 if (j0 + 1 < ce) {
-                    np1 = p.colparam[j0 + 1];
+                    nb1 = p.colparam[j0 + 1].y;
                     if (p.col_video) nv1 = p.col_video[j0 + 1];
                     if (SEGMAX) ns1 = p.col_seg[j0 + 1];
                 }
             };
+            auto append = [&](float c, uint32_t j) {
+                buf[cnt] = make_key_desc(c, j);
+                ++cnt;
+            };
+            auto is_ignored = [&](int v) {
+                bool m = false;
+                for (int z = 0; z < p.n_ign; ++z) m |= (v == ign[row * kMaxIgnore + z]);
+                return m;
+            };
+            auto compact_rows = [&](uint32_t need, int keep_max) {
+                while (need) {
+                    const int src = __ffs(need) - 1;
+                    need &= need - 1;
+                    const int c_r = __shfl_sync(0xffffffffu, cnt, src);
+                    float t_r;
+                    const int nc = compact_row(wbuf + (int64_t)src * kCandCap, c_r, p.kprime, keep_max, lane, &t_r);
+                    if (lane == src) {
+                        cnt = nc;
+                        tau = fmaxf(tau, t_r);
+                    }
+                }
+            };
+            // Intermediate compactions fire early (a fresh tau rejects more in the cheap path) and
+            // only need a loose threshold; a tile can add at most BN entries, hence the cap.
+            const int trigger = min(4 * p.kprime, kCandCap - BN);
+            const int keep_max = max(p.kprime, min(2 * p.kprime, trigger - 128));
             fetch_cols(0);
             for (int t = 0; t < ntiles; ++t) {
                 // stage this tile's column parameters (buffer `as`), then prefetch the next tile's
-                colp[as * BN + et * 2] = np0;
-                colp[as * BN + et * 2 + 1] = np1;
-                colv[as * BN + et * 2] = nv0;
-                colv[as * BN + et * 2 + 1] = nv1;
-                if (SEGMAX) {
-                    cols[as * BN + et * 2] = ns0;
-                    cols[as * BN + et * 2 + 1] = ns1;
-                }
+                *reinterpret_cast<float2 *>(colb + as * BN + et * 2) = make_float2(nb0, nb1);
+                *reinterpret_cast<int2 *>(colv + as * BN + et * 2) = make_int2(nv0, nv1);
+                if (SEGMAX) *reinterpret_cast<int2 *>(cols + as * BN + et * 2) = make_int2(ns0, ns1);
                 named_bar_sync(1, kEpiThreads);
                 if (t + 1 < ntiles) fetch_cols(t + 1);
-                // make room: a tile can add at most BN entries
-                if (__any_sync(0xffffffffu, cnt > kCandCap - BN)) {
-                    uint32_t need = __ballot_sync(0xffffffffu, cnt > kCandCap - BN);
-                    while (need) {
-                        int src = __ffs(need) - 1;
-                        need &= need - 1;
-                        int c_r = __shfl_sync(0xffffffffu, cnt, src);
-                        float t_r;
-                        int nc = compact_row(wbuf + (int64_t)src * kCandCap, c_r, p.kprime, lane, &t_r);
-                        if (lane == src) {
-                            cnt = nc;
-                            tau = fmaxf(tau, t_r);
-                        }
-                    }
+                {
+                    const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
+                    if (need) compact_rows(need, keep_max);
                 }
                 mbar_wait(&tfull_bar[as], aphase);
                 tc_fence_after();
                 const uint32_t tacc = tmem_base + lane_addr + (uint32_t)(as * BN);
                 const uint32_t jbase = (uint32_t)(cs + (int64_t)t * BN);
-                const float2 *cp = colp + as * BN;
+                const float *cb = colb + as * BN;
                 const int *cv = colv + as * BN;
                 const int *csg = cols + as * BN;
 #pragma unroll 1
@@ -314,40 +344,61 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                         tc_fence_before();
                         mbar_arrive(&tempty_bar[as]);
                     }
+                    // 8 columns at a time: coarse scores, their max, ONE compare against the row's
+                    // threshold.  Only a group holding a candidate (rare once tau has warmed up)
+                    // takes the per-element path.
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const int col = ch * 32 + i;
-                        const float2 sp = cp[col];
-                        const float c = __fmaf_rn(__uint_as_float(r[i]), sp.x, sp.y);
+                    for (int g8 = 0; g8 < 4; ++g8) {
+                        const int col0 = ch * 32 + g8 * 8;
+                        const float4 b0 = *reinterpret_cast<const float4 *>(cb + col0);
+                        const float4 b1 = *reinterpret_cast<const float4 *>(cb + col0 + 4);
+                        float c[8];
+                        c[0] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 0]), 2.0f, b0.x);
+                        c[1] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 1]), 2.0f, b0.y);
+                        c[2] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 2]), 2.0f, b0.z);
+                        c[3] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 3]), 2.0f, b0.w);
+                        c[4] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 4]), 2.0f, b1.x);
+                        c[5] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 5]), 2.0f, b1.y);
+                        c[6] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 6]), 2.0f, b1.z);
+                        c[7] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 7]), 2.0f, b1.w);
+                        const float m8 = fmaxf(fmaxf(fmaxf(c[0], c[1]), fmaxf(c[2], c[3])),
+                                               fmaxf(fmaxf(c[4], c[5]), fmaxf(c[6], c[7])));
                         if (SEGMAX) {
-                            const int sg = csg[col];
-                            if (sg != cur_seg) {  // warp-uniform
-                                if (cur_max > tau && !grp_masked) {
-                                    buf[cnt] = make_key_desc(cur_max, cur_arg);
-                                    ++cnt;
+                            // cur_max tracks the best element ABOVE tau of the current video; elements
+                            // <= tau can never make a video a candidate and are skipped wholesale.
+                            if (m8 > tau) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    const int col = col0 + i;
+                                    const int sg = csg[col];
+                                    if (sg != cur_seg) {  // warp-uniform
+                                        if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
+                                        cur_seg = sg;
+                                        cur_max = -INFINITY;
+                                        grp_masked = p.n_ign > 0 ? is_ignored(cv[col]) : false;
+                                    }
+                                    if (c[i] > tau && c[i] > cur_max) {
+                                        cur_max = c[i];
+                                        cur_arg = jbase + col;
+                                    }
                                 }
-                                cur_seg = sg;
-                                cur_max = -INFINITY;
-                                grp_masked = false;
-                                if (p.n_ign > 0) {
-                                    const int v = cv[col];
-                                    for (int z = 0; z < p.n_ign; ++z) grp_masked |= (v == ign[row * kMaxIgnore + z]);
+                            } else {
+                                const int sg = csg[col0 + 7];
+                                if (sg != cur_seg) {  // a video boundary inside (or at the head of) the group
+                                    if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
+                                    cur_seg = sg;
+                                    cur_max = -INFINITY;
+                                    grp_masked = p.n_ign > 0 ? is_ignored(cv[col0 + 7]) : false;
                                 }
-                            }
-                            if (c > cur_max) {
-                                cur_max = c;
-                                cur_arg = jbase + col;
                             }
                         } else {
-                            if (c > tau) {
-                                bool masked = false;
-                                if (p.n_ign > 0) {
-                                    const int v = cv[col];
-                                    for (int z = 0; z < p.n_ign; ++z) masked |= (v == ign[row * kMaxIgnore + z]);
-                                }
-                                if (!masked) {
-                                    buf[cnt] = make_key_desc(c, jbase + col);
-                                    ++cnt;
+                            if (m8 > tau) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    if (c[i] > tau) {
+                                        const int col = col0 + i;
+                                        if (!(p.n_ign > 0 && is_ignored(cv[col]))) append(c[i], jbase + col);
+                                    }
                                 }
                             }
                         }
@@ -359,27 +410,11 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                 }
             }
             if (SEGMAX) {
-                if (cur_max > tau && !grp_masked) {
-                    buf[cnt] = make_key_desc(cur_max, cur_arg);
-                    ++cnt;
-                }
+                if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
             }
             __syncwarp();
-            // final compaction of this unit to <= k' entries per row
-            {
-                uint32_t need = __ballot_sync(0xffffffffu, cnt > p.kprime);
-                while (need) {
-                    int src = __ffs(need) - 1;
-                    need &= need - 1;
-                    int c_r = __shfl_sync(0xffffffffu, cnt, src);
-                    float t_r;
-                    int nc = compact_row(wbuf + (int64_t)src * kCandCap, c_r, p.kprime, lane, &t_r);
-                    if (lane == src) {
-                        cnt = nc;
-                        tau = fmaxf(tau, t_r);
-                    }
-                }
-            }
+            // final compaction of this unit to exactly <= k' entries per row
+            compact_rows(__ballot_sync(0xffffffffu, cnt > p.kprime), p.kprime);
             p.cand_cnt[(int64_t)u * BM + row] = qvalid ? cnt : 0;
             p.cand_tau[(int64_t)u * BM + row] = tau;
         }
