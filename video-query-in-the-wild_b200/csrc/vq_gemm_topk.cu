@@ -48,9 +48,9 @@ struct SmemLayout {
 // exact k'-th largest and ties at T are kept in buffer (= column) order up to the quota, so the
 // result is deterministic.  Returns the new count; *tau_out = a score such that everything
 // discarded is <= tau.
+template <int E>
 __device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, int keep_max, int lane,
                                            float *tau_out) {
-    constexpr int E = kCandCap / 32;
     uint32_t hi[E], lo[E];
     __syncwarp();  // the lanes' appends to this row are visible to the whole warp
 #pragma unroll
@@ -299,23 +299,30 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                 for (int z = 0; z < p.n_ign; ++z) m |= (v == ign[row * kMaxIgnore + z]);
                 return m;
             };
+            // E = buffer registers per lane a compaction scans: the trigger bounds the fill level
             auto compact_rows = [&](uint32_t need, int keep_max) {
                 while (need) {
                     const int src = __ffs(need) - 1;
                     need &= need - 1;
                     const int c_r = __shfl_sync(0xffffffffu, cnt, src);
+                    uint64_t *rb = wbuf + (int64_t)src * kCandCap;
                     float t_r;
-                    const int nc = compact_row(wbuf + (int64_t)src * kCandCap, c_r, p.kprime, keep_max, lane, &t_r);
+                    int nc;
+                    if (c_r <= 320) nc = compact_row<10>(rb, c_r, p.kprime, keep_max, lane, &t_r);
+                    else if (c_r <= 576) nc = compact_row<18>(rb, c_r, p.kprime, keep_max, lane, &t_r);
+                    else nc = compact_row<kCandCap / 32>(rb, c_r, p.kprime, keep_max, lane, &t_r);
                     if (lane == src) {
                         cnt = nc;
                         tau = fmaxf(tau, t_r);
                     }
                 }
             };
-            // Intermediate compactions fire early (a fresh tau rejects more in the cheap path) and
-            // only need a loose threshold; a tile can add at most BN entries, hence the cap.
-            const int trigger = min(4 * p.kprime, kCandCap - BN);
-            const int keep_max = max(p.kprime, min(2 * p.kprime, trigger - 128));
+            // Intermediate compactions are cheap (few registers, early-exit bisection) and fire
+            // often -- checked after every 32 columns -- so that tau stays close to the k'-th best
+            // seen so far and the per-element path below stays rare.  A 32-column step can add at
+            // most 32 entries, hence the cap.
+            const int trigger = min(2 * p.kprime, kCandCap - 64);
+            const int keep_max = min(p.kprime + p.kprime / 2, trigger - 32);
             fetch_cols(0);
             for (int t = 0; t < ntiles; ++t) {
                 // stage this tile's column parameters (buffer `as`), then prefetch the next tile's
@@ -324,10 +331,6 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                 if (SEGMAX) *reinterpret_cast<int2 *>(cols + as * BN + et * 2) = make_int2(ns0, ns1);
                 named_bar_sync(1, kEpiThreads);
                 if (t + 1 < ntiles) fetch_cols(t + 1);
-                {
-                    const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
-                    if (need) compact_rows(need, keep_max);
-                }
                 mbar_wait(&tfull_bar[as], aphase);
                 tc_fence_after();
                 const uint32_t tacc = tmem_base + lane_addr + (uint32_t)(as * BN);
@@ -344,65 +347,73 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                         tc_fence_before();
                         mbar_arrive(&tempty_bar[as]);
                     }
-                    // 8 columns at a time: coarse scores, their max, ONE compare against the row's
-                    // threshold.  Only a group holding a candidate (rare once tau has warmed up)
-                    // takes the per-element path.
+                    // coarse scores of 32 columns and their maxima per group of 8, all independent
+                    // (the lone epilogue warp of each scheduler needs the ILP); then ONE compare
+                    // against the row's threshold decides whether anything here is a candidate.
+                    float c[32], m8[4];
 #pragma unroll
                     for (int g8 = 0; g8 < 4; ++g8) {
-                        const int col0 = ch * 32 + g8 * 8;
-                        const float4 b0 = *reinterpret_cast<const float4 *>(cb + col0);
-                        const float4 b1 = *reinterpret_cast<const float4 *>(cb + col0 + 4);
-                        float c[8];
-                        c[0] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 0]), 2.0f, b0.x);
-                        c[1] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 1]), 2.0f, b0.y);
-                        c[2] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 2]), 2.0f, b0.z);
-                        c[3] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 3]), 2.0f, b0.w);
-                        c[4] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 4]), 2.0f, b1.x);
-                        c[5] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 5]), 2.0f, b1.y);
-                        c[6] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 6]), 2.0f, b1.z);
-                        c[7] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 7]), 2.0f, b1.w);
-                        const float m8 = fmaxf(fmaxf(fmaxf(c[0], c[1]), fmaxf(c[2], c[3])),
-                                               fmaxf(fmaxf(c[4], c[5]), fmaxf(c[6], c[7])));
-                        if (SEGMAX) {
-                            // cur_max tracks the best element ABOVE tau of the current video; elements
-                            // <= tau can never make a video a candidate and are skipped wholesale.
-                            if (m8 > tau) {
+                        const float4 b0 = *reinterpret_cast<const float4 *>(cb + ch * 32 + g8 * 8);
+                        const float4 b1 = *reinterpret_cast<const float4 *>(cb + ch * 32 + g8 * 8 + 4);
+                        float *cg = c + g8 * 8;
+                        cg[0] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 0]), 2.0f, b0.x);
+                        cg[1] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 1]), 2.0f, b0.y);
+                        cg[2] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 2]), 2.0f, b0.z);
+                        cg[3] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 3]), 2.0f, b0.w);
+                        cg[4] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 4]), 2.0f, b1.x);
+                        cg[5] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 5]), 2.0f, b1.y);
+                        cg[6] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 6]), 2.0f, b1.z);
+                        cg[7] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 7]), 2.0f, b1.w);
+                        m8[g8] = fmaxf(fmaxf(fmaxf(cg[0], cg[1]), fmaxf(cg[2], cg[3])),
+                                       fmaxf(fmaxf(cg[4], cg[5]), fmaxf(cg[6], cg[7])));
+                    }
+                    const float m32 = fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3]));
+                    if (SEGMAX) {
+                        // cur_max tracks the best element ABOVE tau of the current video; elements
+                        // <= tau can never make a video a candidate and are skipped wholesale.
+                        if (m32 > tau) {
 #pragma unroll
-                                for (int i = 0; i < 8; ++i) {
-                                    const int col = col0 + i;
-                                    const int sg = csg[col];
-                                    if (sg != cur_seg) {  // warp-uniform
-                                        if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
-                                        cur_seg = sg;
-                                        cur_max = -INFINITY;
-                                        grp_masked = p.n_ign > 0 ? is_ignored(cv[col]) : false;
-                                    }
-                                    if (c[i] > tau && c[i] > cur_max) {
-                                        cur_max = c[i];
-                                        cur_arg = jbase + col;
-                                    }
-                                }
-                            } else {
-                                const int sg = csg[col0 + 7];
-                                if (sg != cur_seg) {  // a video boundary inside (or at the head of) the group
+                            for (int i = 0; i < 32; ++i) {
+                                const int col = ch * 32 + i;
+                                const int sg = csg[col];
+                                if (sg != cur_seg) {  // warp-uniform
                                     if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
                                     cur_seg = sg;
                                     cur_max = -INFINITY;
-                                    grp_masked = p.n_ign > 0 ? is_ignored(cv[col0 + 7]) : false;
+                                    grp_masked = p.n_ign > 0 ? is_ignored(cv[col]) : false;
+                                }
+                                if (c[i] > tau && c[i] > cur_max) {
+                                    cur_max = c[i];
+                                    cur_arg = jbase + col;
                                 }
                             }
                         } else {
-                            if (m8 > tau) {
+                            const int sg = csg[ch * 32 + 31];
+                            if (sg != cur_seg) {  // a video boundary inside (or at the head of) these columns
+                                if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
+                                cur_seg = sg;
+                                cur_max = -INFINITY;
+                                grp_masked = p.n_ign > 0 ? is_ignored(cv[ch * 32 + 31]) : false;
+                            }
+                        }
+                    } else {
+                        if (m32 > tau) {
 #pragma unroll
-                                for (int i = 0; i < 8; ++i) {
-                                    if (c[i] > tau) {
-                                        const int col = col0 + i;
-                                        if (!(p.n_ign > 0 && is_ignored(cv[col]))) append(c[i], jbase + col);
+                            for (int g8 = 0; g8 < 4; ++g8) {
+                                if (m8[g8] > tau) {
+#pragma unroll
+                                    for (int i = 0; i < 8; ++i) {
+                                        if (c[g8 * 8 + i] > tau) {
+                                            const int col = ch * 32 + g8 * 8 + i;
+                                            if (!(p.n_ign > 0 && is_ignored(cv[col]))) append(c[g8 * 8 + i], jbase + col);
+                                        }
                                     }
                                 }
                             }
                         }
                     }
+                    const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
+                    if (need) compact_rows(need, keep_max);
                 }
                 if (++as == 2) {
                     as = 0;
