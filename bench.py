@@ -404,7 +404,7 @@ def run_b200(a):
                 "d2h_bytes_per_step": a.nq * k * 12, "ms_per_step": e2e_ms / a.steps},
         "gpu_launches": (stats["launches"] + (1 if G > 1 else 0)) * a.steps,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                     "traffic": traffic, "kernel": "gemm_topk_kernel<1,false>", "kernel_ms": g_ms,
+                     "traffic": traffic, "kernel": "gemm_topk_pair_kernel<false> (cta_group::2)", "kernel_ms": g_ms,
                      "algorithmic_flops_per_launch": flops, "peak_source": which},
         "phases_ms": {kk: sum(p[kk] for p in phase_ms) / len(phase_ms) for kk in phase_ms[0]},
         "search_stats": stats, "result_checksum": checksum, "clocks": clocks,

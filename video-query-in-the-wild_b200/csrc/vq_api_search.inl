@@ -27,11 +27,10 @@ static void error_model(int prec, int dtype, int dp, float *eps_rel, float *eps_
 }
 
 // Split the gallery into chunks so that (query blocks x chunks) fills the SMs evenly.
-static void plan_chunks(const vq_index *ix, int64_t nq, int kprime, bool segmax, std::vector<int64_t> *cs) {
-    const int sms = sm_count();
+// `nqb` work items per chunk (query blocks, or pairs of them) are spread over `sms` slots.
+static void plan_chunks(const vq_index *ix, int64_t nqb, int sms, int kprime, bool segmax, std::vector<int64_t> *cs) {
     const int64_t n = ix->n;
     const int64_t ntiles = (n + kTileN - 1) / kTileN;
-    const int64_t nqb = (nq + kTileM - 1) / kTileM;
     int64_t max_chunks = std::min<int64_t>(ntiles, (int64_t)(128 * 64) / kprime);
     max_chunks = std::min<int64_t>(max_chunks, std::max<int64_t>(1, ntiles / 8));  // >= 8 tiles per chunk
     max_chunks = std::max<int64_t>(1, std::min<int64_t>(max_chunks, 64));
@@ -96,6 +95,8 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     }
     const int kprime = choose_kprime(k, prec, dtype);
     VQ_CHECK(k <= kprime, VQ_ERR_CAPACITY, "k=%d exceeds the streaming top-k limit %d", k, kMaxKPrime);
+    // bf16 single pass with dim <= 512 runs on CTA pairs (resident queries, split gallery tiles)
+    const bool pair = prec != VQ_PREC_SPLIT3 && ix->dp <= 512 && !getenv("VQ_DEBUG_NO_PAIR");
     // query operand planes
     Tmp qhi, qlo;
     ix->ev_valid = false;
@@ -107,15 +108,22 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
                                split ? (__nv_bfloat16 *)qlo.p : nullptr, nullptr, nullptr, nullptr, st));
     ++launches;
     CUtensorMap maps[4];
-    VQ_TRY(make_map(&maps[0], qhi.p, nq, ix->dp, kTileM));
-    VQ_TRY(make_map(&maps[1], split ? qlo.p : qhi.p, nq, ix->dp, kTileM));
-    VQ_TRY(make_map(&maps[2], ix->hi, ix->n, ix->dp, kTileN));
-    VQ_TRY(make_map(&maps[3], split ? (void *)ix->lo : (void *)ix->hi, ix->n, ix->dp, kTileN));
-    // work decomposition
+    if (pair) {
+        VQ_TRY(make_map(&maps[0], qhi.p, nq, ix->dp, kTileM));
+        VQ_TRY(make_map(&maps[1], ix->hi, ix->n, ix->dp, kTileN / 2));
+    } else {
+        VQ_TRY(make_map(&maps[0], qhi.p, nq, ix->dp, kTileM));
+        VQ_TRY(make_map(&maps[1], split ? qlo.p : qhi.p, nq, ix->dp, kTileM));
+        VQ_TRY(make_map(&maps[2], ix->hi, ix->n, ix->dp, kTileN));
+        VQ_TRY(make_map(&maps[3], split ? (void *)ix->lo : (void *)ix->hi, ix->n, ix->dp, kTileN));
+    }
+    // work decomposition (pair path: query blocks padded to an even count, the pad block is all out of range)
+    int n_qblocks = (int)((nq + kTileM - 1) / kTileM);
+    if (pair) n_qblocks = (n_qblocks + 1) / 2 * 2;
+    const int slots = pair ? gemm_topk_pair_slots() : sm_count();
     std::vector<int64_t> cs;
-    plan_chunks(ix, nq, kprime, segmax, &cs);
+    plan_chunks(ix, pair ? n_qblocks / 2 : n_qblocks, slots, kprime, segmax, &cs);
     const int n_chunks = (int)cs.size() - 1;
-    const int n_qblocks = (int)((nq + kTileM - 1) / kTileM);
     const size_t units = (size_t)n_chunks * n_qblocks;
     VQ_TRY(ensure(&ix->chunk_start_dev, &ix->chunk_cap, cs.size()));
     VQ_CUDA(cudaMemcpyAsync(ix->chunk_start_dev, cs.data(), cs.size() * 8, cudaMemcpyHostToDevice, st));
@@ -135,9 +143,12 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     gp.col_seg = segmax ? ix->seg_of_row : nullptr;
     gp.q_ignore = n_ign > 0 ? ign : nullptr; gp.n_ign = n_ign; gp.kprime = kprime;
     gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau;
-    const int grid = (int)std::min<size_t>(units, (size_t)sm_count());
     VQ_CUDA(cudaEventRecord(ix->ev[1], st));
-    VQ_TRY(launch_gemm_topk(maps, gp, split ? 3 : 1, segmax, grid, st));
+    if (pair) {
+        VQ_TRY(launch_gemm_topk_pair(maps, gp, segmax, (int)std::min<size_t>(units / 2, (size_t)slots), st));
+    } else {
+        VQ_TRY(launch_gemm_topk(maps, gp, split ? 3 : 1, segmax, (int)std::min<size_t>(units, (size_t)slots), st));
+    }
     VQ_CUDA(cudaEventRecord(ix->ev[2], st));
     ++launches;
 

@@ -1,8 +1,8 @@
 // vq_gemm_topk.cu -- kernels (1)+(2): query x gallery similarity GEMM on tcgen05/TMEM tiles fed
 // by TMA, with a fused epilogue that turns each accumulator tile into coarse scores
-// (c = scale_j * <q,g_j> + bias_j; l2sq: 2<q,g> - |g|^2) and streams them into a per-query
-// candidate list (threshold filter + warp-cooperative select), optionally max-pooling over the
-// moments of one untrimmed video first.  The Q x N score matrix never exists in HBM.
+// (l2sq: c = 2<q,g> - |g|^2) and streams them into a per-query candidate list (threshold filter +
+// warp-cooperative select), optionally max-pooling over the moments of one untrimmed video
+// first.  The Q x N score matrix never exists in HBM.
 //
 // Replaces the arithmetic of faiss.IndexFlatL2.search (dataloader_baseline.py:1592-1597,
 // :935-940, :1268-1273) and the labelling "ignore" rule (:1548) for the candidates it emits.
@@ -10,9 +10,16 @@
 // chain, proves the top-k complete against the discard threshold tau emitted here, and sends
 // unproven queries to the exact fallback.
 //
-// Structure (one CTA per SM, persistent over work units = (gallery chunk, 128-query block)):
-//   warp 0     TMA producer: A (queries) and B (gallery) k-blocks of 64 bf16 -> 128B-swizzled smem
-//   warp 1     MMA issuer: tcgen05.mma kind::f16, M=128 N=256 K=16, fp32 accumulators in TMEM
+// Two kernels share one epilogue:
+//   gemm_topk_pair_kernel (bf16 single pass, dim <= 512): a CTA PAIR per work item
+//     (cluster of 2, tcgen05 cta_group::2, UMMA M=256 N=256 K=16).  Each CTA keeps its 128 query
+//     rows resident in shared memory for the whole gallery chunk and streams only its HALF of
+//     every gallery tile (128 rows x 64 k, 16 KB per stage); the MMA reads both halves.  Per SM
+//     that is 16 KB of L2->SM traffic per 128x256x64 MMA block instead of 48 KB.
+//   gemm_topk_kernel (split-bf16 fp32 mode, or dim > 512): one CTA per work item, A and B
+//     k-blocks streamed together.
+//   warp 0     TMA producer: k-blocks of 64 bf16 -> 128B-swizzled smem
+//   warp 1     MMA issuer (pair: leader CTA only), fp32 accumulators in TMEM
 //              (2 x 256 columns, double buffered against the epilogue)
 //   warps 2-5  epilogue: tcgen05.ld 32 lanes x 32 columns, one query row per thread
 #include "vq_common.cuh"
@@ -40,6 +47,24 @@ struct SmemLayout {
     static constexpr int OFF_TMEM = OFF_BAR + NBAR * 8;
     static constexpr int TOTAL = OFF_TMEM + 16 + 1024;  // + alignment slack
 };
+
+// pair kernel: resident A (up to 8 k-blocks) + B half-tile stages
+struct PairLayout {
+    static constexpr int KB_MAX = 8;                         // dim <= 512
+    static constexpr int BH_BYTES = (BN / 2) * BK * 2;       // 16 KB: this CTA's half of a gallery tile k-block
+    static constexpr int STAGES = 5;
+    static constexpr int OFF_B = KB_MAX * A_BYTES;           // 128 KB
+    static constexpr int OFF_COLP = OFF_B + STAGES * BH_BYTES;
+    static constexpr int OFF_COLV = OFF_COLP + 2 * BN * 4;
+    static constexpr int OFF_COLS = OFF_COLV + 2 * BN * 4;
+    static constexpr int OFF_IGN = OFF_COLS + 2 * BN * 4;
+    static constexpr int OFF_BAR = OFF_IGN + BM * kMaxIgnore * 4;
+    // full[S] empty[S] tfull[2] tempty[2] afull aempty
+    static constexpr int NBAR = 2 * STAGES + 6;
+    static constexpr int OFF_TMEM = OFF_BAR + NBAR * 8;
+    static constexpr int TOTAL = OFF_TMEM + 16 + 1024;
+};
+static_assert(PairLayout::TOTAL <= 227 * 1024, "pair kernel shared memory");
 
 // Warp-cooperative compaction of one query row's candidate buffer.  Finds a threshold word T by
 // bisection on the ordered score bits such that kprime <= #{score >= T}; with keep_max > kprime
@@ -109,6 +134,205 @@ __device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, i
     __syncwarp();
     *tau_out = ordered_to_f32(T);
     return pos;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Epilogue role (warps 2-5 of either kernel).  Work items w = w0, w0 + w_stride, ... < n_work.
+// ---------------------------------------------------------------------------------------------
+template <bool SEGMAX, bool PAIR>
+__device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *colb, int *colv, int *cols, int *ign,
+                                              uint64_t *tfull_bar, uint64_t *tempty_bar, uint32_t tempty_leader,
+                                              uint32_t tmem_base, int w0, int w_stride, int n_work, int rank) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int et = threadIdx.x - 64;         // 0..127
+    const int quarter = warp & 3;            // TMEM lane quarter this warp may read
+    const int row = quarter * 32 + lane;     // accumulator row == query row in the block
+    const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int w = w0; w < n_work; w += w_stride) {
+        // PAIR: work item = (chunk, pair of query blocks), this CTA takes block 2*pair + rank
+        const int per_chunk = PAIR ? p.n_qblocks / 2 : p.n_qblocks;
+        const int chunk = w / per_chunk;
+        const int qb = PAIR ? 2 * (w % per_chunk) + rank : w % per_chunk;
+        const int u = chunk * p.n_qblocks + qb;
+        const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+        const int ntiles = (int)((ce - cs + BN - 1) / BN);
+        const int64_t q = (int64_t)qb * BM + row;
+        const bool qvalid = q < p.nq;
+        uint64_t *buf = p.cand + ((int64_t)u * BM + row) * kCandCap;
+        uint64_t *wbuf = p.cand + ((int64_t)u * BM + quarter * 32) * kCandCap;
+        float tau = qvalid ? -INFINITY : INFINITY;
+        int cnt = 0;
+        // group-max state (SEGMAX)
+        int cur_seg = -2;
+        float cur_max = -INFINITY;
+        uint32_t cur_arg = 0;
+        bool grp_masked = false;
+        if (p.n_ign > 0) {  // each thread only ever reads its own row's ignore list
+            for (int t = 0; t < p.n_ign; ++t)
+                ign[row * kMaxIgnore + t] = qvalid ? p.q_ignore[q * p.n_ign + t] : -1;
+        }
+        // column parameters of tile 0 (2 columns per thread); the coarse score is
+        // c = 2 <q,g> - |g|^2 (colparam = (2, -|g|^2), vq_prepare.cu), only the bias is staged
+        float nb0, nb1;
+        int nv0 = -1, nv1 = -1, ns0 = -1, ns1 = -1;
+        auto fetch_cols = [&](int t) {
+            int64_t j0 = cs + (int64_t)t * BN + et * 2;
+            nb0 = nb1 = -INFINITY;
+            nv0 = nv1 = -1;
+            ns0 = ns1 = -1;
+            if (j0 < ce) {
+                nb0 = p.colparam[j0].y;
+                if (p.col_video) nv0 = p.col_video[j0];
+                if (SEGMAX) ns0 = p.col_seg[j0];
+            }
+            if (j0 + 1 < ce) {
+                nb1 = p.colparam[j0 + 1].y;
+                if (p.col_video) nv1 = p.col_video[j0 + 1];
+                if (SEGMAX) ns1 = p.col_seg[j0 + 1];
+            }
+        };
+        auto append = [&](float c, uint32_t j) {
+            buf[cnt] = make_key_desc(c, j);
+            ++cnt;
+        };
+        auto is_ignored = [&](int v) {
+            bool m = false;
+            for (int z = 0; z < p.n_ign; ++z) m |= (v == ign[row * kMaxIgnore + z]);
+            return m;
+        };
+        // E = buffer registers per lane a compaction scans: the trigger bounds the fill level
+        auto compact_rows = [&](uint32_t need, int keep_max) {
+            while (need) {
+                const int src = __ffs(need) - 1;
+                need &= need - 1;
+                const int c_r = __shfl_sync(0xffffffffu, cnt, src);
+                uint64_t *rb = wbuf + (int64_t)src * kCandCap;
+                float t_r;
+                int nc;
+                if (c_r <= 320) nc = compact_row<10>(rb, c_r, p.kprime, keep_max, lane, &t_r);
+                else if (c_r <= 576) nc = compact_row<18>(rb, c_r, p.kprime, keep_max, lane, &t_r);
+                else nc = compact_row<kCandCap / 32>(rb, c_r, p.kprime, keep_max, lane, &t_r);
+                if (lane == src) {
+                    cnt = nc;
+                    tau = fmaxf(tau, t_r);
+                }
+            }
+        };
+        // Intermediate compactions are cheap (few registers, early-exit bisection) and fire
+        // often -- checked after every 32 columns -- so that tau stays close to the k'-th best
+        // seen so far and the per-element path below stays rare.  A 32-column step can add at
+        // most 32 entries, hence the cap.
+        const int trigger = min(2 * p.kprime, kCandCap - 64);
+        const int keep_max = min(p.kprime + p.kprime / 2, trigger - 32);
+        fetch_cols(0);
+        for (int t = 0; t < ntiles; ++t) {
+            // stage this tile's column parameters (buffer `as`), then prefetch the next tile's
+            *reinterpret_cast<float2 *>(colb + as * BN + et * 2) = make_float2(nb0, nb1);
+            *reinterpret_cast<int2 *>(colv + as * BN + et * 2) = make_int2(nv0, nv1);
+            if (SEGMAX) *reinterpret_cast<int2 *>(cols + as * BN + et * 2) = make_int2(ns0, ns1);
+            named_bar_sync(1, kEpiThreads);
+            if (t + 1 < ntiles) fetch_cols(t + 1);
+            mbar_wait(&tfull_bar[as], aphase);
+            tc_fence_after();
+            const uint32_t tacc = tmem_base + lane_addr + (uint32_t)(as * BN);
+            const uint32_t jbase = (uint32_t)(cs + (int64_t)t * BN);
+            const float *cb = colb + as * BN;
+            const int *cv = colv + as * BN;
+            const int *csg = cols + as * BN;
+#pragma unroll 1
+            for (int ch = 0; ch < BN / 32; ++ch) {
+                uint32_t r[32];
+                tmem_ld32(tacc + ch * 32, r);
+                tmem_wait_ld();
+                if (ch == BN / 32 - 1) {  // accumulator fully read: hand TMEM back to the MMA warp
+                    tc_fence_before();
+                    if (PAIR) mbar_arrive_cluster(tempty_leader + 8u * as);  // the pair's MMA thread waits on the leader's
+                    else mbar_arrive(&tempty_bar[as]);
+                }
+                // coarse scores of 32 columns and their maxima per group of 8, all independent
+                // (the lone epilogue warp of each scheduler needs the ILP); then ONE compare
+                // against the row's threshold decides whether anything here is a candidate.
+                float c[32], m8[4];
+#pragma unroll
+                for (int g8 = 0; g8 < 4; ++g8) {
+                    const float4 b0 = *reinterpret_cast<const float4 *>(cb + ch * 32 + g8 * 8);
+                    const float4 b1 = *reinterpret_cast<const float4 *>(cb + ch * 32 + g8 * 8 + 4);
+                    float *cg = c + g8 * 8;
+                    cg[0] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 0]), 2.0f, b0.x);
+                    cg[1] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 1]), 2.0f, b0.y);
+                    cg[2] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 2]), 2.0f, b0.z);
+                    cg[3] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 3]), 2.0f, b0.w);
+                    cg[4] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 4]), 2.0f, b1.x);
+                    cg[5] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 5]), 2.0f, b1.y);
+                    cg[6] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 6]), 2.0f, b1.z);
+                    cg[7] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 7]), 2.0f, b1.w);
+                    m8[g8] = fmaxf(fmaxf(fmaxf(cg[0], cg[1]), fmaxf(cg[2], cg[3])),
+                                   fmaxf(fmaxf(cg[4], cg[5]), fmaxf(cg[6], cg[7])));
+                }
+                const float m32 = fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3]));
+                if (SEGMAX) {
+                    // cur_max tracks the best element ABOVE tau of the current video; elements
+                    // <= tau can never make a video a candidate and are skipped wholesale.
+                    if (m32 > tau) {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i) {
+                            const int col = ch * 32 + i;
+                            const int sg = csg[col];
+                            if (sg != cur_seg) {  // warp-uniform
+                                if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
+                                cur_seg = sg;
+                                cur_max = -INFINITY;
+                                grp_masked = p.n_ign > 0 ? is_ignored(cv[col]) : false;
+                            }
+                            if (c[i] > tau && c[i] > cur_max) {
+                                cur_max = c[i];
+                                cur_arg = jbase + col;
+                            }
+                        }
+                    } else {
+                        const int sg = csg[ch * 32 + 31];
+                        if (sg != cur_seg) {  // a video boundary inside (or at the head of) these columns
+                            if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
+                            cur_seg = sg;
+                            cur_max = -INFINITY;
+                            grp_masked = p.n_ign > 0 ? is_ignored(cv[ch * 32 + 31]) : false;
+                        }
+                    }
+                } else {
+                    if (m32 > tau) {
+#pragma unroll
+                        for (int g8 = 0; g8 < 4; ++g8) {
+                            if (m8[g8] > tau) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) {
+                                    if (c[g8 * 8 + i] > tau) {
+                                        const int col = ch * 32 + g8 * 8 + i;
+                                        if (!(p.n_ign > 0 && is_ignored(cv[col]))) append(c[g8 * 8 + i], jbase + col);
+                                    }
+                                }
+                            }
+                        }
+                    }
+                }
+                const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
+                if (need) compact_rows(need, keep_max);
+            }
+            if (++as == 2) {
+                as = 0;
+                aphase ^= 1u;
+            }
+        }
+        if (SEGMAX) {
+            if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
+        }
+        __syncwarp();
+        // final compaction of this unit to exactly <= k' entries per row
+        compact_rows(__ballot_sync(0xffffffffu, cnt > p.kprime), p.kprime);
+        p.cand_cnt[(int64_t)u * BM + row] = qvalid ? cnt : 0;
+        p.cand_tau[(int64_t)u * BM + row] = tau;
+    }
 }
 
 template <int NPASS, bool SEGMAX>
@@ -244,191 +468,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
             }
         }
     } else {
-        // ================================ epilogue =====================================
-        const int et = threadIdx.x - 64;         // 0..127
-        const int quarter = warp & 3;            // TMEM lane quarter this warp may read
-        const int row = quarter * 32 + lane;     // accumulator row == query row in the block
-        const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
-        int as = 0;
-        uint32_t aphase = 0;
-        for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-            const int chunk = u / p.n_qblocks, qb = u % p.n_qblocks;
-            const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
-            const int ntiles = (int)((ce - cs + BN - 1) / BN);
-            const int64_t q = (int64_t)qb * BM + row;
-            const bool qvalid = q < p.nq;
-            uint64_t *buf = p.cand + ((int64_t)u * BM + row) * kCandCap;
-            uint64_t *wbuf = p.cand + ((int64_t)u * BM + quarter * 32) * kCandCap;
-            float tau = qvalid ? -INFINITY : INFINITY;
-            int cnt = 0;
-            // group-max state (SEGMAX)
-            int cur_seg = -2;
-            float cur_max = -INFINITY;
-            uint32_t cur_arg = 0;
-            bool grp_masked = false;
-            if (p.n_ign > 0) {  // each thread only ever reads its own row's ignore list
-                for (int t = 0; t < p.n_ign; ++t)
-                    ign[row * kMaxIgnore + t] = qvalid ? p.q_ignore[q * p.n_ign + t] : -1;
-            }
-            // column parameters of tile 0 (2 columns per thread); the coarse score is
-            // c = 2 <q,g> - |g|^2 (colparam = (2, -|g|^2), vq_prepare.cu), only the bias is staged
-            float nb0, nb1;
-            int nv0 = -1, nv1 = -1, ns0 = -1, ns1 = -1;
-            auto fetch_cols = [&](int t) {
-                int64_t j0 = cs + (int64_t)t * BN + et * 2;
-                nb0 = nb1 = -INFINITY;
-                nv0 = nv1 = -1;
-                ns0 = ns1 = -1;
-                if (j0 < ce) {
-                    nb0 = p.colparam[j0].y;
-                    if (p.col_video) nv0 = p.col_video[j0];
-                    if (SEGMAX) ns0 = p.col_seg[j0];
-                }
-                if (j0 + 1 < ce) {
-                    nb1 = p.colparam[j0 + 1].y;
-                    if (p.col_video) nv1 = p.col_video[j0 + 1];
-                    if (SEGMAX) ns1 = p.col_seg[j0 + 1];
-                }
-            };
-            auto append = [&](float c, uint32_t j) {
-                buf[cnt] = make_key_desc(c, j);
-                ++cnt;
-            };
-            auto is_ignored = [&](int v) {
-                bool m = false;
-                for (int z = 0; z < p.n_ign; ++z) m |= (v == ign[row * kMaxIgnore + z]);
-                return m;
-            };
-            // E = buffer registers per lane a compaction scans: the trigger bounds the fill level
-            auto compact_rows = [&](uint32_t need, int keep_max) {
-                while (need) {
-                    const int src = __ffs(need) - 1;
-                    need &= need - 1;
-                    const int c_r = __shfl_sync(0xffffffffu, cnt, src);
-                    uint64_t *rb = wbuf + (int64_t)src * kCandCap;
-                    float t_r;
-                    int nc;
-                    if (c_r <= 320) nc = compact_row<10>(rb, c_r, p.kprime, keep_max, lane, &t_r);
-                    else if (c_r <= 576) nc = compact_row<18>(rb, c_r, p.kprime, keep_max, lane, &t_r);
-                    else nc = compact_row<kCandCap / 32>(rb, c_r, p.kprime, keep_max, lane, &t_r);
-                    if (lane == src) {
-                        cnt = nc;
-                        tau = fmaxf(tau, t_r);
-                    }
-                }
-            };
-            // Intermediate compactions are cheap (few registers, early-exit bisection) and fire
-            // often -- checked after every 32 columns -- so that tau stays close to the k'-th best
-            // seen so far and the per-element path below stays rare.  A 32-column step can add at
-            // most 32 entries, hence the cap.
-            const int trigger = min(2 * p.kprime, kCandCap - 64);
-            const int keep_max = min(p.kprime + p.kprime / 2, trigger - 32);
-            fetch_cols(0);
-            for (int t = 0; t < ntiles; ++t) {
-                // stage this tile's column parameters (buffer `as`), then prefetch the next tile's
-                *reinterpret_cast<float2 *>(colb + as * BN + et * 2) = make_float2(nb0, nb1);
-                *reinterpret_cast<int2 *>(colv + as * BN + et * 2) = make_int2(nv0, nv1);
-                if (SEGMAX) *reinterpret_cast<int2 *>(cols + as * BN + et * 2) = make_int2(ns0, ns1);
-                named_bar_sync(1, kEpiThreads);
-                if (t + 1 < ntiles) fetch_cols(t + 1);
-                mbar_wait(&tfull_bar[as], aphase);
-                tc_fence_after();
-                const uint32_t tacc = tmem_base + lane_addr + (uint32_t)(as * BN);
-                const uint32_t jbase = (uint32_t)(cs + (int64_t)t * BN);
-                const float *cb = colb + as * BN;
-                const int *cv = colv + as * BN;
-                const int *csg = cols + as * BN;
-#pragma unroll 1
-                for (int ch = 0; ch < BN / 32; ++ch) {
-                    uint32_t r[32];
-                    tmem_ld32(tacc + ch * 32, r);
-                    tmem_wait_ld();
-                    if (ch == BN / 32 - 1) {  // accumulator fully read: hand TMEM back to the MMA warp
-                        tc_fence_before();
-                        mbar_arrive(&tempty_bar[as]);
-                    }
-                    // coarse scores of 32 columns and their maxima per group of 8, all independent
-                    // (the lone epilogue warp of each scheduler needs the ILP); then ONE compare
-                    // against the row's threshold decides whether anything here is a candidate.
-                    float c[32], m8[4];
-#pragma unroll
-                    for (int g8 = 0; g8 < 4; ++g8) {
-                        const float4 b0 = *reinterpret_cast<const float4 *>(cb + ch * 32 + g8 * 8);
-                        const float4 b1 = *reinterpret_cast<const float4 *>(cb + ch * 32 + g8 * 8 + 4);
-                        float *cg = c + g8 * 8;
-                        cg[0] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 0]), 2.0f, b0.x);
-                        cg[1] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 1]), 2.0f, b0.y);
-                        cg[2] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 2]), 2.0f, b0.z);
-                        cg[3] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 3]), 2.0f, b0.w);
-                        cg[4] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 4]), 2.0f, b1.x);
-                        cg[5] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 5]), 2.0f, b1.y);
-                        cg[6] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 6]), 2.0f, b1.z);
-                        cg[7] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 7]), 2.0f, b1.w);
-                        m8[g8] = fmaxf(fmaxf(fmaxf(cg[0], cg[1]), fmaxf(cg[2], cg[3])),
-                                       fmaxf(fmaxf(cg[4], cg[5]), fmaxf(cg[6], cg[7])));
-                    }
-                    const float m32 = fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3]));
-                    if (SEGMAX) {
-                        // cur_max tracks the best element ABOVE tau of the current video; elements
-                        // <= tau can never make a video a candidate and are skipped wholesale.
-                        if (m32 > tau) {
-#pragma unroll
-                            for (int i = 0; i < 32; ++i) {
-                                const int col = ch * 32 + i;
-                                const int sg = csg[col];
-                                if (sg != cur_seg) {  // warp-uniform
-                                    if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
-                                    cur_seg = sg;
-                                    cur_max = -INFINITY;
-                                    grp_masked = p.n_ign > 0 ? is_ignored(cv[col]) : false;
-                                }
-                                if (c[i] > tau && c[i] > cur_max) {
-                                    cur_max = c[i];
-                                    cur_arg = jbase + col;
-                                }
-                            }
-                        } else {
-                            const int sg = csg[ch * 32 + 31];
-                            if (sg != cur_seg) {  // a video boundary inside (or at the head of) these columns
-                                if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
-                                cur_seg = sg;
-                                cur_max = -INFINITY;
-                                grp_masked = p.n_ign > 0 ? is_ignored(cv[ch * 32 + 31]) : false;
-                            }
-                        }
-                    } else {
-                        if (m32 > tau) {
-#pragma unroll
-                            for (int g8 = 0; g8 < 4; ++g8) {
-                                if (m8[g8] > tau) {
-#pragma unroll
-                                    for (int i = 0; i < 8; ++i) {
-                                        if (c[g8 * 8 + i] > tau) {
-                                            const int col = ch * 32 + g8 * 8 + i;
-                                            if (!(p.n_ign > 0 && is_ignored(cv[col]))) append(c[g8 * 8 + i], jbase + col);
-                                        }
-                                    }
-                                }
-                            }
-                        }
-                    }
-                    const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
-                    if (need) compact_rows(need, keep_max);
-                }
-                if (++as == 2) {
-                    as = 0;
-                    aphase ^= 1u;
-                }
-            }
-            if (SEGMAX) {
-                if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
-            }
-            __syncwarp();
-            // final compaction of this unit to exactly <= k' entries per row
-            compact_rows(__ballot_sync(0xffffffffu, cnt > p.kprime), p.kprime);
-            p.cand_cnt[(int64_t)u * BM + row] = qvalid ? cnt : 0;
-            p.cand_tau[(int64_t)u * BM + row] = tau;
-        }
+        epilogue_role<SEGMAX, false>(p, colb, colv, cols, ign, tfull_bar, tempty_bar, 0u, tmem_base, (int)blockIdx.x,
+                                     (int)gridDim.x, n_units, 0);
     }
 
     tc_fence_before();
@@ -436,6 +477,158 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
     if (warp == 1) {
         tc_fence_after();
         tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// CTA-pair kernel (see the header comment).  Barriers: full[s] / afull / tempty[a] are waited on by
+// the leader's MMA thread and live in the LEADER's shared memory (the peer reaches them through
+// the cluster window); empty[s] / aempty / tfull[a] are signalled by the leader's multicast
+// tcgen05.commit into BOTH CTAs and each CTA waits on its own copy.
+// ---------------------------------------------------------------------------------------------
+template <bool SEGMAX>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_constant__ CUtensorMap tm_b,
+                      const GemmTopkParams p) {
+    using L = PairLayout;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float *colb = (float *)(smem + L::OFF_COLP);
+    int *colv = (int *)(smem + L::OFF_COLV);
+    int *cols = (int *)(smem + L::OFF_COLS);
+    int *ign = (int *)(smem + L::OFF_IGN);
+    uint64_t *full_bar = (uint64_t *)(smem + L::OFF_BAR);
+    uint64_t *empty_bar = full_bar + L::STAGES;
+    uint64_t *tfull_bar = empty_bar + L::STAGES;
+    uint64_t *tempty_bar = tfull_bar + 2;
+    uint64_t *afull_bar = tempty_bar + 2;
+    uint64_t *aempty_bar = afull_bar + 1;
+    uint32_t *tmem_slot = (uint32_t *)(smem + L::OFF_TMEM);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int rank = (int)cluster_ctarank();
+    const int pair = (int)blockIdx.x >> 1, n_pairs = (int)gridDim.x >> 1;
+    const int n_work = p.n_chunks * (p.n_qblocks / 2);
+    const int KB = p.kb_count;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_a);
+        tma_prefetch_desc(&tm_b);
+        for (int s = 0; s < L::STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);   // leader's producer arrives with the byte count of BOTH halves
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&tfull_bar[s], 1);
+            mbar_init(&tempty_bar[s], 2 * kEpiThreads);  // both CTAs' epilogue threads
+        }
+        mbar_init(afull_bar, 1);
+        mbar_init(aempty_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc_cg2(tmem_slot, 512);
+        tmem_relinquish_cg2();
+    }
+    tc_fence_before();
+    cluster_sync_all();  // barriers of both CTAs initialised before any remote arrive / multicast commit
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================ TMA producer (both CTAs) =====================
+        if (lane == 0) {
+            const uint32_t full_leader = mapa_u32(full_bar, 0);
+            const uint32_t afull_leader = mapa_u32(afull_bar, 0);
+            int stage = 0;
+            uint32_t phase = 0, aphase = 0;
+            for (int w = pair; w < n_work; w += n_pairs) {
+                const int per_chunk = p.n_qblocks / 2;
+                const int chunk = w / per_chunk, qb = 2 * (w % per_chunk) + rank;
+                const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+                const int ntiles = (int)((ce - cs + BN - 1) / BN);
+                // this CTA's 128 query rows, resident for the whole chunk
+                mbar_wait(aempty_bar, aphase ^ 1u);
+                aphase ^= 1u;
+                if (rank == 0) mbar_expect_tx(afull_bar, 2u * (uint32_t)KB * A_BYTES);
+                for (int kb = 0; kb < KB; ++kb)
+                    tma_load_2d_cg2(&tm_a, afull_leader, smem + kb * A_BYTES, kb * BK, qb * BM, kEvictLast);
+                // this CTA's half of every gallery tile
+                for (int t = 0; t < ntiles; ++t) {
+                    const int row0 = (int)(cs + (int64_t)t * BN) + rank * (BN / 2);
+                    for (int kb = 0; kb < KB; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1u);
+                        if (rank == 0) mbar_expect_tx(&full_bar[stage], 2u * L::BH_BYTES);
+                        tma_load_2d_cg2(&tm_b, full_leader + 8u * stage, smem + L::OFF_B + stage * L::BH_BYTES, kb * BK,
+                                        row0, kEvictNormal);
+                        if (++stage == L::STAGES) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                }
+            }
+            // the leader's last multicast commit has landed in THIS CTA before anyone may leave
+            mbar_wait(aempty_bar, aphase ^ 1u);
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer (leader CTA) ======================
+        if (rank == 0) {
+            constexpr uint32_t idesc = umma_idesc_bf16(2 * BM, BN);
+            int stage = 0;
+            uint32_t phase = 0, aphase = 0;
+            int as = 0;
+            uint32_t tphase = 0;
+            for (int w = pair; w < n_work; w += n_pairs) {
+                const int chunk = w / (p.n_qblocks / 2);
+                const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+                const int ntiles = (int)((ce - cs + BN - 1) / BN);
+                mbar_wait(afull_bar, aphase);
+                aphase ^= 1u;
+                tc_fence_after();
+                for (int t = 0; t < ntiles; ++t) {
+                    mbar_wait(&tempty_bar[as], tphase ^ 1u);
+                    tc_fence_after();
+                    const uint32_t tacc = tmem_base + (uint32_t)(as * BN);
+                    for (int kb = 0; kb < KB; ++kb) {
+                        mbar_wait(&full_bar[stage], phase);
+                        tc_fence_after();
+                        if (lane == 0) {
+                            const uint64_t ad = umma_desc_sw128(smem_u32(smem + kb * A_BYTES));
+                            const uint64_t bd = umma_desc_sw128(smem_u32(smem + L::OFF_B + stage * L::BH_BYTES));
+#pragma unroll
+                            for (int k = 0; k < BK / 16; ++k)
+                                umma_bf16_cg2(tacc, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                            umma_commit_cg2(&empty_bar[stage]);
+                            if (kb == KB - 1) {
+                                umma_commit_cg2(&tfull_bar[as]);
+                                if (t == ntiles - 1) umma_commit_cg2(aempty_bar);  // resident A may be replaced
+                            }
+                        }
+                        __syncwarp();
+                        if (++stage == L::STAGES) {
+                            stage = 0;
+                            phase ^= 1u;
+                        }
+                    }
+                    if (++as == 2) {
+                        as = 0;
+                        tphase ^= 1u;
+                    }
+                }
+            }
+        }
+    } else {
+        epilogue_role<SEGMAX, true>(p, colb, colv, cols, ign, tfull_bar, tempty_bar, mapa_u32(tempty_bar, 0), tmem_base,
+                                    pair, n_pairs, n_work, rank);
+    }
+
+    __syncwarp();
+    tc_fence_before();
+    cluster_sync_all();  // no CTA leaves while its peer can still touch its barriers / shared memory
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc_cg2(tmem_base, 512);
     }
 }
 
@@ -453,6 +646,63 @@ int launch_gemm_topk(const CUtensorMap *maps, const GemmTopkParams &p, int npass
                      cudaStream_t st) {
     if (npass == 1) return segmax ? launch_t<1, true>(maps, p, grid, st) : launch_t<1, false>(maps, p, grid, st);
     return segmax ? launch_t<3, true>(maps, p, grid, st) : launch_t<3, false>(maps, p, grid, st);
+}
+
+static int g_pair_slots = 0;
+
+template <bool SEGMAX>
+static int launch_pair_t(const CUtensorMap *maps, const GemmTopkParams &p, int n_pairs, cudaStream_t st) {
+    auto kern = gemm_topk_pair_kernel<SEGMAX>;
+    VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairLayout::TOTAL));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(2 * n_pairs);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = PairLayout::TOTAL;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    VQ_CUDA(cudaLaunchKernelEx(&cfg, kern, maps[0], maps[1], p));
+    return VQ_OK;
+}
+
+// co-resident CTA pairs (GPC shapes can strand an SM): the persistent grid is sized to this
+int gemm_topk_pair_slots() {
+    if (g_pair_slots) return g_pair_slots;
+    auto kern = gemm_topk_pair_kernel<false>;
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, PairLayout::TOTAL);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(sms / 2 * 2);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = PairLayout::TOTAL;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    int mc = 0;
+    if (cudaOccupancyMaxActiveClusters(&mc, kern, &cfg) != cudaSuccess || mc <= 0) {
+        cudaGetLastError();
+        mc = sms / 2;
+    }
+    g_pair_slots = mc < sms / 2 ? mc : sms / 2;
+    return g_pair_slots;
+}
+
+// maps2 = {A box [64 x 128], B box [64 x 128]}; p.n_qblocks must be even; p.kb_count <= 8
+int launch_gemm_topk_pair(const CUtensorMap *maps2, const GemmTopkParams &p, bool segmax, int n_pairs,
+                          cudaStream_t st) {
+    VQ_CHECK(p.n_qblocks % 2 == 0 && p.kb_count <= PairLayout::KB_MAX, VQ_ERR_INVALID, "pair kernel preconditions");
+    return segmax ? launch_pair_t<true>(maps2, p, n_pairs, st) : launch_pair_t<false>(maps2, p, n_pairs, st);
 }
 
 }  // namespace vq

@@ -31,6 +31,12 @@ struct GemmTopkParams {
 int launch_gemm_topk(const CUtensorMap *maps4, const GemmTopkParams &p, int npass, bool segmax,
                      int grid, cudaStream_t st);
 
+// CTA-pair variant (bf16 single pass, padded dim <= 512): maps2 = {queries, gallery}, both with
+// boxes of 64 columns x 128 rows; p.n_qblocks must be even (pad with an out-of-range block).
+int launch_gemm_topk_pair(const CUtensorMap *maps2, const GemmTopkParams &p, bool segmax, int n_pairs,
+                          cudaStream_t st);
+int gemm_topk_pair_slots();  // co-resident CTA pairs on this device
+
 // ---- vq_prepare.cu ----
 // fp32 or bf16 rows [n,d] -> bf16 planes hi/lo [n,dp] (zero padded), colparam (2, -|x|^2),
 // norm2 [n]; max_norm2 (ordered-uint atomicMax target, may be null).
