@@ -142,7 +142,8 @@ static EncodeTiledFn encode_fn() {
     return fn;
 }
 
-// bf16 plane [rows, dp] row-major -> boxes of 64 columns x box_rows rows, 128-byte swizzle
+// bf16 plane [rows, dp] row-major (dp = plane pitch incl. the augmentation block) -> boxes of 64
+// columns x box_rows rows, 128-byte swizzle; the box at column pitch-16 is zero-filled past the edge
 static int make_map(CUtensorMap *m, const void *base, int64_t rows, int dp, int box_rows) {
     EncodeTiledFn fn = encode_fn();
     VQ_CHECK(fn, VQ_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
@@ -165,12 +166,11 @@ using namespace vq;
 // index object
 // ---------------------------------------------------------------------------------------
 struct vq_index {
-    int d = 0, dp = 0, dtype = -1, prec = VQ_PREC_AUTO;
+    int d = 0, dp = 0, dpa = 0, dtype = -1, prec = VQ_PREC_AUTO;  // dpa = dp + kAugCols: operand plane pitch
     int64_t n = 0, cap = 0;
     void *raw = nullptr;            // [cap, d] f32 or bf16: the rows as given (canonical re-scoring)
-    __nv_bfloat16 *hi = nullptr;    // [cap, dp]
-    __nv_bfloat16 *lo = nullptr;    // [cap, dp] (f32 input only)
-    float2 *colparam = nullptr;     // [cap]
+    __nv_bfloat16 *hi = nullptr;    // [cap, dpa]
+    __nv_bfloat16 *lo = nullptr;    // [cap, dpa] (f32 input only)
     float *norm2 = nullptr;         // [cap]
     uint32_t *gmax_bits = nullptr;  // [1]
     int32_t *label = nullptr, *video = nullptr;  // [n]
@@ -221,6 +221,7 @@ int vq_index_create(int d, vq_index **out) {
     vq_index *ix = new vq_index();
     ix->d = d;
     ix->dp = (d + 63) / 64 * 64;
+    ix->dpa = ix->dp + kAugCols;
     if (cudaMalloc(&ix->gmax_bits, 4) != cudaSuccess || cudaMalloc(&ix->unproven_count, 4) != cudaSuccess ||
         cudaMallocHost(&ix->stat_pinned, 4) != cudaSuccess) {
         set_error("vq_index_create: allocation failed: %s", cudaGetErrorString(cudaGetLastError()));
@@ -238,7 +239,7 @@ int vq_index_create(int d, vq_index **out) {
 int vq_index_destroy(vq_index *ix) {
     if (!ix) return VQ_OK;
     cudaDeviceSynchronize();
-    void *ptrs[] = {ix->raw,   ix->hi,         ix->lo,           ix->colparam,     ix->norm2,    ix->gmax_bits,
+    void *ptrs[] = {ix->raw,   ix->hi,         ix->lo,           ix->norm2,    ix->gmax_bits,
                     ix->label, ix->video,      ix->seg_of_row,   ix->seg_start_dev, ix->cand,     ix->cand_cnt,
                     ix->cand_tau, ix->chunk_start_dev, ix->unproven, ix->unproven_count};
     for (void *p : ptrs)
@@ -297,18 +298,16 @@ int vq_index_add(vq_index *ix, const void *xb, int64_t n, int dtype, void *strea
         char *raw = (char *)ix->raw;
         VQ_TRY(grow<char>(&raw, ix->n * ix->d * es, ncap * ix->d * es, st));
         ix->raw = raw;
-        VQ_TRY(grow<__nv_bfloat16>(&ix->hi, ix->n * ix->dp, ncap * ix->dp, st));
-        if (dtype == VQ_F32) VQ_TRY(grow<__nv_bfloat16>(&ix->lo, ix->n * ix->dp, ncap * ix->dp, st));
-        VQ_TRY(grow<float2>(&ix->colparam, ix->n, ncap, st));
+        VQ_TRY(grow<__nv_bfloat16>(&ix->hi, ix->n * ix->dpa, ncap * ix->dpa, st));
+        if (dtype == VQ_F32) VQ_TRY(grow<__nv_bfloat16>(&ix->lo, ix->n * ix->dpa, ncap * ix->dpa, st));
         VQ_TRY(grow<float>(&ix->norm2, ix->n, ncap, st));
         ix->cap = ncap;
     }
     const size_t es = esize(dtype);
     char *dst = (char *)ix->raw + (size_t)ix->n * ix->d * es;
     VQ_CUDA(cudaMemcpyAsync(dst, xb, (size_t)n * ix->d * es, cudaMemcpyDefault, st));
-    VQ_TRY(launch_prepare_rows(dst, dtype, n, ix->d, ix->dp, ix->hi + ix->n * ix->dp,
-                               ix->lo ? ix->lo + ix->n * ix->dp : nullptr, ix->colparam + ix->n, ix->norm2 + ix->n,
-                               ix->gmax_bits, st));
+    VQ_TRY(launch_prepare_rows(dst, dtype, n, ix->d, ix->dp, false, ix->hi + ix->n * ix->dpa,
+                               ix->lo ? ix->lo + ix->n * ix->dpa : nullptr, ix->norm2 + ix->n, ix->gmax_bits, st));
     ix->n = nn;
     // metadata no longer covers all rows
     if (ix->label) { cudaFree(ix->label); ix->label = nullptr; }

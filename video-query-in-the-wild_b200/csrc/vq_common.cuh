@@ -210,7 +210,9 @@ __device__ __forceinline__ uint32_t mapa_u32(const void *p, uint32_t rank) {
     return r;
 }
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+    // relaxed: the arrive publishes no generic-memory data (TMEM reads are ordered by tcgen05.fence); the
+    // release form costs a MEMBAR.GPU + ERRBAR per call
+    asm volatile("mbarrier.arrive.relaxed.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA tile load issued by either CTA of a pair into its OWN shared memory, completing on a
 // barrier that may live in the peer (leader) CTA

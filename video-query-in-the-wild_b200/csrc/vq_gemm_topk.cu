@@ -1,8 +1,9 @@
 // vq_gemm_topk.cu -- kernels (1)+(2): query x gallery similarity GEMM on tcgen05/TMEM tiles fed
 // by TMA, with a fused epilogue that turns each accumulator tile into coarse scores
-// (l2sq: c = 2<q,g> - |g|^2) and streams them into a per-query candidate list (threshold filter +
-// warp-cooperative select), optionally max-pooling over the moments of one untrimmed video
-// first.  The Q x N score matrix never exists in HBM.
+// (l2sq: c = 2<q,g> - |g|^2; the -|g|^2/2 term rides in a 16-column augmentation k-block, see
+// vq_kernels.h, so the accumulator IS c/2) and streams them into a per-query candidate list
+// (threshold filter + warp-cooperative select), optionally max-pooling over the moments of one
+// untrimmed video first.  The Q x N score matrix never exists in HBM.
 //
 // Replaces the arithmetic of faiss.IndexFlatL2.search (dataloader_baseline.py:1592-1597,
 // :935-940, :1268-1273) and the labelling "ignore" rule (:1548) for the candidates it emits.
@@ -38,26 +39,22 @@ struct SmemLayout {
     static constexpr int NPLANE = NPASS == 1 ? 1 : 2;
     static constexpr int STAGE_BYTES = NPLANE * (A_BYTES + B_BYTES);
     static constexpr int STAGES = NPASS == 1 ? 4 : 2;
-    static constexpr int OFF_COLP = STAGES * STAGE_BYTES;          // float[2][BN] column bias (-|g|^2)
-    static constexpr int OFF_COLV = OFF_COLP + 2 * BN * 4;         // int[2][BN]
-    static constexpr int OFF_COLS = OFF_COLV + 2 * BN * 4;         // int[2][BN]
-    static constexpr int OFF_IGN = OFF_COLS + 2 * BN * 4;          // int[BM][kMaxIgnore]
+    static constexpr int OFF_SCR = STAGES * STAGE_BYTES;           // float[4][32] per-warp transpose scratch
+    static constexpr int OFF_IGN = OFF_SCR + 4 * 32 * 4;           // int[BM][kMaxIgnore]
     static constexpr int OFF_BAR = OFF_IGN + BM * kMaxIgnore * 4;  // mbarriers
     static constexpr int NBAR = 2 * STAGES + 4;
     static constexpr int OFF_TMEM = OFF_BAR + NBAR * 8;
     static constexpr int TOTAL = OFF_TMEM + 16 + 1024;  // + alignment slack
 };
 
-// pair kernel: resident A (up to 8 k-blocks) + B half-tile stages
+// pair kernel: resident A (up to 8 k-blocks + the augmentation block) + B half-tile stages
 struct PairLayout {
     static constexpr int KB_MAX = 8;                         // dim <= 512
     static constexpr int BH_BYTES = (BN / 2) * BK * 2;       // 16 KB: this CTA's half of a gallery tile k-block
-    static constexpr int STAGES = 5;
-    static constexpr int OFF_B = KB_MAX * A_BYTES;           // 128 KB
-    static constexpr int OFF_COLP = OFF_B + STAGES * BH_BYTES;
-    static constexpr int OFF_COLV = OFF_COLP + 2 * BN * 4;
-    static constexpr int OFF_COLS = OFF_COLV + 2 * BN * 4;
-    static constexpr int OFF_IGN = OFF_COLS + 2 * BN * 4;
+    static constexpr int STAGES = 4;
+    static constexpr int OFF_B = (KB_MAX + 1) * A_BYTES;     // 144 KB
+    static constexpr int OFF_SCR = OFF_B + STAGES * BH_BYTES;
+    static constexpr int OFF_IGN = OFF_SCR + 4 * 32 * 4;
     static constexpr int OFF_BAR = OFF_IGN + BM * kMaxIgnore * 4;
     // full[S] empty[S] tfull[2] tempty[2] afull aempty
     static constexpr int NBAR = 2 * STAGES + 6;
@@ -138,16 +135,21 @@ __device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, i
 
 // ---------------------------------------------------------------------------------------------
 // Epilogue role (warps 2-5 of either kernel).  Work items w = w0, w0 + w_stride, ... < n_work.
+// Thread = accumulator row = query.  Per 32 columns: tcgen05.ld, max of the 32 values, ONE compare
+// against the row's threshold.  Rows that hold a candidate are handled by the whole warp: the
+// row's values are transposed through shared memory so that lane i tests column i, and the hits
+// are appended to the row's list with one ballot.
 // ---------------------------------------------------------------------------------------------
 template <bool SEGMAX, bool PAIR>
-__device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *colb, int *colv, int *cols, int *ign,
-                                              uint64_t *tfull_bar, uint64_t *tempty_bar, uint32_t tempty_leader,
-                                              uint32_t tmem_base, int w0, int w_stride, int n_work, int rank) {
+__device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *scr, int *ign, uint64_t *tfull_bar,
+                                              uint64_t *tempty_bar, uint32_t tempty_leader, uint32_t tmem_base,
+                                              int w0, int w_stride, int n_work, int rank) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int et = threadIdx.x - 64;         // 0..127
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
     const int row = quarter * 32 + lane;     // accumulator row == query row in the block
     const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+    const uint32_t lt_mask = (1u << lane) - 1u;
+    float *wscr = scr + quarter * 32;
     int as = 0;
     uint32_t aphase = 0;
     for (int w = w0; w < n_work; w += w_stride) {
@@ -162,44 +164,27 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *co
         const bool qvalid = q < p.nq;
         uint64_t *buf = p.cand + ((int64_t)u * BM + row) * kCandCap;
         uint64_t *wbuf = p.cand + ((int64_t)u * BM + quarter * 32) * kCandCap;
-        float tau = qvalid ? -INFINITY : INFINITY;
+        // tau: everything discarded so far has coarse score <= tau; tauh = tau / 2 is what the
+        // accumulator (= score / 2) is compared with
+        float tau = qvalid ? -INFINITY : INFINITY, tauh = tau;
         int cnt = 0;
-        // group-max state (SEGMAX)
+        // group-max state (SEGMAX), in accumulator (half-score) units
         int cur_seg = -2;
-        float cur_max = -INFINITY;
+        float cur_maxh = -INFINITY;
         uint32_t cur_arg = 0;
         bool grp_masked = false;
-        if (p.n_ign > 0) {  // each thread only ever reads its own row's ignore list
-            for (int t = 0; t < p.n_ign; ++t)
-                ign[row * kMaxIgnore + t] = qvalid ? p.q_ignore[q * p.n_ign + t] : -1;
+        __syncwarp();
+        if (p.n_ign > 0) {
+            for (int t = 0; t < p.n_ign; ++t) ign[row * kMaxIgnore + t] = qvalid ? p.q_ignore[q * p.n_ign + t] : -1;
         }
-        // column parameters of tile 0 (2 columns per thread); the coarse score is
-        // c = 2 <q,g> - |g|^2 (colparam = (2, -|g|^2), vq_prepare.cu), only the bias is staged
-        float nb0, nb1;
-        int nv0 = -1, nv1 = -1, ns0 = -1, ns1 = -1;
-        auto fetch_cols = [&](int t) {
-            int64_t j0 = cs + (int64_t)t * BN + et * 2;
-            nb0 = nb1 = -INFINITY;
-            nv0 = nv1 = -1;
-            ns0 = ns1 = -1;
-            if (j0 < ce) {
-                nb0 = p.colparam[j0].y;
-                if (p.col_video) nv0 = p.col_video[j0];
-                if (SEGMAX) ns0 = p.col_seg[j0];
-            }
-            if (j0 + 1 < ce) {
-                nb1 = p.colparam[j0 + 1].y;
-                if (p.col_video) nv1 = p.col_video[j0 + 1];
-                if (SEGMAX) ns1 = p.col_seg[j0 + 1];
-            }
-        };
+        __syncwarp();  // the warp-cooperative path reads other rows' ignore lists
         auto append = [&](float c, uint32_t j) {
             buf[cnt] = make_key_desc(c, j);
             ++cnt;
         };
-        auto is_ignored = [&](int v) {
+        auto is_ignored = [&](int r, int v) {
             bool m = false;
-            for (int z = 0; z < p.n_ign; ++z) m |= (v == ign[row * kMaxIgnore + z]);
+            for (int z = 0; z < p.n_ign; ++z) m |= (v == ign[r * kMaxIgnore + z]);
             return m;
         };
         // E = buffer registers per lane a compaction scans: the trigger bounds the fill level
@@ -217,107 +202,109 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *co
                 if (lane == src) {
                     cnt = nc;
                     tau = fmaxf(tau, t_r);
+                    tauh = 0.5f * tau;
                 }
             }
         };
         // Intermediate compactions are cheap (few registers, early-exit bisection) and fire
-        // often -- checked after every 32 columns -- so that tau stays close to the k'-th best
-        // seen so far and the per-element path below stays rare.  A 32-column step can add at
-        // most 32 entries, hence the cap.
+        // often so that tau stays close to the k'-th best seen so far.  A 32-column step can add
+        // at most 33 entries, hence the cap.
         const int trigger = min(2 * p.kprime, kCandCap - 64);
         const int keep_max = min(p.kprime + p.kprime / 2, trigger - 32);
-        fetch_cols(0);
         for (int t = 0; t < ntiles; ++t) {
-            // stage this tile's column parameters (buffer `as`), then prefetch the next tile's
-            *reinterpret_cast<float2 *>(colb + as * BN + et * 2) = make_float2(nb0, nb1);
-            *reinterpret_cast<int2 *>(colv + as * BN + et * 2) = make_int2(nv0, nv1);
-            if (SEGMAX) *reinterpret_cast<int2 *>(cols + as * BN + et * 2) = make_int2(ns0, ns1);
-            named_bar_sync(1, kEpiThreads);
-            if (t + 1 < ntiles) fetch_cols(t + 1);
             mbar_wait(&tfull_bar[as], aphase);
             tc_fence_after();
             const uint32_t tacc = tmem_base + lane_addr + (uint32_t)(as * BN);
-            const uint32_t jbase = (uint32_t)(cs + (int64_t)t * BN);
-            const float *cb = colb + as * BN;
-            const int *cv = colv + as * BN;
-            const int *csg = cols + as * BN;
+            const int64_t j0 = cs + (int64_t)t * BN;
+            const uint32_t jbase = (uint32_t)j0;
+            const int ncols = (int)min((int64_t)BN, ce - j0);  // < BN only in the last tile of a chunk
 #pragma unroll 1
             for (int ch = 0; ch < BN / 32; ++ch) {
                 uint32_t r[32];
                 tmem_ld32(tacc + ch * 32, r);
                 tmem_wait_ld();
-                if (ch == BN / 32 - 1) {  // accumulator fully read: hand TMEM back to the MMA warp
+                if (ch == BN / 32 - 1) {  // accumulator fully read: hand TMEM back to the MMA thread
                     tc_fence_before();
-                    if (PAIR) mbar_arrive_cluster(tempty_leader + 8u * as);  // the pair's MMA thread waits on the leader's
+                    if (PAIR) mbar_arrive_cluster(tempty_leader + 8u * as);  // it waits on the leader's barrier
                     else mbar_arrive(&tempty_bar[as]);
                 }
-                // coarse scores of 32 columns and their maxima per group of 8, all independent
-                // (the lone epilogue warp of each scheduler needs the ILP); then ONE compare
-                // against the row's threshold decides whether anything here is a candidate.
-                float c[32], m8[4];
+                if (ncols < BN) {  // columns past the chunk end (zero-filled operands) can never qualify
+                    if (ch * 32 >= ncols) continue;
 #pragma unroll
-                for (int g8 = 0; g8 < 4; ++g8) {
-                    const float4 b0 = *reinterpret_cast<const float4 *>(cb + ch * 32 + g8 * 8);
-                    const float4 b1 = *reinterpret_cast<const float4 *>(cb + ch * 32 + g8 * 8 + 4);
-                    float *cg = c + g8 * 8;
-                    cg[0] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 0]), 2.0f, b0.x);
-                    cg[1] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 1]), 2.0f, b0.y);
-                    cg[2] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 2]), 2.0f, b0.z);
-                    cg[3] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 3]), 2.0f, b0.w);
-                    cg[4] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 4]), 2.0f, b1.x);
-                    cg[5] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 5]), 2.0f, b1.y);
-                    cg[6] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 6]), 2.0f, b1.z);
-                    cg[7] = __fmaf_rn(__uint_as_float(r[g8 * 8 + 7]), 2.0f, b1.w);
-                    m8[g8] = fmaxf(fmaxf(fmaxf(cg[0], cg[1]), fmaxf(cg[2], cg[3])),
-                                   fmaxf(fmaxf(cg[4], cg[5]), fmaxf(cg[6], cg[7])));
+                    for (int i = 0; i < 32; ++i)
+                        if (ch * 32 + i >= ncols) r[i] = 0xff800000u;
                 }
-                const float m32 = fmaxf(fmaxf(m8[0], m8[1]), fmaxf(m8[2], m8[3]));
+                float v[32];
+#pragma unroll
+                for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+                // max of 32 (3-input max tree)
+                float m[11];
+#pragma unroll
+                for (int i = 0; i < 10; ++i) m[i] = fmaxf(fmaxf(v[3 * i], v[3 * i + 1]), v[3 * i + 2]);
+                m[10] = fmaxf(v[30], v[31]);
+                const float m32 = fmaxf(fmaxf(fmaxf(fmaxf(m[0], m[1]), m[2]), fmaxf(fmaxf(m[3], m[4]), m[5])),
+                                        fmaxf(fmaxf(fmaxf(m[6], m[7]), m[8]), fmaxf(m[9], m[10])));
                 if (SEGMAX) {
-                    // cur_max tracks the best element ABOVE tau of the current video; elements
+                    // cur_maxh tracks the best element ABOVE tau of the current video; elements
                     // <= tau can never make a video a candidate and are skipped wholesale.
-                    if (m32 > tau) {
+                    if (m32 > tauh) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
                             const int col = ch * 32 + i;
-                            const int sg = csg[col];
-                            if (sg != cur_seg) {  // warp-uniform
-                                if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
-                                cur_seg = sg;
-                                cur_max = -INFINITY;
-                                grp_masked = p.n_ign > 0 ? is_ignored(cv[col]) : false;
-                            }
-                            if (c[i] > tau && c[i] > cur_max) {
-                                cur_max = c[i];
-                                cur_arg = jbase + col;
-                            }
-                        }
-                    } else {
-                        const int sg = csg[ch * 32 + 31];
-                        if (sg != cur_seg) {  // a video boundary inside (or at the head of) these columns
-                            if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
-                            cur_seg = sg;
-                            cur_max = -INFINITY;
-                            grp_masked = p.n_ign > 0 ? is_ignored(cv[ch * 32 + 31]) : false;
-                        }
-                    }
-                } else {
-                    if (m32 > tau) {
-#pragma unroll
-                        for (int g8 = 0; g8 < 4; ++g8) {
-                            if (m8[g8] > tau) {
-#pragma unroll
-                                for (int i = 0; i < 8; ++i) {
-                                    if (c[g8 * 8 + i] > tau) {
-                                        const int col = ch * 32 + g8 * 8 + i;
-                                        if (!(p.n_ign > 0 && is_ignored(cv[col]))) append(c[g8 * 8 + i], jbase + col);
-                                    }
+                            if (col < ncols) {  // warp-uniform
+                                const int sg = __ldg(p.col_seg + j0 + col);
+                                if (sg != cur_seg) {  // warp-uniform
+                                    if (cur_maxh > tauh && !grp_masked) append(2.0f * cur_maxh, cur_arg);
+                                    cur_seg = sg;
+                                    cur_maxh = -INFINITY;
+                                    grp_masked = p.n_ign > 0 ? is_ignored(row, __ldg(p.col_video + j0 + col)) : false;
+                                }
+                                if (v[i] > tauh && v[i] > cur_maxh) {
+                                    cur_maxh = v[i];
+                                    cur_arg = jbase + col;
                                 }
                             }
                         }
+                    } else {
+                        const int col = min(ch * 32 + 31, ncols - 1);
+                        const int sg = __ldg(p.col_seg + j0 + col);
+                        if (sg != cur_seg) {  // a video boundary inside (or at the head of) these columns
+                            if (cur_maxh > tauh && !grp_masked) append(2.0f * cur_maxh, cur_arg);
+                            cur_seg = sg;
+                            cur_maxh = -INFINITY;
+                            grp_masked = p.n_ign > 0 ? is_ignored(row, __ldg(p.col_video + j0 + col)) : false;
+                        }
+                    }
+                    const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
+                    if (need) compact_rows(need, keep_max);
+                } else {
+                    uint32_t bal = __ballot_sync(0xffffffffu, m32 > tauh);
+                    if (bal) {  // warp-uniform; rare once tau has warmed up
+                        while (bal) {
+                            const int L = __ffs(bal) - 1;
+                            bal &= bal - 1;
+                            if (lane == L) {
+#pragma unroll
+                                for (int i = 0; i < 8; ++i)
+                                    *reinterpret_cast<float4 *>(wscr + 4 * i) =
+                                        make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                            }
+                            __syncwarp();
+                            const float x = wscr[lane];  // row L, column ch*32 + lane
+                            const float tL = __shfl_sync(0xffffffffu, tauh, L);
+                            const int cL = __shfl_sync(0xffffffffu, cnt, L);
+                            const uint32_t j = jbase + (uint32_t)(ch * 32 + lane);
+                            bool hit = x > tL;
+                            if (hit && p.n_ign > 0) hit = !is_ignored(quarter * 32 + L, __ldg(p.col_video + j));
+                            const uint32_t hm = __ballot_sync(0xffffffffu, hit);
+                            if (hit) wbuf[(int64_t)L * kCandCap + cL + __popc(hm & lt_mask)] = make_key_desc(2.0f * x, j);
+                            if (lane == L) cnt += __popc(hm);
+                            __syncwarp();  // scratch is reused by the next row
+                        }
+                        const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
+                        if (need) compact_rows(need, keep_max);
                     }
                 }
-                const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
-                if (need) compact_rows(need, keep_max);
             }
             if (++as == 2) {
                 as = 0;
@@ -325,7 +312,7 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *co
             }
         }
         if (SEGMAX) {
-            if (cur_max > tau && !grp_masked) append(cur_max, cur_arg);
+            if (cur_maxh > tauh && !grp_masked) append(2.0f * cur_maxh, cur_arg);
         }
         __syncwarp();
         // final compaction of this unit to exactly <= k' entries per row
@@ -344,9 +331,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
     extern __shared__ uint8_t smem_raw[];
     // 1024-byte alignment (SWIZZLE_128B) by offset arithmetic: keeps the pointer in the shared window (LDS/STS)
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    float *colb = (float *)(smem + L::OFF_COLP);
-    int *colv = (int *)(smem + L::OFF_COLV);
-    int *cols = (int *)(smem + L::OFF_COLS);
+    float *scr = (float *)(smem + L::OFF_SCR);
     int *ign = (int *)(smem + L::OFF_IGN);
     uint64_t *full_bar = (uint64_t *)(smem + L::OFF_BAR);
     uint64_t *empty_bar = full_bar + L::STAGES;
@@ -386,19 +371,21 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
 
     if (warp == 0) {
         // ================================ TMA producer =================================
-        if (lane == 0) {
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-                const int chunk = u / p.n_qblocks, qb = u % p.n_qblocks;
-                const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
-                const int ntiles = (int)((ce - cs + BN - 1) / BN);
-                const int q0 = qb * BM;
-                for (int t = 0; t < ntiles; ++t) {
-                    const int row0 = (int)(cs + (int64_t)t * BN);
-                    for (int kb = 0; kb < KB; ++kb) {
-                        mbar_wait(&empty_bar[stage], phase ^ 1u);
-                        uint8_t *sa = smem + stage * L::STAGE_BYTES;
+        // The whole warp runs the loops (warp-uniform control flow keeps the TMA operands in
+        // uniform registers); one elected lane issues.
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
+            const int chunk = u / p.n_qblocks, qb = u % p.n_qblocks;
+            const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+            const int ntiles = (int)((ce - cs + BN - 1) / BN);
+            const int q0 = qb * BM;
+            for (int t = 0; t < ntiles; ++t) {
+                const int row0 = (int)(cs + (int64_t)t * BN);
+                for (int kb = 0; kb <= KB; ++kb) {  // kb == KB: the augmentation block (zero-filled past 16 columns)
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    uint8_t *sa = smem + stage * L::STAGE_BYTES;
+                    if (elect_one()) {
                         mbar_expect_tx(&full_bar[stage], L::STAGE_BYTES);
                         tma_load_2d(&tm_a_hi, &full_bar[stage], sa, kb * BK, q0, kEvictLast);
                         if (NPASS > 1) {
@@ -408,10 +395,11 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                         } else {
                             tma_load_2d(&tm_b_hi, &full_bar[stage], sa + A_BYTES, kb * BK, row0, kEvictNormal);
                         }
-                        if (++stage == L::STAGES) {
-                            stage = 0;
-                            phase ^= 1u;
-                        }
+                    }
+                    __syncwarp();
+                    if (++stage == L::STAGES) {
+                        stage = 0;
+                        phase ^= 1u;
                     }
                 }
             }
@@ -431,29 +419,32 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
                 mbar_wait(&tempty_bar[as], aphase ^ 1u);
                 tc_fence_after();
                 const uint32_t tacc = tmem_base + (uint32_t)(as * BN);
-                for (int kb = 0; kb < KB; ++kb) {
+                for (int kb = 0; kb <= KB; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    if (lane == 0) {
-                        const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
+                    const uint32_t sa = smem_u32(smem + stage * L::STAGE_BYTES);
+                    if (elect_one()) {  // warp-uniform operands + elect.sync: no per-lane waterfall around the MMAs
+                        const int nk = kb == KB ? kAugCols / 16 : BK / 16;  // augmentation block: one K=16 step, hi x hi only
                         if (NPASS == 1) {
                             const uint64_t ad = umma_desc_sw128(sa), bd = umma_desc_sw128(sa + A_BYTES);
-#pragma unroll
-                            for (int k = 0; k < BK / 16; ++k)
-                                umma_bf16(tacc, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                            for (int k = 0; k < nk; ++k) umma_bf16(tacc, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
                         } else {
                             const uint64_t ah = umma_desc_sw128(sa), al = umma_desc_sw128(sa + A_BYTES);
                             const uint64_t bh = umma_desc_sw128(sa + 2 * A_BYTES);
                             const uint64_t bl = umma_desc_sw128(sa + 2 * A_BYTES + B_BYTES);
+                            if (kb == KB) {
+                                umma_bf16(tacc, ah, bh, idesc, 1);
+                            } else {
 #pragma unroll
-                            for (int k = 0; k < BK / 16; ++k) {
-                                umma_bf16(tacc, al + 2 * k, bh + 2 * k, idesc, (kb | k) != 0);
-                                umma_bf16(tacc, ah + 2 * k, bl + 2 * k, idesc, 1);
-                                umma_bf16(tacc, ah + 2 * k, bh + 2 * k, idesc, 1);
+                                for (int k = 0; k < BK / 16; ++k) {
+                                    umma_bf16(tacc, al + 2 * k, bh + 2 * k, idesc, (kb | k) != 0);
+                                    umma_bf16(tacc, ah + 2 * k, bl + 2 * k, idesc, 1);
+                                    umma_bf16(tacc, ah + 2 * k, bh + 2 * k, idesc, 1);
+                                }
                             }
                         }
                         umma_commit(&empty_bar[stage]);  // frees the smem stage when the MMAs retire
-                        if (kb == KB - 1) umma_commit(&tfull_bar[as]);
+                        if (kb == KB) umma_commit(&tfull_bar[as]);
                     }
                     __syncwarp();
                     if (++stage == L::STAGES) {
@@ -468,7 +459,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
             }
         }
     } else {
-        epilogue_role<SEGMAX, false>(p, colb, colv, cols, ign, tfull_bar, tempty_bar, 0u, tmem_base, (int)blockIdx.x,
+        epilogue_role<SEGMAX, false>(p, scr, ign, tfull_bar, tempty_bar, 0u, tmem_base, (int)blockIdx.x,
                                      (int)gridDim.x, n_units, 0);
     }
 
@@ -493,9 +484,7 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
     using L = PairLayout;
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    float *colb = (float *)(smem + L::OFF_COLP);
-    int *colv = (int *)(smem + L::OFF_COLV);
-    int *cols = (int *)(smem + L::OFF_COLS);
+    float *scr = (float *)(smem + L::OFF_SCR);
     int *ign = (int *)(smem + L::OFF_IGN);
     uint64_t *full_bar = (uint64_t *)(smem + L::OFF_BAR);
     uint64_t *empty_bar = full_bar + L::STAGES;
@@ -537,40 +526,44 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
 
     if (warp == 0) {
         // ================================ TMA producer (both CTAs) =====================
-        if (lane == 0) {
-            const uint32_t full_leader = mapa_u32(full_bar, 0);
-            const uint32_t afull_leader = mapa_u32(afull_bar, 0);
-            int stage = 0;
-            uint32_t phase = 0, aphase = 0;
-            for (int w = pair; w < n_work; w += n_pairs) {
-                const int per_chunk = p.n_qblocks / 2;
-                const int chunk = w / per_chunk, qb = 2 * (w % per_chunk) + rank;
-                const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
-                const int ntiles = (int)((ce - cs + BN - 1) / BN);
-                // this CTA's 128 query rows, resident for the whole chunk
-                mbar_wait(aempty_bar, aphase ^ 1u);
-                aphase ^= 1u;
-                if (rank == 0) mbar_expect_tx(afull_bar, 2u * (uint32_t)KB * A_BYTES);
-                for (int kb = 0; kb < KB; ++kb)
+        const uint32_t full_leader = mapa_u32(full_bar, 0);
+        const uint32_t afull_leader = mapa_u32(afull_bar, 0);
+        int stage = 0;
+        uint32_t phase = 0, aphase = 0;
+        for (int w = pair; w < n_work; w += n_pairs) {
+            const int per_chunk = p.n_qblocks / 2;
+            const int chunk = w / per_chunk, qb = 2 * (w % per_chunk) + rank;
+            const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+            const int ntiles = (int)((ce - cs + BN - 1) / BN);
+            // this CTA's 128 query rows, resident for the whole chunk
+            mbar_wait(aempty_bar, aphase ^ 1u);
+            aphase ^= 1u;
+            if (elect_one()) {
+                if (rank == 0) mbar_expect_tx(afull_bar, 2u * (uint32_t)(KB + 1) * A_BYTES);
+                for (int kb = 0; kb <= KB; ++kb)  // kb == KB: the augmentation block
                     tma_load_2d_cg2(&tm_a, afull_leader, smem + kb * A_BYTES, kb * BK, qb * BM, kEvictLast);
-                // this CTA's half of every gallery tile
-                for (int t = 0; t < ntiles; ++t) {
-                    const int row0 = (int)(cs + (int64_t)t * BN) + rank * (BN / 2);
-                    for (int kb = 0; kb < KB; ++kb) {
-                        mbar_wait(&empty_bar[stage], phase ^ 1u);
+            }
+            __syncwarp();
+            // this CTA's half of every gallery tile
+            for (int t = 0; t < ntiles; ++t) {
+                const int row0 = (int)(cs + (int64_t)t * BN) + rank * (BN / 2);
+                for (int kb = 0; kb <= KB; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    if (elect_one()) {
                         if (rank == 0) mbar_expect_tx(&full_bar[stage], 2u * L::BH_BYTES);
                         tma_load_2d_cg2(&tm_b, full_leader + 8u * stage, smem + L::OFF_B + stage * L::BH_BYTES, kb * BK,
                                         row0, kEvictNormal);
-                        if (++stage == L::STAGES) {
-                            stage = 0;
-                            phase ^= 1u;
-                        }
+                    }
+                    __syncwarp();
+                    if (++stage == L::STAGES) {
+                        stage = 0;
+                        phase ^= 1u;
                     }
                 }
             }
-            // the leader's last multicast commit has landed in THIS CTA before anyone may leave
-            mbar_wait(aempty_bar, aphase ^ 1u);
         }
+        // the leader's last multicast commit has landed in THIS CTA before anyone may leave
+        mbar_wait(aempty_bar, aphase ^ 1u);
     } else if (warp == 1) {
         // ================================ MMA issuer (leader CTA) ======================
         if (rank == 0) {
@@ -590,17 +583,21 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
                     mbar_wait(&tempty_bar[as], tphase ^ 1u);
                     tc_fence_after();
                     const uint32_t tacc = tmem_base + (uint32_t)(as * BN);
-                    for (int kb = 0; kb < KB; ++kb) {
+                    for (int kb = 0; kb <= KB; ++kb) {
                         mbar_wait(&full_bar[stage], phase);
                         tc_fence_after();
-                        if (lane == 0) {
-                            const uint64_t ad = umma_desc_sw128(smem_u32(smem + kb * A_BYTES));
-                            const uint64_t bd = umma_desc_sw128(smem_u32(smem + L::OFF_B + stage * L::BH_BYTES));
+                        const uint64_t ad = umma_desc_sw128(smem_u32(smem + kb * A_BYTES));
+                        const uint64_t bd = umma_desc_sw128(smem_u32(smem + L::OFF_B + stage * L::BH_BYTES));
+                        if (elect_one()) {  // warp-uniform operands + elect.sync: no per-lane waterfall around the MMAs
+                            if (kb == KB) {  // augmentation block: one K=16 step
+                                umma_bf16_cg2(tacc, ad, bd, idesc, 1);
+                            } else {
 #pragma unroll
-                            for (int k = 0; k < BK / 16; ++k)
-                                umma_bf16_cg2(tacc, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                                for (int k = 0; k < BK / 16; ++k)
+                                    umma_bf16_cg2(tacc, ad + 2 * k, bd + 2 * k, idesc, (kb | k) != 0);
+                            }
                             umma_commit_cg2(&empty_bar[stage]);
-                            if (kb == KB - 1) {
+                            if (kb == KB) {
                                 umma_commit_cg2(&tfull_bar[as]);
                                 if (t == ntiles - 1) umma_commit_cg2(aempty_bar);  // resident A may be replaced
                             }
@@ -619,8 +616,8 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             }
         }
     } else {
-        epilogue_role<SEGMAX, true>(p, colb, colv, cols, ign, tfull_bar, tempty_bar, mapa_u32(tempty_bar, 0), tmem_base,
-                                    pair, n_pairs, n_work, rank);
+        epilogue_role<SEGMAX, true>(p, scr, ign, tfull_bar, tempty_bar, mapa_u32(tempty_bar, 0), tmem_base, pair,
+                                    n_pairs, n_work, rank);
     }
 
     __syncwarp();

@@ -11,13 +11,19 @@ static constexpr int kTileN = 256;      // gallery rows per tile (UMMA N)
 static constexpr int kCandCap = 1024;   // candidate slots per (work unit, query)
 static constexpr int kMaxIgnore = 8;    // ignore-list length per query (the reference uses 5)
 static constexpr int kMaxKPrime = 512;  // largest pre-filter list (must be <= kCandCap - kTileN)
+// Operand planes are [rows, dp + kAugCols] bf16: dp = dim padded to 64, then one 16-column
+// "augmentation" block that folds the row-norm bias of the squared-L2 score into the GEMM:
+//   gallery row: (h, m, l, 0...) with h + m + l = -|g|^2 / 2 split into three bf16 terms
+//   query row  : (1, 1, 1, 0...)
+// so the accumulator is <q,g> - |g|^2/2 = (coarse score)/2 and the epilogue needs no per-column
+// parameters at all.
+static constexpr int kAugCols = 16;
 
 struct GemmTopkParams {
     int64_t nq, n;
-    int kb_count;              // padded dim / 64
+    int kb_count;              // padded dim / 64 (full k-blocks; the augmentation block follows them)
     int n_qblocks, n_chunks;
     const int64_t *chunk_start;  // device [n_chunks+1], gallery row ranges of the chunks
-    const float2 *colparam;      // device [n]: (scale, bias) of the coarse score
     const int32_t *col_video;    // device [n] or null
     const int32_t *col_seg;      // device [n] or null (segment id per row, SEGMAX)
     const int32_t *q_ignore;     // device [nq, n_ign] or null
@@ -38,11 +44,11 @@ int launch_gemm_topk_pair(const CUtensorMap *maps2, const GemmTopkParams &p, boo
 int gemm_topk_pair_slots();  // co-resident CTA pairs on this device
 
 // ---- vq_prepare.cu ----
-// fp32 or bf16 rows [n,d] -> bf16 planes hi/lo [n,dp] (zero padded), colparam (2, -|x|^2),
-// norm2 [n]; max_norm2 (ordered-uint atomicMax target, may be null).
-int launch_prepare_rows(const void *x, int dtype, int64_t n, int d, int dp, __nv_bfloat16 *hi,
-                        __nv_bfloat16 *lo, float2 *colparam, float *norm2, uint32_t *max_norm2_bits,
-                        cudaStream_t st);
+// fp32 or bf16 rows [n,d] -> bf16 planes hi/lo [n, dp + kAugCols] (zero padded; augmentation block
+// as described above: aug_query selects the query form), norm2 [n] (may be null); max_norm2
+// (ordered-uint atomicMax target, may be null).
+int launch_prepare_rows(const void *x, int dtype, int64_t n, int d, int dp, bool aug_query, __nv_bfloat16 *hi,
+                        __nv_bfloat16 *lo, float *norm2, uint32_t *max_norm2_bits, cudaStream_t st);
 int launch_pool_normalize(const float *x, int64_t B, int C, int T, float *out, cudaStream_t st);
 
 // ---- vq_exact.cu ----

@@ -1,7 +1,7 @@
 // vq_prepare.cu -- index-build side kernels (a1, a2).
 //   prepare_rows : embedding rows -> bf16 operand planes for the tensor-core pre-filter
 //                  (hi = bf16(x), lo = bf16(x - hi), zero padded to a multiple of 64 columns),
-//                  per-row |x|^2 and the coarse-score column parameters (2, -|x|^2).
+//                  per-row |x|^2, and the augmentation block that carries -|x|^2/2 into the GEMM.
 //                  Replaces the list->concat->index.add of dataloader_baseline.py:1502-1510.
 //   pool_normalize: F.normalize(p=2,dim=1) per time step (main.py:232) + temporal mean
 //                  (dataloader_baseline.py:1481), canonical arithmetic (see oracle).
@@ -20,17 +20,16 @@ __device__ __forceinline__ float ldf<__nv_bfloat16>(const __nv_bfloat16 *p) { re
 // one warp per row; 8 rows per 256-thread block
 template <typename T>
 __global__ void __launch_bounds__(256) prepare_rows_kernel(const T *__restrict__ x, int64_t n, int d, int dp,
-                                                           __nv_bfloat16 *__restrict__ hi,
+                                                           int aug_query, __nv_bfloat16 *__restrict__ hi,
                                                            __nv_bfloat16 *__restrict__ lo,
-                                                           float2 *__restrict__ colparam,
-                                                           float *__restrict__ norm2,
-                                                           uint32_t *max_bits) {
+                                                           float *__restrict__ norm2, uint32_t *max_bits) {
     const int lane = threadIdx.x & 31;
     const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= n) return;
+    const int pitch = dp + kAugCols;
     const T *xr = x + row * d;
-    __nv_bfloat16 *hr = hi + row * dp;
-    __nv_bfloat16 *lr = lo ? lo + row * dp : nullptr;
+    __nv_bfloat16 *hr = hi + row * pitch;
+    __nv_bfloat16 *lr = lo ? lo + row * pitch : nullptr;
     float acc = 0.f;
     for (int c = lane * 2; c < dp; c += 64) {
         float v0 = c < d ? ldf(xr + c) : 0.f;
@@ -47,23 +46,42 @@ __global__ void __launch_bounds__(256) prepare_rows_kernel(const T *__restrict__
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    // augmentation block (kernels.h): lanes 0..7 write two columns each
+    if (lane < kAugCols / 2) {
+        __nv_bfloat16 a0 = __float2bfloat16_rn(0.f), a1 = a0;
+        if (lane < 2) {
+            if (aug_query) {
+                a0 = __float2bfloat16_rn(1.f);
+                a1 = lane == 0 ? a0 : a1;
+            } else {
+                const float b = -0.5f * acc;  // exact scaling
+                const __nv_bfloat16 bh = __float2bfloat16_rn(b);
+                const float r1 = b - __bfloat162float(bh);  // exact (Sterbenz-like: bh is b's leading bits)
+                const __nv_bfloat16 bm = __float2bfloat16_rn(r1);
+                const __nv_bfloat16 bl = __float2bfloat16_rn(r1 - __bfloat162float(bm));
+                a0 = lane == 0 ? bh : bl;
+                a1 = lane == 0 ? bm : a1;
+            }
+        }
+        *reinterpret_cast<__nv_bfloat162 *>(hr + dp + lane * 2) = __nv_bfloat162(a0, a1);
+        if (lr) *reinterpret_cast<__nv_bfloat162 *>(lr + dp + lane * 2) = __nv_bfloat162(__float2bfloat16_rn(0.f), __float2bfloat16_rn(0.f));
+    }
     if (lane == 0) {
         if (norm2) norm2[row] = acc;
-        if (colparam) colparam[row] = make_float2(2.0f, -acc);
         if (max_bits) atomicMax(max_bits, __float_as_uint(acc));  // acc >= 0: bit order == value order
     }
 }
 
-int launch_prepare_rows(const void *x, int dtype, int64_t n, int d, int dp, __nv_bfloat16 *hi,
-                        __nv_bfloat16 *lo, float2 *colparam, float *norm2, uint32_t *max_bits,
-                        cudaStream_t st) {
+int launch_prepare_rows(const void *x, int dtype, int64_t n, int d, int dp, bool aug_query, __nv_bfloat16 *hi,
+                        __nv_bfloat16 *lo, float *norm2, uint32_t *max_bits, cudaStream_t st) {
     if (n == 0) return VQ_OK;
     unsigned grid = (unsigned)((n + 7) / 8);
     if (dtype == VQ_F32)
-        prepare_rows_kernel<float><<<grid, 256, 0, st>>>((const float *)x, n, d, dp, hi, lo, colparam, norm2, max_bits);
+        prepare_rows_kernel<float><<<grid, 256, 0, st>>>((const float *)x, n, d, dp, aug_query ? 1 : 0, hi, lo, norm2,
+                                                          max_bits);
     else
-        prepare_rows_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)x, n, d, dp, hi, lo,
-                                                                  colparam, norm2, max_bits);
+        prepare_rows_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)x, n, d, dp, aug_query ? 1 : 0,
+                                                                  hi, lo, norm2, max_bits);
     VQ_CUDA(cudaGetLastError());
     return VQ_OK;
 }
