@@ -56,8 +56,10 @@ def merge_gathered(D, I, group=None, merge=None):
     import torch
     import torch.distributed as dist
     ws = dist.get_world_size(group)
-    gD = torch.empty((ws,) + tuple(D.shape), dtype=D.dtype, device=D.device)
-    gI = torch.empty((ws,) + tuple(I.shape), dtype=I.dtype, device=I.device)
+    nq, k = D.shape
+    # rank-major concatenation along dim 0 (the layout both NCCL and gloo accept), viewed [ws, nq, k]
+    gD = torch.empty((ws * nq, k), dtype=D.dtype, device=D.device)
+    gI = torch.empty((ws * nq, k), dtype=I.dtype, device=I.device)
     dist.all_gather_into_tensor(gD, D.contiguous(), group=group)
     dist.all_gather_into_tensor(gI, I.contiguous(), group=group)
-    return (merge or topk_merge)(gD, gI)
+    return (merge or topk_merge)(gD.view(ws, nq, k), gI.view(ws, nq, k))
