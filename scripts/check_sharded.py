@@ -1,0 +1,35 @@
+"""torchrun --nproc-per-node G scripts/check_sharded.py : row-sharded search (one NCCL all-gather +
+merge) must equal the single-index search bit for bit, duplicates across shards included."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+import bench
+import vqwild_b200 as vq
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+n, nq, d, k = 400_003, 3000, 512, 100
+g = bench.gen_rows(torch, "g", 0, n, d, dev)
+g[n - 5] = g[17]                      # duplicate rows on different shards: tie -> lowest global row
+xq = bench.gen_rows(torch, "q", 0, nq, d, dev)
+xq[0] = g[17]
+r0, r1 = rank * n // world, (rank + 1) * n // world
+shard = vq.IndexFlatL2(d)
+shard.add(g[r0:r1].contiguous())
+D, I = vq.sharded_search(shard, xq, k, r0)
+full = vq.IndexFlatL2(d)
+full.add(g)
+Df, If = full.search(xq, k)
+ok = torch.equal(I, If) and torch.equal(D.view(torch.int32), Df.view(torch.int32))
+flag = torch.tensor([1 if ok else 0], device=dev)
+dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+if rank == 0:
+    print("sharded == single-index on %d ranks: %s (I[0,:3]=%s)" % (world, bool(flag.item()), I[0, :3].tolist()))
+dist.destroy_process_group()
+sys.exit(0 if flag.item() else 1)
