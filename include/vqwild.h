@@ -103,7 +103,7 @@ VQ_API int vq_index_search_segmax(vq_index *ix, const void *xq, int64_t nq, int 
 
 /* Statistics of the last search on this index (host ints): [0] queries that needed the exact
  * fallback, [1] tensor-core tiles issued, [2] candidate slots per query, [3] work units,
- * [4] gallery chunks, [5] kernels launched by the call. */
+ * [4] gallery segments (stream-K pieces of the query-group x gallery space), [5] kernels launched. */
 VQ_API int vq_index_last_stats(const vq_index *ix, int64_t *out6);
 /* Device time (ms, CUDA events on the caller's stream) of the phases of the last tensor-core
  * search on this index: [0] query operand preparation, [1] the tcgen05 GEMM + streaming

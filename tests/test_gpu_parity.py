@@ -57,6 +57,41 @@ def test_search_matches_oracle(vq, prec):
     assert I[0, 0] == 45 and I[0, 1] == 123 and D[0, 0] == 0.0
 
 
+@pytest.mark.parametrize("nq,n,d,k,bf16", [(130, 300_000, 64, 10, True), (130, 200_000, 64, 100, False),
+                                            (1000, 60_000, 128, 50, True), (20, 2_100, 64, 5, True)])
+def test_search_streamk_segments(vq, nq, n, d, k, bf16):
+    """Stream-K decomposition: few query groups against a long gallery are cut into many segments
+    per group (one candidate list each, merged by the select kernel); duplicates straddle cuts."""
+    import torch
+    rng = np.random.default_rng(11)
+    g = _emb(rng, n, d)
+    q = _emb(rng, nq, d)
+    if bf16:
+        g = torch.from_numpy(g).to(torch.bfloat16).float().numpy()
+        q = torch.from_numpy(q).to(torch.bfloat16).float().numpy()
+    for a, b in [(5, n - 7), (n // 2 - 1, n // 2 + 300), (1000, 1999)]:
+        g[b] = g[a]
+    q[1] = g[5]
+    q[2] = g[n // 2 - 1]
+    ix = vq.IndexFlatL2(d)
+    if bf16:
+        ix.add(torch.from_numpy(g).to(torch.bfloat16).cuda())
+        D, I = ix.search(torch.from_numpy(q).to(torch.bfloat16).cuda(), k)
+        D, I = D.cpu().numpy(), I.cpu().numpy()
+    else:
+        ix.add(g)
+        D, I = ix.search(q, k)
+    st = ix.last_stats()
+    print(st)
+    Do, Io = orc.search(q, g, k)
+    assert np.array_equal(I, Io)
+    assert np.array_equal(D.view(np.uint32), Do.view(np.uint32))
+    assert I[1, 0] == 5 and I[1, 1] == n - 7
+    if n >= 100_000:
+        assert st["segments"] > st["work_units"] // 2 or st["segments"] >= 32  # the groups really were cut
+        assert st["fallback_queries"] == 0
+
+
 def test_search_scores_within_fp64_tolerance(vq):
     rng = np.random.default_rng(11)
     q, g = _emb(rng, 64, 512), _emb(rng, 3000, 512)

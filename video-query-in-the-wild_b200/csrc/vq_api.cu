@@ -183,8 +183,10 @@ struct vq_index {
     int32_t *cand_cnt = nullptr;
     float *cand_tau = nullptr;
     size_t cand_units = 0;
-    int64_t *chunk_start_dev = nullptr;
-    size_t chunk_cap = 0;
+    int64_t *plan_rows_dev = nullptr;  // segment plan of the last search (GemmTopkParams)
+    size_t plan_rows_cap = 0;
+    int32_t *plan_ints_dev = nullptr;
+    size_t plan_ints_cap = 0;
     int32_t *unproven = nullptr;
     size_t unproven_cap = 0;
     int32_t *unproven_count = nullptr;
@@ -241,7 +243,7 @@ int vq_index_destroy(vq_index *ix) {
     cudaDeviceSynchronize();
     void *ptrs[] = {ix->raw,   ix->hi,         ix->lo,           ix->norm2,    ix->gmax_bits,
                     ix->label, ix->video,      ix->seg_of_row,   ix->seg_start_dev, ix->cand,     ix->cand_cnt,
-                    ix->cand_tau, ix->chunk_start_dev, ix->unproven, ix->unproven_count};
+                    ix->cand_tau, ix->plan_rows_dev, ix->plan_ints_dev, ix->unproven, ix->unproven_count};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (ix->stat_pinned) cudaFreeHost(ix->stat_pinned);

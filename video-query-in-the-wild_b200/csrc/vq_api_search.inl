@@ -26,35 +26,75 @@ static void error_model(int prec, int dtype, int dp, float *eps_rel, float *eps_
     if (getenv("VQ_DEBUG_FORCE_FALLBACK")) *eps_abs = 1e30f;  // test hook: no query can be proven
 }
 
-// Split the gallery into chunks so that (query blocks x chunks) fills the SMs evenly.
-// `nqb` work items per chunk (query blocks, or pairs of them) are spread over `sms` slots.
-static void plan_chunks(const vq_index *ix, int64_t nqb, int sms, int kprime, bool segmax, std::vector<int64_t> *cs) {
+// Work plan (vq_kernels.h, GemmTopkParams).  The gallery is cut into `n_chunks` row ranges so that
+// (query groups x chunks) fills the persistent CTAs evenly; segment (chunk, group) goes to CTA
+// (chunk * n_groups + group) mod n_cta, i.e. the CTAs sweep a chunk TOGETHER (every gallery tile is
+// fetched from HBM once per wave and shared through L2).  Segment (chunk, g) names (chunk-1, g) as
+// its predecessor: its threshold starts from the predecessor's final one when that is already
+// known, so only the first chunk of a group pays the threshold warm-up.
+struct SegPlan {
+    std::vector<int64_t> rows;  // seg_begin[nseg] | seg_end[nseg]
+    std::vector<int32_t> ints;  // seg_group[nseg] | cta_seg_start[n_cta+1] | seg_pred[nseg] | group_segs[n_groups*n_chunks]
+    int nseg = 0, n_cta = 0, n_chunks = 0;
+};
+
+static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int kprime, bool segmax, SegPlan *pl) {
     const int64_t n = ix->n;
     const int64_t ntiles = (n + kTileN - 1) / kTileN;
-    int64_t max_chunks = std::min<int64_t>(ntiles, (int64_t)(128 * 64) / kprime);
-    max_chunks = std::min<int64_t>(max_chunks, std::max<int64_t>(1, ntiles / 8));  // >= 8 tiles per chunk
+    int64_t max_chunks = std::min<int64_t>(ntiles, (int64_t)(128 * 64) / kprime);  // select's gather capacity
+    max_chunks = std::min<int64_t>(max_chunks, std::max<int64_t>(1, ntiles / 8));   // >= 8 tiles per chunk
     max_chunks = std::max<int64_t>(1, std::min<int64_t>(max_chunks, 64));
     int64_t best = 1;
     double best_eff = -1.0;
     for (int64_t c = 1; c <= max_chunks; ++c) {
-        const int64_t units = nqb * c;
-        const double eff = (double)units / (double)(((units + sms - 1) / sms) * sms);
-        if (eff > best_eff + 0.02) {
+        const int64_t units = n_groups * c;
+        const double eff = (double)units / (double)(((units + slots - 1) / slots) * slots);
+        if (eff > best_eff + 0.01) {
             best_eff = eff;
             best = c;
         }
     }
-    cs->clear();
-    cs->push_back(0);
+    std::vector<int64_t> cs{0};
     for (int64_t c = 1; c < best; ++c) {
         int64_t target = (ntiles * c / best) * kTileN;
-        if (segmax) {  // move to the next video boundary
+        if (segmax) {  // a video's moments stay in one chunk
             auto it = std::lower_bound(ix->seg_start.begin(), ix->seg_start.end(), target);
             target = it == ix->seg_start.end() ? n : *it;
         }
-        if (target > cs->back() && target < n) cs->push_back(target);
+        if (target > cs.back() && target < n) cs.push_back(target);
     }
-    cs->push_back(n);
+    cs.push_back(n);
+    const int64_t n_chunks = (int64_t)cs.size() - 1;
+    const int64_t units = n_groups * n_chunks;
+    const int64_t P = std::max<int64_t>(1, std::min<int64_t>(slots, units));
+    // segment ids in CTA-major order
+    std::vector<int32_t> s_of_u((size_t)units), cta((size_t)P + 1);
+    std::vector<int64_t> sb((size_t)units), se((size_t)units);
+    std::vector<int32_t> sg((size_t)units), pred((size_t)units), gsegs((size_t)units);
+    int32_t sid = 0;
+    for (int64_t c = 0; c < P; ++c) {
+        cta[(size_t)c] = sid;
+        for (int64_t u = c; u < units; u += P) s_of_u[(size_t)u] = sid++;
+    }
+    cta[(size_t)P] = sid;
+    for (int64_t u = 0; u < units; ++u) {
+        const int64_t chunk = u / n_groups, g = u % n_groups;
+        const int32_t s_ = s_of_u[(size_t)u];
+        sb[(size_t)s_] = cs[(size_t)chunk];
+        se[(size_t)s_] = cs[(size_t)chunk + 1];
+        sg[(size_t)s_] = (int32_t)g;
+        pred[(size_t)s_] = (chunk > 0 && !getenv("VQ_DEBUG_NO_CHAIN")) ? s_of_u[(size_t)(u - n_groups)] : -1;  // A/B hook
+        gsegs[(size_t)(g * n_chunks + chunk)] = s_;
+    }
+    pl->nseg = (int)units;
+    pl->n_cta = (int)P;
+    pl->n_chunks = (int)n_chunks;
+    pl->rows = sb;
+    pl->rows.insert(pl->rows.end(), se.begin(), se.end());
+    pl->ints = sg;
+    pl->ints.insert(pl->ints.end(), cta.begin(), cta.end());
+    pl->ints.insert(pl->ints.end(), pred.begin(), pred.end());
+    pl->ints.insert(pl->ints.end(), gsegs.begin(), gsegs.end());
 }
 
 template <typename T>
@@ -120,13 +160,16 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     // work decomposition (pair path: query blocks padded to an even count, the pad block is all out of range)
     int n_qblocks = (int)((nq + kTileM - 1) / kTileM);
     if (pair) n_qblocks = (n_qblocks + 1) / 2 * 2;
+    const int group_size = pair ? 2 : 1;
+    const int n_groups = n_qblocks / group_size;
     const int slots = pair ? gemm_topk_pair_slots() : sm_count();
-    std::vector<int64_t> cs;
-    plan_chunks(ix, pair ? n_qblocks / 2 : n_qblocks, slots, kprime, segmax, &cs);
-    const int n_chunks = (int)cs.size() - 1;
-    const size_t units = (size_t)n_chunks * n_qblocks;
-    VQ_TRY(ensure(&ix->chunk_start_dev, &ix->chunk_cap, cs.size()));
-    VQ_CUDA(cudaMemcpyAsync(ix->chunk_start_dev, cs.data(), cs.size() * 8, cudaMemcpyHostToDevice, st));
+    SegPlan pl;
+    plan_segments(ix, n_groups, slots, kprime, segmax, &pl);
+    const size_t units = (size_t)pl.nseg * group_size;
+    VQ_TRY(ensure(&ix->plan_rows_dev, &ix->plan_rows_cap, pl.rows.size()));
+    VQ_TRY(ensure(&ix->plan_ints_dev, &ix->plan_ints_cap, pl.ints.size()));
+    VQ_CUDA(cudaMemcpyAsync(ix->plan_rows_dev, pl.rows.data(), pl.rows.size() * 8, cudaMemcpyHostToDevice, st));
+    VQ_CUDA(cudaMemcpyAsync(ix->plan_ints_dev, pl.ints.data(), pl.ints.size() * 4, cudaMemcpyHostToDevice, st));
     VQ_TRY(ensure(&ix->cand, &ix->cand_bytes, units * kTileM * kCandCap));
     if (ix->cand_units < units) {
         if (ix->cand_cnt) { VQ_CUDA(cudaDeviceSynchronize()); cudaFree(ix->cand_cnt); cudaFree(ix->cand_tau); }
@@ -137,24 +180,31 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     VQ_TRY(ensure(&ix->unproven, &ix->unproven_cap, (size_t)nq));
 
     GemmTopkParams gp{};
-    gp.nq = nq; gp.n = ix->n; gp.kb_count = ix->dp / 64; gp.n_qblocks = n_qblocks; gp.n_chunks = n_chunks;
-    gp.chunk_start = ix->chunk_start_dev;
+    gp.nq = nq; gp.n = ix->n; gp.kb_count = ix->dp / 64; gp.n_qblocks = n_qblocks; gp.n_seg = pl.nseg;
+    gp.seg_begin = ix->plan_rows_dev; gp.seg_end = ix->plan_rows_dev + pl.nseg;
+    gp.seg_group = ix->plan_ints_dev; gp.cta_seg_start = ix->plan_ints_dev + pl.nseg;
+    gp.seg_pred = ix->plan_ints_dev + pl.nseg + pl.n_cta + 1;
+    // 0xff.. = NaN = "threshold of this unit not final yet" (read by successor segments)
+    VQ_CUDA(cudaMemsetAsync(ix->cand_tau, 0xff, units * kTileM * 4, st));
     gp.col_video = n_ign > 0 ? ix->video : nullptr;
     gp.col_seg = segmax ? ix->seg_of_row : nullptr;
     gp.q_ignore = n_ign > 0 ? ign : nullptr; gp.n_ign = n_ign; gp.kprime = kprime;
+    gp.dense_rows = 8;  // measured: 8 beats 4 and "never" (scripts/ab_gemm.py, profiles/r01_ab_gemm_chain_dense.txt)
+    if (const char *e = getenv("VQ_DEBUG_DENSE_ROWS")) gp.dense_rows = atoi(e);  // A/B hook (33 = never)
     gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau;
     VQ_CUDA(cudaEventRecord(ix->ev[1], st));
     if (pair) {
-        VQ_TRY(launch_gemm_topk_pair(maps, gp, segmax, (int)std::min<size_t>(units / 2, (size_t)slots), st));
+        VQ_TRY(launch_gemm_topk_pair(maps, gp, segmax, pl.n_cta, st));
     } else {
-        VQ_TRY(launch_gemm_topk(maps, gp, split ? 3 : 1, segmax, (int)std::min<size_t>(units, (size_t)slots), st));
+        VQ_TRY(launch_gemm_topk(maps, gp, split ? 3 : 1, segmax, pl.n_cta, st));
     }
     VQ_CUDA(cudaEventRecord(ix->ev[2], st));
     ++launches;
 
     SelectParams sp{};
     sp.nq = nq; sp.n = ix->n; sp.d = ix->d; sp.dtype = dtype; sp.q = xq; sp.g = ix->raw;
-    sp.n_qblocks = n_qblocks; sp.n_chunks = n_chunks; sp.cand = ix->cand; sp.cand_cnt = ix->cand_cnt;
+    sp.group_size = group_size; sp.group_segs = ix->plan_ints_dev + 2 * pl.nseg + pl.n_cta + 1;
+    sp.segs_per_group = pl.n_chunks; sp.cand = ix->cand; sp.cand_cnt = ix->cand_cnt;
     sp.cand_tau = ix->cand_tau; sp.kprime = kprime; sp.k = k;
     error_model(prec, ix->dtype, ix->dp, &sp.eps_rel, &sp.eps_abs);
     sp.gmax_norm2_bits = ix->gmax_bits;
@@ -180,11 +230,11 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     ++launches;
 
     int64_t tiles = 0;
-    for (int c = 0; c < n_chunks; ++c) tiles += (cs[c + 1] - cs[c] + kTileN - 1) / kTileN;
-    ix->stats[1] = tiles * n_qblocks;
+    for (int c = 0; c < pl.nseg; ++c) tiles += (pl.rows[(size_t)pl.nseg + c] - pl.rows[(size_t)c] + kTileN - 1) / kTileN;
+    ix->stats[1] = tiles * group_size;
     ix->stats[2] = kprime;
     ix->stats[3] = (int64_t)units;
-    ix->stats[4] = n_chunks;
+    ix->stats[4] = pl.nseg;
     ix->stats[5] = launches;
     return VQ_OK;
 }

@@ -134,7 +134,7 @@ __device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, i
 }
 
 // ---------------------------------------------------------------------------------------------
-// Epilogue role (warps 2-5 of either kernel).  Work items w = w0, w0 + w_stride, ... < n_work.
+// Epilogue role (warps 2-5 of either kernel).  Segments [s0, s1) of this CTA (pair).
 // Thread = accumulator row = query.  Per 32 columns: tcgen05.ld, max of the 32 values, ONE compare
 // against the row's threshold.  Rows that hold a candidate are handled by the whole warp: the
 // row's values are transposed through shared memory so that lane i tests column i, and the hits
@@ -143,7 +143,7 @@ __device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, i
 template <bool SEGMAX, bool PAIR>
 __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *scr, int *ign, uint64_t *tfull_bar,
                                               uint64_t *tempty_bar, uint32_t tempty_leader, uint32_t tmem_base,
-                                              int w0, int w_stride, int n_work, int rank) {
+                                              int s0, int s1, int rank) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int quarter = warp & 3;            // TMEM lane quarter this warp may read
     const int row = quarter * 32 + lane;     // accumulator row == query row in the block
@@ -152,13 +152,12 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
     float *wscr = scr + quarter * 32;
     int as = 0;
     uint32_t aphase = 0;
-    for (int w = w0; w < n_work; w += w_stride) {
-        // PAIR: work item = (chunk, pair of query blocks), this CTA takes block 2*pair + rank
-        const int per_chunk = PAIR ? p.n_qblocks / 2 : p.n_qblocks;
-        const int chunk = w / per_chunk;
-        const int qb = PAIR ? 2 * (w % per_chunk) + rank : w % per_chunk;
-        const int u = chunk * p.n_qblocks + qb;
-        const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+    for (int sg_i = s0; sg_i < s1; ++sg_i) {
+        // PAIR: segment of a pair of query blocks, this CTA takes block 2*group + rank
+        const int grp = p.seg_group[sg_i];
+        const int qb = PAIR ? 2 * grp + rank : grp;
+        const int u = PAIR ? 2 * sg_i + rank : sg_i;
+        const int64_t cs = p.seg_begin[sg_i], ce = p.seg_end[sg_i];
         const int ntiles = (int)((ce - cs + BN - 1) / BN);
         const int64_t q = (int64_t)qb * BM + row;
         const bool qvalid = q < p.nq;
@@ -166,7 +165,16 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
         uint64_t *wbuf = p.cand + ((int64_t)u * BM + quarter * 32) * kCandCap;
         // tau: everything discarded so far has coarse score <= tau; tauh = tau / 2 is what the
         // accumulator (= score / 2) is compared with
-        float tau = qvalid ? -INFINITY : INFINITY, tauh = tau;
+        float tau = qvalid ? -INFINITY : INFINITY;
+        {   // start from the predecessor segment's final threshold if it has been published (NaN = not yet):
+            // everything it discarded or still lists below its k'-th entry is <= that value
+            const int pr = p.seg_pred[sg_i];
+            if (pr >= 0 && qvalid) {
+                const float t0 = *(const volatile float *)(p.cand_tau + ((int64_t)(PAIR ? 2 * pr + rank : pr) * BM + row));
+                if (t0 == t0) tau = t0;
+            }
+        }
+        float tauh = 0.5f * tau;
         int cnt = 0;
         // group-max state (SEGMAX), in accumulator (half-score) units
         int cur_seg = -2;
@@ -279,7 +287,23 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                     if (need) compact_rows(need, keep_max);
                 } else {
                     uint32_t bal = __ballot_sync(0xffffffffu, m32 > tauh);
-                    if (bal) {  // warp-uniform; rare once tau has warmed up
+                    if (__popc(bal) >= p.dense_rows) {
+                        // threshold warm-up (start of a segment): most rows hold candidates, so every
+                        // thread scans its own 32 values instead of serialising the rows through the warp
+                        if (m32 > tauh) {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i) {
+                                if (v[i] > tauh) {
+                                    const uint32_t j = jbase + (uint32_t)(ch * 32 + i);
+                                    bool ok = true;
+                                    if (p.n_ign > 0) ok = !is_ignored(row, __ldg(p.col_video + j));
+                                    if (ok) append(2.0f * v[i], j);
+                                }
+                            }
+                        }
+                        const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
+                        if (need) compact_rows(need, keep_max);
+                    } else if (bal) {  // warp-uniform; rare once tau has warmed up
                         while (bal) {
                             const int L = __ffs(bal) - 1;
                             bal &= bal - 1;
@@ -340,7 +364,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
     uint32_t *tmem_slot = (uint32_t *)(smem + L::OFF_TMEM);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int n_units = p.n_chunks * p.n_qblocks;
+    const int seg0 = p.cta_seg_start[blockIdx.x], seg1 = p.cta_seg_start[blockIdx.x + 1];
     const int KB = p.kb_count;
 
     if (warp == 0 && lane == 0) {
@@ -375,9 +399,9 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
         // uniform registers); one elected lane issues.
         int stage = 0;
         uint32_t phase = 0;
-        for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-            const int chunk = u / p.n_qblocks, qb = u % p.n_qblocks;
-            const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+        for (int sg_i = seg0; sg_i < seg1; ++sg_i) {
+            const int qb = p.seg_group[sg_i];
+            const int64_t cs = p.seg_begin[sg_i], ce = p.seg_end[sg_i];
             const int ntiles = (int)((ce - cs + BN - 1) / BN);
             const int q0 = qb * BM;
             for (int t = 0; t < ntiles; ++t) {
@@ -411,9 +435,8 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
         uint32_t phase = 0;
         int as = 0;
         uint32_t aphase = 0;
-        for (int u = blockIdx.x; u < n_units; u += gridDim.x) {
-            const int chunk = u / p.n_qblocks;
-            const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+        for (int sg_i = seg0; sg_i < seg1; ++sg_i) {
+            const int64_t cs = p.seg_begin[sg_i], ce = p.seg_end[sg_i];
             const int ntiles = (int)((ce - cs + BN - 1) / BN);
             for (int t = 0; t < ntiles; ++t) {
                 mbar_wait(&tempty_bar[as], aphase ^ 1u);
@@ -459,8 +482,7 @@ gemm_topk_kernel(const __grid_constant__ CUtensorMap tm_a_hi, const __grid_const
             }
         }
     } else {
-        epilogue_role<SEGMAX, false>(p, scr, ign, tfull_bar, tempty_bar, 0u, tmem_base, (int)blockIdx.x,
-                                     (int)gridDim.x, n_units, 0);
+        epilogue_role<SEGMAX, false>(p, scr, ign, tfull_bar, tempty_bar, 0u, tmem_base, seg0, seg1, 0);
     }
 
     tc_fence_before();
@@ -496,8 +518,8 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int rank = (int)cluster_ctarank();
-    const int pair = (int)blockIdx.x >> 1, n_pairs = (int)gridDim.x >> 1;
-    const int n_work = p.n_chunks * (p.n_qblocks / 2);
+    const int pair = (int)blockIdx.x >> 1;
+    const int seg0 = p.cta_seg_start[pair], seg1 = p.cta_seg_start[pair + 1];
     const int KB = p.kb_count;
 
     if (warp == 0 && lane == 0) {
@@ -530,12 +552,11 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
         const uint32_t afull_leader = mapa_u32(afull_bar, 0);
         int stage = 0;
         uint32_t phase = 0, aphase = 0;
-        for (int w = pair; w < n_work; w += n_pairs) {
-            const int per_chunk = p.n_qblocks / 2;
-            const int chunk = w / per_chunk, qb = 2 * (w % per_chunk) + rank;
-            const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+        for (int sg_i = seg0; sg_i < seg1; ++sg_i) {
+            const int qb = 2 * p.seg_group[sg_i] + rank;
+            const int64_t cs = p.seg_begin[sg_i], ce = p.seg_end[sg_i];
             const int ntiles = (int)((ce - cs + BN - 1) / BN);
-            // this CTA's 128 query rows, resident for the whole chunk
+            // this CTA's 128 query rows, resident for the whole segment
             mbar_wait(aempty_bar, aphase ^ 1u);
             aphase ^= 1u;
             if (elect_one()) {
@@ -572,9 +593,8 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             uint32_t phase = 0, aphase = 0;
             int as = 0;
             uint32_t tphase = 0;
-            for (int w = pair; w < n_work; w += n_pairs) {
-                const int chunk = w / (p.n_qblocks / 2);
-                const int64_t cs = p.chunk_start[chunk], ce = p.chunk_start[chunk + 1];
+            for (int sg_i = seg0; sg_i < seg1; ++sg_i) {
+                const int64_t cs = p.seg_begin[sg_i], ce = p.seg_end[sg_i];
                 const int ntiles = (int)((ce - cs + BN - 1) / BN);
                 mbar_wait(afull_bar, aphase);
                 aphase ^= 1u;
@@ -616,8 +636,8 @@ gemm_topk_pair_kernel(const __grid_constant__ CUtensorMap tm_a, const __grid_con
             }
         }
     } else {
-        epilogue_role<SEGMAX, true>(p, scr, ign, tfull_bar, tempty_bar, mapa_u32(tempty_bar, 0), tmem_base, pair,
-                                    n_pairs, n_work, rank);
+        epilogue_role<SEGMAX, true>(p, scr, ign, tfull_bar, tempty_bar, mapa_u32(tempty_bar, 0), tmem_base, seg0,
+                                    seg1, rank);
     }
 
     __syncwarp();

@@ -19,19 +19,31 @@ static constexpr int kMaxKPrime = 512;  // largest pre-filter list (must be <= k
 // parameters at all.
 static constexpr int kAugCols = 16;
 
+// Work decomposition: the gallery is cut into chunks (row ranges); a SEGMENT is one chunk of one
+// query group (a 128-query block, or a pair of them for the CTA-pair kernel) and streams into its own
+// candidate lists.  Each persistent CTA (pair) owns a contiguous run of the segment array; the host
+// orders that array so that the CTAs sweep a chunk together (L2 sharing of the gallery tiles).
+// seg_pred: the segment of the same group on the previous chunk (or -1): a segment starts from its
+// predecessor's final threshold when that has already been published, skipping the warm-up.
 struct GemmTopkParams {
     int64_t nq, n;
     int kb_count;              // padded dim / 64 (full k-blocks; the augmentation block follows them)
-    int n_qblocks, n_chunks;
-    const int64_t *chunk_start;  // device [n_chunks+1], gallery row ranges of the chunks
+    int n_qblocks;             // 128-query blocks (even for the pair kernel)
+    int n_seg;
+    const int64_t *seg_begin, *seg_end;  // device [n_seg] gallery rows of each segment
+    const int32_t *seg_group;            // device [n_seg] query group of each segment
+    const int32_t *cta_seg_start;        // device [n_cta+1] segments [cta_seg_start[c], cta_seg_start[c+1]) belong to CTA (pair) c
+    const int32_t *seg_pred;             // device [n_seg] predecessor segment or -1
     const int32_t *col_video;    // device [n] or null
     const int32_t *col_seg;      // device [n] or null (segment id per row, SEGMAX)
     const int32_t *q_ignore;     // device [nq, n_ign] or null
     int n_ign;
     int kprime;
+    int dense_rows;  // rows of a warp with candidates in one 32-column step from which every thread scans its own row
+    // unit = (segment, query block inside the group): u = seg * group_size + member
     uint64_t *cand;   // [units][kTileM][kCandCap] keys (ordered coarse score << 32 | ~row)
     int32_t *cand_cnt;  // [units][kTileM]
-    float *cand_tau;    // [units][kTileM] everything not listed has coarse score <= tau
+    float *cand_tau;    // [units][kTileM] everything not listed has coarse score <= tau (NaN until the unit is done)
 };
 
 int launch_gemm_topk(const CUtensorMap *maps4, const GemmTopkParams &p, int npass, bool segmax,
@@ -61,7 +73,9 @@ struct SelectParams {
     int d;
     int dtype;           // element type of q/g (VQ_F32 / VQ_BF16)
     const void *q, *g;   // original rows (canonical re-scoring reads these)
-    int n_qblocks, n_chunks;
+    int group_size;                  // query blocks per group (2 for the pair kernel)
+    const int32_t *group_segs;       // device [n_groups][segs_per_group]: segment ids of group g
+    int segs_per_group;
     const uint64_t *cand;
     const int32_t *cand_cnt;
     const float *cand_tau;

@@ -1,7 +1,7 @@
 // vq_select.cu -- second half of kernel (2): turns the pre-filter candidates of
 // vq_gemm_topk.cu into the exact answer.
 //   per query (one 128-thread block):
-//     1. gather the <= k' coarse keys of every gallery chunk, keep the k' best (bisection select)
+//     1. gather the <= k' coarse keys of every gallery segment of the query's group, keep the k' best (bisection select)
 //     2. re-score the survivors with the canonical fp32 chain (oracle-identical bits); in
 //        segment-max mode re-score every moment of each surviving video and take its exact best
 //     3. bitonic-sort by (d2 asc, row asc)  -> the reference's ranked order
@@ -19,24 +19,27 @@ static constexpr int kSelThreads = 128;
 template <typename T, bool SEGMAX>
 __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams p) {
     extern __shared__ __align__(16) uint8_t sm[];
-    const int E = p.n_chunks * p.kprime;
     const int ksort = next_pow2(p.kprime);
-    uint64_t *keys = (uint64_t *)sm;                     // [E] coarse keys
-    uint64_t *ex = keys + E;                             // [ksort] exact keys
+    uint64_t *keys = (uint64_t *)sm;                     // [segs_per_group * k'] coarse keys
+    uint64_t *ex = keys + p.segs_per_group * p.kprime;  // [ksort] exact keys
     uint32_t *aux = (uint32_t *)(ex + ksort);            // [ksort] segmax: video per exact key slot
     float *qs = (float *)(aux + ksort);                  // [d]
     int *scratch = (int *)(qs + p.d);                    // [40]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t q = blockIdx.x;
     const int qb = (int)(q / kTileM), r = (int)(q % kTileM);
+    const int grp = qb / p.group_size, member = qb % p.group_size;
+    const int32_t *segs = p.group_segs + (int64_t)grp * p.segs_per_group;  // this query's segments
+    const int nsg = p.segs_per_group;
+    const int E = nsg * p.kprime;
     const T *qrow = (const T *)p.q + q * p.d;
 
     // ---- 1. gather ----
     for (int i = tid; i < p.d; i += kSelThreads) qs[i] = to_f32<T>(qrow[i]);
     float tau = -INFINITY;
     int total = 0;
-    for (int c = 0; c < p.n_chunks; ++c) {
-        const int64_t ur = ((int64_t)c * p.n_qblocks + qb) * kTileM + r;
+    for (int c = 0; c < nsg; ++c) {
+        const int64_t ur = ((int64_t)segs[c] * p.group_size + member) * kTileM + r;
         const int cnt = p.cand_cnt[ur];
         tau = fmaxf(tau, p.cand_tau[ur]);
         total += cnt;
@@ -172,7 +175,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
 }
 
 size_t select_smem_bytes(const SelectParams &p) {
-    const size_t E = (size_t)p.n_chunks * p.kprime;
+    const size_t E = (size_t)p.segs_per_group * p.kprime;
     const size_t ks = (size_t)next_pow2(p.kprime);
     return E * 8 + ks * 8 + ks * 4 + (size_t)p.d * 4 + 40 * 4 + 16;
 }
@@ -189,8 +192,8 @@ static int launch_sel(const SelectParams &p, cudaStream_t st) {
 
 int launch_select(const SelectParams &p, cudaStream_t st) {
     if (p.nq == 0) return VQ_OK;
-    VQ_CHECK((int64_t)p.n_chunks * p.kprime <= (int64_t)kSelThreads * 64, VQ_ERR_CAPACITY,
-             "select: %d chunks x k'=%d exceeds the per-query gather capacity", p.n_chunks, p.kprime);
+    VQ_CHECK((int64_t)p.segs_per_group * p.kprime <= (int64_t)kSelThreads * 64, VQ_ERR_CAPACITY,
+             "select: %d segments x k'=%d exceeds the per-query gather capacity", p.segs_per_group, p.kprime);
     VQ_CHECK(select_smem_bytes(p) <= 200 * 1024, VQ_ERR_CAPACITY, "select: shared memory budget exceeded");
     const bool seg = p.seg_of_row != nullptr;
     if (p.dtype == VQ_F32) return seg ? launch_sel<float, true>(p, st) : launch_sel<float, false>(p, st);

@@ -98,7 +98,7 @@ class IndexFlatL2:
     def last_stats(self):
         out = (C.c_int64 * 6)()
         L.check(L.lib().vq_index_last_stats(self._h, out))
-        keys = ("fallback_queries", "tc_tiles", "kprime", "work_units", "chunks", "launches")
+        keys = ("fallback_queries", "tc_tiles", "kprime", "work_units", "segments", "launches")
         return dict(zip(keys, [int(v) for v in out]))
 
 
