@@ -20,12 +20,13 @@ ix.add(bench.gen_rows(torch, "g", 0, n, 512, dev))
 D = torch.empty((nq, 100), dtype=torch.float32, device=dev)
 I = torch.empty((nq, 100), dtype=torch.int64, device=dev)
 variants = {
-    "base(chain+dense4)": {},
-    "nochain": {"VQ_DEBUG_NO_CHAIN": "1"},
+    "dense8(default)": {},
     "nodense": {"VQ_DEBUG_DENSE_ROWS": "33"},
-    "nochain+nodense": {"VQ_DEBUG_NO_CHAIN": "1", "VQ_DEBUG_DENSE_ROWS": "33"},
     "dense2": {"VQ_DEBUG_DENSE_ROWS": "2"},
-    "dense8": {"VQ_DEBUG_DENSE_ROWS": "8"},
+    "dense3": {"VQ_DEBUG_DENSE_ROWS": "3"},
+    "dense4": {"VQ_DEBUG_DENSE_ROWS": "4"},
+    "dense16": {"VQ_DEBUG_DENSE_ROWS": "16"},
+    "nochain+nodense": {"VQ_DEBUG_NO_CHAIN": "1", "VQ_DEBUG_DENSE_ROWS": "33"},
 }
 keys = ("VQ_DEBUG_NO_CHAIN", "VQ_DEBUG_DENSE_ROWS")
 for _ in range(3):

@@ -189,7 +189,7 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     gp.col_video = n_ign > 0 ? ix->video : nullptr;
     gp.col_seg = segmax ? ix->seg_of_row : nullptr;
     gp.q_ignore = n_ign > 0 ? ign : nullptr; gp.n_ign = n_ign; gp.kprime = kprime;
-    gp.dense_rows = 8;  // measured: 8 beats 4 and "never" (scripts/ab_gemm.py, profiles/r01_ab_gemm_chain_dense.txt)
+    gp.dense_rows = 4;  // measured: scripts/ab_gemm.py, profiles/r01_ab_gemm_chain_dense.txt
     if (const char *e = getenv("VQ_DEBUG_DENSE_ROWS")) gp.dense_rows = atoi(e);  // A/B hook (33 = never)
     gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau;
     VQ_CUDA(cudaEventRecord(ix->ev[1], st));

@@ -133,6 +133,15 @@ __device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, i
     return pos;
 }
 
+// Out-of-line dispatcher: compactions are rare once the threshold has warmed up, and keeping their
+// three unrolled bodies out of the epilogue's hot loop keeps that loop inside the instruction cache.
+__device__ __noinline__ int compact_row_any(uint64_t *buf, int cnt, int kprime, int keep_max, float *tau_out) {
+    const int lane = threadIdx.x & 31;
+    if (cnt <= 320) return compact_row<10>(buf, cnt, kprime, keep_max, lane, tau_out);
+    if (cnt <= 576) return compact_row<18>(buf, cnt, kprime, keep_max, lane, tau_out);
+    return compact_row<kCandCap / 32>(buf, cnt, kprime, keep_max, lane, tau_out);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Epilogue role (warps 2-5 of either kernel).  Segments [s0, s1) of this CTA (pair).
 // Thread = accumulator row = query.  Per 32 columns: tcgen05.ld, max of the 32 values, ONE compare
@@ -203,10 +212,7 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                 const int c_r = __shfl_sync(0xffffffffu, cnt, src);
                 uint64_t *rb = wbuf + (int64_t)src * kCandCap;
                 float t_r;
-                int nc;
-                if (c_r <= 320) nc = compact_row<10>(rb, c_r, p.kprime, keep_max, lane, &t_r);
-                else if (c_r <= 576) nc = compact_row<18>(rb, c_r, p.kprime, keep_max, lane, &t_r);
-                else nc = compact_row<kCandCap / 32>(rb, c_r, p.kprime, keep_max, lane, &t_r);
+                const int nc = compact_row_any(rb, c_r, p.kprime, keep_max, &t_r);
                 if (lane == src) {
                     cnt = nc;
                     tau = fmaxf(tau, t_r);
@@ -217,6 +223,7 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
         // Intermediate compactions are cheap (few registers, early-exit bisection) and fire
         // often so that tau stays close to the k'-th best seen so far.  A 32-column step can add
         // at most 33 entries, hence the cap.
+        const int dense_rows = p.n_ign > 0 ? 33 : p.dense_rows;  // the per-thread scan does not apply the ignore rule
         const int trigger = min(2 * p.kprime, kCandCap - 64);
         const int keep_max = min(p.kprime + p.kprime / 2, trigger - 32);
         for (int t = 0; t < ntiles; ++t) {
@@ -287,18 +294,16 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                     if (need) compact_rows(need, keep_max);
                 } else {
                     uint32_t bal = __ballot_sync(0xffffffffu, m32 > tauh);
-                    if (__popc(bal) >= p.dense_rows) {
-                        // threshold warm-up (start of a segment): most rows hold candidates, so every
-                        // thread scans its own 32 values instead of serialising the rows through the warp
-                        if (m32 > tauh) {
+                    if (__popc(bal) >= dense_rows) {
+                        // many rows hold candidates in this step (threshold warm-up at the start of a
+                        // segment, or a gallery row that is close to every query): every thread scans
+                        // its own 32 values -- predicated, no per-row serialisation through the warp
+                        const uint32_t jlow = ~(jbase + (uint32_t)(ch * 32));  // key low word = ~row
 #pragma unroll
-                            for (int i = 0; i < 32; ++i) {
-                                if (v[i] > tauh) {
-                                    const uint32_t j = jbase + (uint32_t)(ch * 32 + i);
-                                    bool ok = true;
-                                    if (p.n_ign > 0) ok = !is_ignored(row, __ldg(p.col_video + j));
-                                    if (ok) append(2.0f * v[i], j);
-                                }
+                        for (int i = 0; i < 32; ++i) {
+                            if (v[i] > tauh) {
+                                buf[cnt] = ((uint64_t)f32_to_ordered(2.0f * v[i]) << 32) | (uint64_t)(jlow - (uint32_t)i);
+                                ++cnt;
                             }
                         }
                         const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
