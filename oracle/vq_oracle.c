@@ -517,12 +517,55 @@ ORC_API void orc_segmax_topk(const float *q, const float *g, int64_t nq, int64_t
  * Sampler.pdist, misc_utils/metric_learning_loss.py:276-289:
  *   prod = A A^T; norm = diag(prod); res = (norm_i + norm_j - 2*prod_ij).clamp(min=0);
  *   return res.clamp(min=eps).sqrt()
- * prod is evaluated with the canonical sequential fmaf chain (torch.mm's summation order is
- * a BLAS detail the reference does not pin); the remaining fp32 ops are in the source order.
+ * prod is evaluated with the canonical BLOCKED chain below (torch.mm's summation order is a
+ * BLAS detail the reference does not pin); the remaining fp32 ops are in the source order.
+ *
+ * Canonical blocked chain (all dot products and squared distances of the loss path): k runs
+ * in blocks of 32; inside a block, chunk c (4 consecutive k) is a sequential fmaf chain t_c
+ * starting from 0; the 8 chunk sums are added as a fixed tree (t_c + t_{c^4}, then ^2, then
+ * ^1 -- a warp-shuffle butterfly over 8 lanes computes exactly this); the block sum is added
+ * to the running accumulator.  Zero padding of the last block does not change any bit.
+ * This is the order the CUDA kernels use (vq_triplet*.cu): 8 lanes x LDS.128 per row block.
  * ---------------------------------------------------------------------------------- */
+static inline float orc_tree8(const float *t) {
+    float u0 = t[0] + t[4], u1 = t[1] + t[5], u2 = t[2] + t[6], u3 = t[3] + t[7];
+    float w0 = u0 + u2, w1 = u1 + u3;
+    return w0 + w1;
+}
+
 static inline float orc_dot(const float *a, const float *b, int d) {
     float acc = 0.0f;
-    for (int i = 0; i < d; ++i) acc = fmaf(a[i], b[i], acc);
+    for (int k0 = 0; k0 < d; k0 += 32) {
+        float t[8];
+        for (int c = 0; c < 8; ++c) {
+            t[c] = 0.0f;
+            for (int i = 0; i < 4; ++i) {
+                int k = k0 + c * 4 + i;
+                if (k < d) t[c] = fmaf(a[k], b[k], t[c]);
+            }
+        }
+        acc = acc + orc_tree8(t);
+    }
+    return acc;
+}
+
+/* squared L2 with the same blocked chain (loss path only; the search path uses orc_d2) */
+static inline float orc_d2_blocked(const float *a, const float *b, int d) {
+    float acc = 0.0f;
+    for (int k0 = 0; k0 < d; k0 += 32) {
+        float t[8];
+        for (int c = 0; c < 8; ++c) {
+            t[c] = 0.0f;
+            for (int i = 0; i < 4; ++i) {
+                int k = k0 + c * 4 + i;
+                if (k < d) {
+                    float df = a[k] - b[k];
+                    t[c] = fmaf(df, df, t[c]);
+                }
+            }
+        }
+        acc = acc + orc_tree8(t);
+    }
     return acc;
 }
 
@@ -577,7 +620,7 @@ ORC_API int64_t orc_batchhard_mine(const float *dist, const int64_t *labels, int
  *   loss = mean_t l_t
  * and its autograd backward: for active t (l_t > 0)
  *   d/da += 2(n-p)/T, d/dp += -2(a-p)/T, d/dn += 2(a-n)/T.
- * Canonical arithmetic: both sums by the sequential fmaf chain; the mean as a sequential
+ * Canonical arithmetic: both sums by the blocked chain (orc_d2_blocked); the mean as a sequential
  * fp32 sum in triplet order divided by T; each gradient row accumulated by scanning the
  * triplets in order with acc = fmaf(2/T, diff, acc) (anchor, then positive, then negative
  * role of the same triplet).  active[T] optional.
@@ -591,7 +634,7 @@ ORC_API void orc_triplet_fwd_bwd(const float *A, int64_t B, int d, const int32_t
         const float *a = A + (int64_t)trip[t * 3] * d;
         const float *p = A + (int64_t)trip[t * 3 + 1] * d;
         const float *n = A + (int64_t)trip[t * 3 + 2] * d;
-        float dap = orc_d2(a, p, d), dan = orc_d2(a, n, d);
+        float dap = orc_d2_blocked(a, p, d), dan = orc_d2_blocked(a, n, d);
         float v = (dap - dan) + margin;
         lt[t] = v > 0.0f ? v : 0.0f;
         sum += lt[t];

@@ -353,6 +353,63 @@ def test_triplet_cfg2_shape_bit_exact_vs_oracle(vq):
         assert np.array_equal(xs.grad[gi].cpu().numpy().view(np.uint32), go.view(np.uint32))
 
 
+def _check_groups(vq, embs, labs, margin):
+    import torch
+    from vqwild_b200.loss import _BatchHardFn
+    xs = torch.from_numpy(embs).cuda().requires_grad_(True)
+    loss, trip = _BatchHardFn.apply(xs, torch.from_numpy(labs), margin)
+    loss.sum().backward()
+    for gi in range(embs.shape[0]):
+        lo, go, to = orc.batchhard_triplet(embs[gi], labs[gi], margin)
+        t = trip[gi].cpu().numpy()
+        assert np.array_equal(t[t[:, 0] >= 0], to), "group %d mined triplets" % gi
+        assert loss[gi].item() == lo, "group %d loss" % gi
+        assert np.array_equal(xs.grad[gi].cpu().numpy().view(np.uint32), go.view(np.uint32)), "group %d grad" % gi
+
+
+@pytest.mark.parametrize("G,B,d,ncls", [(5, 256, 512, 64), (300, 64, 64, 8), (3, 100, 96, 10), (2, 256, 40, 32),
+                                        (4, 37, 132, 5)])
+def test_triplet_fused_shapes(vq, G, B, d, ncls):
+    """Fused tensor-core kernel (B <= 256, d % 4 == 0): ragged B / d, more groups than SMs."""
+    rng = np.random.default_rng(100 + B + d)
+    labs = np.stack([rng.permutation(np.arange(B) % ncls) for _ in range(G)]).astype(np.int64)
+    embs = np.stack([_emb(rng, B, d, ncls, labs[g], scale=(g % 2 == 0)) for g in range(G)])
+    _check_groups(vq, embs, labs, 0.5)
+
+
+def test_triplet_fused_adversarial(vq):
+    """Ties and degenerate groups: duplicate rows (exact distance ties -> lowest index), an anchor
+    identical to all its positives (pdist's clamp region), a singleton class, a single-class group
+    (no negatives: every anchor skipped), near-duplicates inside the TF32 error band, and a group
+    whose ambiguity overflows the fused kernel's candidate capacity (handed to the CUDA-core path)."""
+    rng = np.random.default_rng(5)
+    B, d, ncls = 128, 64, 16
+    labs = np.stack([np.arange(B) % ncls for _ in range(6)]).astype(np.int64)
+    embs = np.stack([_emb(rng, B, d, ncls, labs[g]) for g in range(6)])
+    embs[0, 16] = embs[0, 0]           # same class (0 and 16): d = clamp floor
+    embs[0, 33] = embs[0, 1]           # 33 % 16 == 1: same class duplicate
+    embs[0, 50] = embs[0, 3]           # 50 % 16 == 2: duplicate in ANOTHER class -> hardest negative ties
+    embs[0, 66] = embs[0, 3]           # two identical negatives for the class-3 anchors: lowest index wins
+    for j in range(0, B, ncls):        # group 1: class 0 all identical -> every positive in the clamp region
+        embs[1, j] = embs[1, 0]
+    labs[2, 5] = 77                    # singleton class
+    labs[3, :] = 4                     # single class: no negatives at all
+    base = embs[4, 7].copy()           # group 4: many rows within 1e-4 of each other (inside the coarse band)
+    for j in range(20, 40):
+        embs[4, j] = base + rng.standard_normal(d).astype(np.float32) * 1e-5
+    embs[5, :] = embs[5, 0] + rng.standard_normal((B, d)).astype(np.float32) * 1e-6  # everything ambiguous
+    _check_groups(vq, embs, labs, 1.0)
+
+
+def test_triplet_simt_path_matches(vq):
+    """The CUDA-core path (B > 256, or d % 4 != 0) produces the same bits as the oracle too."""
+    rng = np.random.default_rng(9)
+    labs = np.stack([np.arange(300) % 30]).astype(np.int64)
+    _check_groups(vq, np.stack([_emb(rng, 300, 48, 30, labs[0])]), labs, 0.7)
+    labs = np.stack([np.arange(50) % 5 for _ in range(2)]).astype(np.int64)
+    _check_groups(vq, np.stack([_emb(rng, 50, 33, 5, labs[g]) for g in range(2)]), labs, 0.7)
+
+
 def test_pool_normalize(vq, golden):
     out = vq.pool_normalize(golden["pool_in"])
     np.testing.assert_allclose(out, golden["pool_out"], rtol=0, atol=1e-6)

@@ -7,6 +7,6 @@ NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 "$NVCC" -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 \
   -Xcompiler -fPIC,-fvisibility=hidden -shared "$@" \
   "$HERE/vq_api.cu" "$HERE/vq_gemm_topk.cu" "$HERE/vq_select.cu" "$HERE/vq_exact.cu" \
-  "$HERE/vq_prepare.cu" "$HERE/vq_metrics.cu" "$HERE/vq_triplet.cu" \
+  "$HERE/vq_prepare.cu" "$HERE/vq_metrics.cu" "$HERE/vq_triplet.cu" "$HERE/vq_triplet_tc.cu" \
   -o "$OUT" -lcudart_static -ldl -lrt -lpthread
 echo "built $OUT"

@@ -142,20 +142,26 @@ static EncodeTiledFn encode_fn() {
     return fn;
 }
 
+int make_tensor_map_2d(CUtensorMap *m, const void *base, CUtensorMapDataType dt, int elem_bytes, uint64_t cols,
+                       uint64_t rows, uint64_t pitch_bytes, uint32_t box_cols, uint32_t box_rows) {
+    EncodeTiledFn fn = encode_fn();
+    VQ_CHECK(fn, VQ_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
+    VQ_CHECK((int)box_cols * elem_bytes <= 128, VQ_ERR_INVALID, "tensor map box wider than the 128-byte swizzle span");
+    cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)(rows > 0 ? rows : 1)};
+    cuuint64_t strides[1] = {(cuuint64_t)pitch_bytes};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1u, 1u};
+    CUresult r = fn(m, dt, 2, const_cast<void *>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    VQ_CHECK(r == CUDA_SUCCESS, VQ_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return VQ_OK;
+}
+
 // bf16 plane [rows, dp] row-major (dp = plane pitch incl. the augmentation block) -> boxes of 64
 // columns x box_rows rows, 128-byte swizzle; the box at column pitch-16 is zero-filled past the edge
 static int make_map(CUtensorMap *m, const void *base, int64_t rows, int dp, int box_rows) {
-    EncodeTiledFn fn = encode_fn();
-    VQ_CHECK(fn, VQ_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
-    cuuint64_t dims[2] = {(cuuint64_t)dp, (cuuint64_t)(rows > 0 ? rows : 1)};
-    cuuint64_t strides[1] = {(cuuint64_t)dp * 2};
-    cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
-    cuuint32_t estr[2] = {1u, 1u};
-    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    VQ_CHECK(r == CUDA_SUCCESS, VQ_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
-    return VQ_OK;
+    return make_tensor_map_2d(m, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (uint64_t)dp, (uint64_t)rows, (uint64_t)dp * 2,
+                              64u, (uint32_t)box_rows);
 }
 
 }  // namespace vq

@@ -457,8 +457,10 @@ int vq_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int
         VQ_TRY(tr.alloc((size_t)G * B * 3 * 4, st));
         tdev = (int32_t *)tr.p;
     }
+    Tmp wk;
+    VQ_TRY(wk.alloc((size_t)(G + 1) * 4, st));
     VQ_TRY(launch_triplet_batchhard(e.as<float>(), l.as<int32_t>(), G, B, d, margin, oL.as<float>(), oG.as<float>(),
-                                    tdev, (float *)lt.p, st));
+                                    tdev, (float *)lt.p, (int32_t *)wk.p, st));
     VQ_TRY(oL.finish(st));
     VQ_TRY(oG.finish(st));
     VQ_TRY(oT.finish(st));

@@ -136,11 +136,20 @@ int launch_nms1d(const double *dets, const int64_t *offsets, int64_t nseg, doubl
 int launch_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k, float *od,
                       int64_t *oi, cudaStream_t st);
 
+// 2-D row-major tensor map (vq_api.cu): box [box_cols x box_rows], 128-byte swizzle, zero OOB fill
+int make_tensor_map_2d(CUtensorMap *m, const void *base, CUtensorMapDataType dt, int elem_bytes, uint64_t cols,
+                       uint64_t rows, uint64_t pitch_bytes, uint32_t box_cols, uint32_t box_rows);
+
 // ---- vq_triplet.cu ----
 int launch_pdist(const float *A, int64_t B, int d, float eps, float *dist, cudaStream_t st);
+// dispatcher (vq_triplet_tc.cu): fused tensor-core kernel when B <= 256 and d % 4 == 0, groups it hands
+// back (and every other shape) go to the CUDA-core path.  scratch: float[G*B]; work: int32[G+1] device.
 int launch_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int64_t B, int d,
                              float margin, float *loss, float *grad, int32_t *trip, float *scratch,
-                             cudaStream_t st);
+                             int32_t *work, cudaStream_t st);
+int launch_triplet_batchhard_simt(const float *emb, const int32_t *labels, int64_t G, int64_t B, int d,
+                                  float margin, float *loss, float *grad, int32_t *trip, float *scratch,
+                                  const int32_t *glist, const int32_t *gcount, cudaStream_t st);
 int launch_triplet_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T,
                          float margin, float *loss, float *grad, float *scratch, cudaStream_t st);
 

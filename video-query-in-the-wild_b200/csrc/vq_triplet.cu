@@ -16,16 +16,41 @@
 
 namespace vq {
 
-__device__ __forceinline__ float dot_chain(const float *a, const float *b, int d) {
+// Canonical blocked chain of the loss path (oracle/vq_oracle.c: orc_dot / orc_d2_blocked): blocks of
+// 32 k; chunk c = 4 consecutive k as a sequential fmaf chain from 0; fixed tree over the 8 chunks
+// (c ^ 4, c ^ 2, c ^ 1); block sums added to the accumulator in order.
+__device__ __forceinline__ float tree8(const float (&t)[8]) {
+    const float u0 = __fadd_rn(t[0], t[4]), u1 = __fadd_rn(t[1], t[5]), u2 = __fadd_rn(t[2], t[6]),
+                u3 = __fadd_rn(t[3], t[7]);
+    return __fadd_rn(__fadd_rn(u0, u2), __fadd_rn(u1, u3));
+}
+template <bool SQDIFF>
+__device__ __forceinline__ float blocked_chain(const float *a, const float *b, int d) {
     float acc = 0.f;
-    for (int i = 0; i < d; ++i) acc = __fmaf_rn(a[i], b[i], acc);
+    for (int k0 = 0; k0 < d; k0 += 32) {
+        float t[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            t[c] = 0.f;
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int k = k0 + c * 4 + i;
+                if (k < d) {
+                    if (SQDIFF) {
+                        const float df = __fsub_rn(a[k], b[k]);
+                        t[c] = __fmaf_rn(df, df, t[c]);
+                    } else {
+                        t[c] = __fmaf_rn(a[k], b[k], t[c]);
+                    }
+                }
+            }
+        }
+        acc = __fadd_rn(acc, tree8(t));
+    }
     return acc;
 }
-__device__ __forceinline__ float d2_chain(const float *a, const float *b, int d) {
-    float acc = 0.f;
-    for (int i = 0; i < d; ++i) acc = canon_step(acc, a[i], b[i]);
-    return acc;
-}
+__device__ __forceinline__ float dot_chain(const float *a, const float *b, int d) { return blocked_chain<false>(a, b, d); }
+__device__ __forceinline__ float d2_chain(const float *a, const float *b, int d) { return blocked_chain<true>(a, b, d); }
 __device__ __forceinline__ float pdist_formula(float ni, float nj, float prod, float eps) {
     float res = __fsub_rn(__fadd_rn(ni, nj), __fmul_rn(2.0f, prod));
     res = res < 0.f ? 0.f : res;
@@ -40,16 +65,23 @@ static constexpr int MBMAX = 1024;  // max group size B
 
 // grid (B/MA rounded up, G).  Dynamic smem: float nrm[B] | float sA[MKC][MA+1] | float sR[MKC][B+1]
 // dist_out (optional): [G? no -- only when G == 1] B x B matrix.
+// glist/gcount (optional): blockIdx.y indexes a device list of group ids (the groups the fused tensor-core
+// kernel handed back, vq_triplet_tc.cu); blocks past *gcount exit.  NCMAX = columns per thread (B <= 8*NCMAX).
+template <int NCMAX>
 __global__ void __launch_bounds__(MT) bh_mine_kernel(const float *__restrict__ emb, const int32_t *__restrict__ labels,
                                                     int B, int d, float margin, float eps, int32_t *__restrict__ trip,
-                                                    float *__restrict__ lt, float *__restrict__ dist_out) {
+                                                    float *__restrict__ lt, float *__restrict__ dist_out,
+                                                    const int32_t *__restrict__ glist, const int32_t *__restrict__ gcount) {
     extern __shared__ __align__(16) float smf[];
     float *nrm = smf;
     float *sA = nrm + B;
     float *sR = sA + MKC * (MA + 1);
     __shared__ int s_p[MA], s_n[MA];
     const int tid = threadIdx.x;
-    const int g = blockIdx.y;
+    const int nlist = glist ? *gcount : (int)gridDim.y;
+    for (int li = blockIdx.y; li < nlist; li += gridDim.y) {
+    const int g = glist ? glist[li] : li;
+    __syncthreads();  // shared tiles of the previous group are no longer read
     const float *E = emb + (int64_t)g * B * d;
     const int32_t *L = labels ? labels + (int64_t)g * B : nullptr;
     const int a0 = blockIdx.x * MA;
@@ -57,9 +89,9 @@ __global__ void __launch_bounds__(MT) bh_mine_kernel(const float *__restrict__ e
     for (int r = tid; r < B; r += MT) nrm[r] = dot_chain(E + (int64_t)r * d, E + (int64_t)r * d, d);
     const int al = tid >> 3, cg = tid & 7;  // anchor (local), column group
     const int ncol = (B + 7) / 8;           // columns per thread: cg, cg+8, ...
-    float acc[MBMAX / 8];
+    float acc[NCMAX];
 #pragma unroll
-    for (int c = 0; c < MBMAX / 8; ++c) acc[c] = 0.f;
+    for (int c = 0; c < NCMAX; ++c) acc[c] = 0.f;
     for (int k0 = 0; k0 < d; k0 += MKC) {
         __syncthreads();
         for (int i = tid; i < MA * MKC; i += MT) {
@@ -71,16 +103,23 @@ __global__ void __launch_bounds__(MT) bh_mine_kernel(const float *__restrict__ e
             sR[k * (B + 1) + r] = (k0 + k < d) ? E[(int64_t)r * d + k0 + k] : 0.f;
         }
         __syncthreads();
-        const int kmax = min(MKC, d - k0);
-        for (int kk = 0; kk < kmax; ++kk) {
-            const float av = sA[kk * (MA + 1) + al];
-            const float *rr = sR + kk * (B + 1);
+        // one canonical 32-block per k chunk (rows past d are zero in shared memory: no effect)
+        float av[MKC];
 #pragma unroll
-            for (int c = 0; c < MBMAX / 8; ++c)
-                if (c < ncol) {
-                    const int j = cg + 8 * c;
-                    if (j < B) acc[c] = __fmaf_rn(av, rr[j], acc[c]);
+        for (int kk = 0; kk < MKC; ++kk) av[kk] = sA[kk * (MA + 1) + al];
+#pragma unroll
+        for (int c = 0; c < NCMAX; ++c) {
+            const int j = cg + 8 * c;
+            if (c < ncol && j < B) {
+                float t[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    t[q] = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) t[q] = __fmaf_rn(av[4 * q + i], sR[(4 * q + i) * (B + 1) + j], t[q]);
                 }
+                acc[c] = __fadd_rn(acc[c], tree8(t));
+            }
         }
     }
     __syncthreads();
@@ -91,7 +130,7 @@ __global__ void __launch_bounds__(MT) bh_mine_kernel(const float *__restrict__ e
     if (a < B) {
         const int la = L ? L[a] : 0;
 #pragma unroll
-        for (int c = 0; c < MBMAX / 8; ++c)
+        for (int c = 0; c < NCMAX; ++c)
             if (c < ncol) {
                 const int j = cg + 8 * c;
                 if (j < B) {
@@ -115,7 +154,7 @@ __global__ void __launch_bounds__(MT) bh_mine_kernel(const float *__restrict__ e
         if (oip >= 0 && (ip < 0 || obp > bp || (obp == bp && oip < ip))) { bp = obp; ip = oip; }
         if (oin >= 0 && (in_ < 0 || obn < bn || (obn == bn && oin < in_))) { bn = obn; in_ = oin; }
     }
-    if (!L) return;
+    if (!L) continue;
     if (cg == 0 && a < B) {
         s_p[al] = ip;
         s_n[al] = in_;
@@ -139,6 +178,7 @@ __global__ void __launch_bounds__(MT) bh_mine_kernel(const float *__restrict__ e
             lt[o] = 0.f;
         }
     }
+    }  // group list
 }
 
 // per-triplet losses for a caller-provided list (one thread per (triplet, role))
@@ -165,9 +205,12 @@ __global__ void __launch_bounds__(256) triplet_losses_kernel(const float *__rest
 __global__ void __launch_bounds__(256) triplet_grad_kernel(const float *__restrict__ emb, int B, int d,
                                                            const int32_t *__restrict__ trip, const float *__restrict__ lt,
                                                            int64_t T_in, float *__restrict__ loss,
-                                                           float *__restrict__ grad) {
+                                                           float *__restrict__ grad, const int32_t *__restrict__ glist,
+                                                           const int32_t *__restrict__ gcount) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int g = blockIdx.y;
+    const int nlist = glist ? *gcount : (int)gridDim.y;
+    for (int li = blockIdx.y; li < nlist; li += gridDim.y) {
+    const int g = glist ? glist[li] : li;
     const int64_t slots = T_in < 0 ? B : T_in;
     const int32_t *TR = trip + (int64_t)g * slots * 3;
     const float *LT = lt + (int64_t)g * slots;
@@ -182,9 +225,9 @@ __global__ void __launch_bounds__(256) triplet_grad_kernel(const float *__restri
             if (TR[t * 3] >= 0) s = __fadd_rn(s, LT[t]);
         loss[g] = T > 0 ? __fdiv_rn(s, (float)T) : 0.f;
     }
-    if (!grad) return;
+    if (!grad) continue;
     const int r = blockIdx.x * 8 + w;
-    if (r >= B) return;
+    if (r >= B) continue;
     const float scale = T > 0 ? __fdiv_rn(2.0f, (float)T) : 0.f;
     float *gr = grad + ((int64_t)g * B + r) * d;
     for (int c0 = 0; c0 < d; c0 += 32 * 8) {
@@ -213,33 +256,44 @@ __global__ void __launch_bounds__(256) triplet_grad_kernel(const float *__restri
             if (c < d) gr[c] = acc[u];
         }
     }
+    }  // group list
 }
 
 static size_t mine_smem(int B) { return ((size_t)B + MKC * (MA + 1) + (size_t)MKC * (B + 1)) * 4; }
 
-int launch_pdist(const float *A, int64_t B, int d, float eps, float *dist, cudaStream_t st) {
-    if (B == 0) return VQ_OK;
-    VQ_CHECK(B <= MBMAX, VQ_ERR_CAPACITY, "pdist: B=%lld exceeds %d", (long long)B, MBMAX);
-    const size_t smem = mine_smem((int)B);
-    VQ_CUDA(cudaFuncSetAttribute(bh_mine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((unsigned)((B + MA - 1) / MA), 1);
-    bh_mine_kernel<<<grid, MT, smem, st>>>(A, nullptr, (int)B, d, 0.f, eps, nullptr, nullptr, dist);
+template <int NCMAX>
+static int launch_mine(const float *emb, const int32_t *labels, int64_t G, int B, int d, float margin, float eps,
+                       int32_t *trip, float *lt, float *dist, const int32_t *glist, const int32_t *gcount,
+                       cudaStream_t st) {
+    const size_t smem = mine_smem(B);
+    auto kern = bh_mine_kernel<NCMAX>;
+    VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    dim3 grid((unsigned)((B + MA - 1) / MA), (unsigned)G);
+    kern<<<grid, MT, smem, st>>>(emb, labels, B, d, margin, eps, trip, lt, dist, glist, gcount);
     VQ_CUDA(cudaGetLastError());
     return VQ_OK;
 }
 
-int launch_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int64_t B, int d, float margin,
-                             float *loss, float *grad, int32_t *trip, float *scratch, cudaStream_t st) {
+int launch_pdist(const float *A, int64_t B, int d, float eps, float *dist, cudaStream_t st) {
+    if (B == 0) return VQ_OK;
+    VQ_CHECK(B <= MBMAX, VQ_ERR_CAPACITY, "pdist: B=%lld exceeds %d", (long long)B, MBMAX);
+    if (B <= 256) return launch_mine<32>(A, nullptr, 1, (int)B, d, 0.f, eps, nullptr, nullptr, dist, nullptr, nullptr, st);
+    return launch_mine<MBMAX / 8>(A, nullptr, 1, (int)B, d, 0.f, eps, nullptr, nullptr, dist, nullptr, nullptr, st);
+}
+
+// CUDA-core path: any B <= 1024, any d.  glist/gcount: restrict to a device list of groups (G = list capacity).
+int launch_triplet_batchhard_simt(const float *emb, const int32_t *labels, int64_t G, int64_t B, int d, float margin,
+                                  float *loss, float *grad, int32_t *trip, float *scratch, const int32_t *glist,
+                                  const int32_t *gcount, cudaStream_t st) {
     if (G == 0 || B == 0) return VQ_OK;
     VQ_CHECK(B <= MBMAX, VQ_ERR_CAPACITY, "triplet: B=%lld exceeds %d", (long long)B, MBMAX);
     VQ_CHECK(G <= 65535, VQ_ERR_CAPACITY, "triplet: G=%lld exceeds 65535 groups per call", (long long)G);
-    const size_t smem = mine_smem((int)B);
-    VQ_CUDA(cudaFuncSetAttribute(bh_mine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    dim3 grid((unsigned)((B + MA - 1) / MA), (unsigned)G);
-    bh_mine_kernel<<<grid, MT, smem, st>>>(emb, labels, (int)B, d, margin, 1e-4f, trip, scratch, nullptr);
-    VQ_CUDA(cudaGetLastError());
+    if (B <= 256)
+        VQ_TRY(launch_mine<32>(emb, labels, G, (int)B, d, margin, 1e-4f, trip, scratch, nullptr, glist, gcount, st));
+    else
+        VQ_TRY(launch_mine<MBMAX / 8>(emb, labels, G, (int)B, d, margin, 1e-4f, trip, scratch, nullptr, glist, gcount, st));
     dim3 grid2((unsigned)((B + 7) / 8), (unsigned)G);
-    triplet_grad_kernel<<<grid2, 256, 0, st>>>(emb, (int)B, d, trip, scratch, -1, loss, grad);
+    triplet_grad_kernel<<<grid2, 256, 0, st>>>(emb, (int)B, d, trip, scratch, -1, loss, grad, glist, gcount);
     VQ_CUDA(cudaGetLastError());
     return VQ_OK;
 }
@@ -251,7 +305,7 @@ int launch_triplet_given(const float *emb, int64_t B, int d, const int32_t *trip
         VQ_CUDA(cudaGetLastError());
     }
     dim3 grid2((unsigned)((B + 7) / 8), 1);
-    triplet_grad_kernel<<<grid2, 256, 0, st>>>(emb, (int)B, d, trip, scratch, T, loss, grad);
+    triplet_grad_kernel<<<grid2, 256, 0, st>>>(emb, (int)B, d, trip, scratch, T, loss, grad, nullptr, nullptr);
     VQ_CUDA(cudaGetLastError());
     return VQ_OK;
 }

@@ -1,0 +1,567 @@
+// vq_triplet_tc.cu -- kernel (3), fused: batch-hard triplet loss forward + backward for groups of
+// B <= 256 embeddings, ONE persistent CTA per group, three streaming passes over the group's rows
+// (HBM once, then L2), everything else in shared memory / TMEM:
+//
+//   pass 1  TMA k-blocks [256 rows x 32 fp32] -> tcgen05.mma kind::tf32 Gram E E^T into TMEM
+//           (two M=128 x N=256 accumulators = all 512 TMEM columns); the row threads compute the
+//           canonical row norms from the same stages.
+//   mine    thread = anchor reads its accumulator row (tcgen05.ld): coarse res = |a|^2+|j|^2-2G.
+//           The TF32 Gram is only a PRE-FILTER with a proven error bound eps: every j whose coarse
+//           value is within 2*eps of the coarse extreme stays a candidate (Sampler.pdist's clamps,
+//           metric_learning_loss.py:276-289, widen the band when they can create ties).
+//   pass 2  canonical blocked chains (oracle: orc_dot / orc_d2_blocked) for (anchor, candidate)
+//           pairs, 8 lanes x LDS.128 per row block -> exact pdist of the candidates -> final
+//           arg-max positive / arg-min negative (ties -> lowest index) and the loss terms
+//           relu(|a-p|^2 - |a-n|^2 + m) (TripletLoss.triplet_distance, :342-355).
+//   pass 3  backward as a deterministic gather: per gradient row the list of triplets that touch
+//           it (in triplet order), acc = fmaf(2/T, x_u - x_v, acc); written once, coalesced.
+//
+// Results are bit-identical to the CUDA-core path (vq_triplet.cu) and to the oracle whatever the
+// tensor cores rounded.  Groups that exceed a fixed capacity (more than 4 candidates for a role,
+// more than 64 candidate triples in a warp) are handed back through `bad_list` and recomputed by
+// the CUDA-core path.
+#include <stdlib.h>
+
+#include <algorithm>
+
+#include "vq_common.cuh"
+#include "vq_kernels.h"
+
+namespace vq {
+
+static constexpr int TB = 256;                    // rows per group tile
+static constexpr int TKB = 32;                    // fp32 columns per k-block (128-byte rows)
+static constexpr int TSTAGE = TB * TKB * 4;       // 32 KB
+static constexpr int TSTAGES = 5;
+static constexpr int TROWT = 256;                 // row threads (warps 2..9)
+static constexpr int TTHREADS = 64 + TROWT;
+static constexpr int TCAND = 4;                   // candidates kept per role and anchor
+static constexpr int TTRIP = 64;                  // candidate triples per warp
+static constexpr int TSLOTS = TTRIP / 4;
+
+struct TcLayout {
+    static constexpr int OFF_NRM = TSTAGES * TSTAGE;       // float[256]
+    static constexpr int OFF_LAB = OFF_NRM + 1024;         // int[256]
+    static constexpr int OFF_TP = OFF_LAB + 1024;          // int[256] mined positive (-1: skipped anchor)
+    static constexpr int OFF_TN = OFF_TP + 1024;           // int[256]
+    static constexpr int OFF_LT = OFF_TN + 1024;           // float[256] per-anchor loss
+    static constexpr int OFF_TL = OFF_LT + 1024;           // uint32[8][64] candidate triples (a | j1<<8 | j2<<16)
+    static constexpr int OFF_RES = OFF_TL + 8 * TTRIP * 4;  // float4[8][64] (d2_1, prod_1, d2_2, prod_2)
+    static constexpr int OFF_EOFF = OFF_RES + 8 * TTRIP * 16;  // int[260] CSR offsets of the gradient gather lists
+    static constexpr int OFF_ECNT = OFF_EOFF + 1040;        // int[256] counters
+    static constexpr int OFF_ENT = OFF_ECNT + 1024;         // uint16[768] entries
+    static constexpr int OFF_MISC = OFF_ENT + 1536;         // int[16]
+    static constexpr int OFF_BAR = OFF_MISC + 64;           // full[S] empty[S] tfull tempty
+    static constexpr int OFF_TMEM = OFF_BAR + (2 * TSTAGES + 2) * 8;
+    static constexpr int TOTAL = OFF_TMEM + 16 + 1024;
+};
+static_assert(TcLayout::TOTAL <= 227 * 1024, "fused triplet kernel shared memory");
+
+struct TripletTcParams {
+    const int32_t *labels;  // [G,B]
+    int G, B, d;
+    float margin;
+    float *loss;     // [G]
+    float *grad;     // [G,B,d] or null
+    int32_t *trip;   // [G,B,3]
+    int32_t *bad_count, *bad_list;
+};
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        :
+        : "r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// instruction descriptor: kind::tf32, A=B=tf32 (K-major), D=fp32
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+__device__ __forceinline__ float tc_tree8_shfl(float t) {  // butterfly over the 8 lanes of a sub-group: c^4, c^2, c^1
+    t = __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, 4));
+    t = __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, 2));
+    t = __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, 1));
+    return t;
+}
+__device__ __forceinline__ float tc_tree8(const float (&t)[8]) {
+    const float u0 = __fadd_rn(t[0], t[4]), u1 = __fadd_rn(t[1], t[5]), u2 = __fadd_rn(t[2], t[6]),
+                u3 = __fadd_rn(t[3], t[7]);
+    return __fadd_rn(__fadd_rn(u0, u2), __fadd_rn(u1, u3));
+}
+__device__ __forceinline__ float tc_pdist(float ni, float nj, float prod, float eps) {  // Sampler.pdist :286-289
+    float res = __fsub_rn(__fadd_rn(ni, nj), __fmul_rn(2.0f, prod));
+    res = res < 0.f ? 0.f : res;
+    res = res < eps ? eps : res;
+    return __fsqrt_rn(res);
+}
+// 16-byte chunk c of row r inside a 128B-swizzled [256 x 32 fp32] stage
+__device__ __forceinline__ float4 tc_ld_chunk(const uint8_t *stage, int r, int c) {
+    return *reinterpret_cast<const float4 *>(stage + r * 128 + ((c ^ (r & 7)) << 4));
+}
+__device__ __forceinline__ float tc_sq4(float4 a, float4 b) {  // chunk chain of (a-b)^2
+    float df = __fsub_rn(a.x, b.x), t = __fmaf_rn(df, df, 0.f);
+    df = __fsub_rn(a.y, b.y); t = __fmaf_rn(df, df, t);
+    df = __fsub_rn(a.z, b.z); t = __fmaf_rn(df, df, t);
+    df = __fsub_rn(a.w, b.w); t = __fmaf_rn(df, df, t);
+    return t;
+}
+__device__ __forceinline__ float tc_dot4(float4 a, float4 b) {
+    float t = __fmaf_rn(a.x, b.x, 0.f);
+    t = __fmaf_rn(a.y, b.y, t);
+    t = __fmaf_rn(a.z, b.z, t);
+    t = __fmaf_rn(a.w, b.w, t);
+    return t;
+}
+
+// ---------------------------------------------------------------------------------------------
+// warp 0: TMA producer   warp 1: MMA issuer (pass 1) / stage releaser (passes 2, 3)
+// warps 2..9: row threads (thread <-> row of the group; TMEM lane quarter = warp % 4)
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TTHREADS, 1)
+triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParams p) {
+    using L = TcLayout;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t *smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float *s_nrm = (float *)(smem + L::OFF_NRM);
+    int *s_lab = (int *)(smem + L::OFF_LAB);
+    int *s_tp = (int *)(smem + L::OFF_TP);
+    int *s_tn = (int *)(smem + L::OFF_TN);
+    float *s_lt = (float *)(smem + L::OFF_LT);
+    uint32_t *s_tl = (uint32_t *)(smem + L::OFF_TL);
+    float4 *s_res = (float4 *)(smem + L::OFF_RES);
+    int *s_eoff = (int *)(smem + L::OFF_EOFF);
+    int *s_ecnt = (int *)(smem + L::OFF_ECNT);
+    uint16_t *s_ent = (uint16_t *)(smem + L::OFF_ENT);
+    int *s_misc = (int *)(smem + L::OFF_MISC);  // [0] max |row|^2 bits  [1] T  [2] bad flag  [4..11] scan partials
+    uint64_t *full_bar = (uint64_t *)(smem + L::OFF_BAR);
+    uint64_t *empty_bar = full_bar + TSTAGES;
+    uint64_t *tfull_bar = empty_bar + TSTAGES;
+    uint64_t *tempty_bar = tfull_bar + 1;
+    uint32_t *tmem_slot = (uint32_t *)(smem + L::OFF_TMEM);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int KB = (p.d + TKB - 1) / TKB;
+    const int B = p.B;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tm_e);
+        for (int s = 0; s < TSTAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 9);  // 8 row warps + the MMA warp (tcgen05.commit in pass 1, plain arrive after)
+        }
+        mbar_init(tfull_bar, 1);
+        mbar_init(tempty_bar, 8);
+        fence_barrier_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ================================ TMA producer =================================
+        int stage = 0;
+        uint32_t phase = 0;
+        for (int g = blockIdx.x; g < p.G; g += gridDim.x) {
+            for (int pass = 0; pass < 3; ++pass) {
+                const uint64_t hint = pass == 2 ? kEvictFirst : kEvictLast;  // the rows are read again in the next pass
+                for (int kb = 0; kb < KB; ++kb) {
+                    mbar_wait(&empty_bar[stage], phase ^ 1u);
+                    if (elect_one()) {
+                        mbar_expect_tx(&full_bar[stage], TSTAGE);
+                        tma_load_2d(&tm_e, &full_bar[stage], smem + stage * TSTAGE, kb * TKB, g * B, hint);
+                    }
+                    __syncwarp();
+                    if (++stage == TSTAGES) {
+                        stage = 0;
+                        phase ^= 1u;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================================ MMA issuer ===================================
+        constexpr uint32_t idesc = umma_idesc_tf32(128, 256);
+        int stage = 0;
+        uint32_t phase = 0, tphase = 0;
+        for (int g = blockIdx.x; g < p.G; g += gridDim.x) {
+            mbar_wait(tempty_bar, tphase ^ 1u);  // the row threads have finished reading the previous Gram
+            tphase ^= 1u;
+            tc_fence_after();
+            for (int kb = 0; kb < KB; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
+                tc_fence_after();
+                const uint32_t sa = smem_u32(smem + stage * TSTAGE);
+                const uint64_t d_top = umma_desc_sw128(sa), d_bot = umma_desc_sw128(sa + 128 * 128);
+                if (elect_one()) {
+#pragma unroll
+                    for (int k = 0; k < TKB / 8; ++k) {  // K = 8 tf32 = 32 bytes per step
+                        umma_tf32(tmem_base, d_top + 2 * k, d_top + 2 * k, idesc, (kb | k) != 0);        // rows 0..127 x all
+                        umma_tf32(tmem_base + 256, d_bot + 2 * k, d_top + 2 * k, idesc, (kb | k) != 0);  // rows 128..255 x all
+                    }
+                    umma_commit(&empty_bar[stage]);
+                    if (kb == KB - 1) umma_commit(tfull_bar);
+                }
+                __syncwarp();
+                if (++stage == TSTAGES) {
+                    stage = 0;
+                    phase ^= 1u;
+                }
+            }
+            for (int kb = 0; kb < 2 * KB; ++kb) {  // passes 2 and 3: this warp does not read the stages
+                mbar_wait(&full_bar[stage], phase);
+                if (lane == 0) mbar_arrive(&empty_bar[stage]);
+                __syncwarp();
+                if (++stage == TSTAGES) {
+                    stage = 0;
+                    phase ^= 1u;
+                }
+            }
+        }
+    } else {
+        // ================================ row threads ==================================
+        const int q = warp & 3, half = (warp - 2) >> 2, rw = warp - 2;
+        const int row0 = half * 128 + q * 32, row = row0 + lane;
+        const int sw = row & 7;
+        const int m = lane >> 3, c = lane & 7;  // sub-group of 8 lanes, 16-byte chunk of a 128-byte row block
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 256);
+        int stage = 0;
+        uint32_t phase = 0, tphase = 0;
+        auto next_stage = [&]() {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            if (++stage == TSTAGES) {
+                stage = 0;
+                phase ^= 1u;
+            }
+        };
+        for (int g = blockIdx.x; g < p.G; g += gridDim.x) {
+            const bool rvalid = row < B;
+            // ---------------- pass 1: canonical |row|^2 from the stages the MMA reads ----------------
+            float na = 0.f;
+            for (int kb = 0; kb < KB; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
+                const uint8_t *sp = smem + stage * TSTAGE + row * 128;
+                float t[8];
+#pragma unroll
+                for (int cc = 0; cc < 8; ++cc) {
+                    const float4 x = *reinterpret_cast<const float4 *>(sp + ((cc ^ sw) << 4));
+                    t[cc] = tc_dot4(x, x);
+                }
+                na = __fadd_rn(na, tc_tree8(t));
+                next_stage();
+            }
+            s_nrm[row] = na;
+            s_lab[row] = rvalid ? p.labels[(int64_t)g * B + row] : 0;
+            s_ecnt[row] = 0;
+            if (threadIdx.x == 64) {
+                s_misc[0] = 0;
+                s_misc[2] = 0;
+            }
+            named_bar_sync(1, TROWT);
+            if (rvalid) atomicMax(&s_misc[0], __float_as_int(na));  // na >= 0: int order == float order
+            named_bar_sync(1, TROWT);
+            const float nmax = __int_as_float(s_misc[0]);
+            const int la = s_lab[row];
+            // |coarse - canonical res| <= eps: TF32 operands (2^-10 each, truncation assumed), fp32
+            // accumulation inside the tensor core, the canonical chain's own rounding
+            const float eps = 4.2e-3f * sqrtf(na * nmax) + 1e-5f * (na + nmax);
+
+            // ---------------- mine: coarse extremes, then candidates inside the band ----------------
+            mbar_wait(tfull_bar, tphase);
+            tphase ^= 1u;
+            tc_fence_after();
+            float maxp = -INFINITY, minn = INFINITY;
+#pragma unroll 1
+            for (int ch = 0; ch < TB / 32; ++ch) {
+                if (ch * 32 >= B) break;
+                uint32_t r[32];
+                tmem_ld32(taddr + ch * 32, r);
+                tmem_wait_ld();
+#pragma unroll
+                for (int i = 0; i < 32; ++i) {
+                    const int j = ch * 32 + i;
+                    const float cv = __fmaf_rn(-2.0f, __uint_as_float(r[i]), __fadd_rn(na, s_nrm[j]));
+                    const bool ok = j < B && j != row;
+                    const bool same = s_lab[j] == la;
+                    if (ok && same) maxp = fmaxf(maxp, cv);
+                    if (ok && !same) minn = fminf(minn, cv);
+                }
+            }
+            const bool avalid = rvalid && maxp > -INFINITY && minn < INFINITY;
+            const float thr_p = maxp < 1e-4f + 2.0f * eps ? -INFINITY : maxp - 2.0f * eps;  // clamp region: every positive ties
+            const float thr_n = fmaxf(minn, 1e-4f) + 2.0f * eps;
+            uint32_t cpw = 0, cnw = 0;  // up to 4 candidate rows per role, one byte each, ascending row order
+            int ncp = 0, ncn = 0;
+            if (__any_sync(0xffffffffu, avalid)) {
+#pragma unroll 1
+                for (int ch = 0; ch < TB / 32; ++ch) {
+                    if (ch * 32 >= B) break;
+                    uint32_t r[32];
+                    tmem_ld32(taddr + ch * 32, r);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        const int j = ch * 32 + i;
+                        const float cv = __fmaf_rn(-2.0f, __uint_as_float(r[i]), __fadd_rn(na, s_nrm[j]));
+                        const bool ok = avalid && j < B && j != row;
+                        const bool same = s_lab[j] == la;
+                        if (ok && same && cv >= thr_p) {
+                            if (ncp < TCAND) cpw |= (uint32_t)j << (8 * ncp);
+                            ++ncp;
+                        }
+                        if (ok && !same && cv <= thr_n) {
+                            if (ncn < TCAND) cnw |= (uint32_t)j << (8 * ncn);
+                            ++ncn;
+                        }
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(tempty_bar);  // TMEM may take the next group's Gram
+            bool bad = ncp > TCAND || ncn > TCAND;
+            ncp = min(ncp, TCAND);
+            ncn = min(ncn, TCAND);
+
+            // ---------------- candidate triples of this warp ----------------
+            int ntr = avalid ? max(ncp, ncn) : 0;
+            int incl = ntr;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            int total = __shfl_sync(0xffffffffu, incl, 31);
+            const int off = incl - ntr;
+            if (total > TTRIP) {  // warp-uniform
+                bad = true;
+                total = 0;
+                ntr = 0;
+            }
+            if (__any_sync(0xffffffffu, bad) && lane == 0) s_misc[2] = 1;
+            for (int t = 0; t < ntr; ++t) {
+                const uint32_t j1 = t < ncp ? (cpw >> (8 * t)) & 255u : (uint32_t)row;
+                const uint32_t j2 = t < ncn ? (cnw >> (8 * t)) & 255u : (uint32_t)row;
+                s_tl[rw * TTRIP + off + t] = (uint32_t)row | (j1 << 8) | (j2 << 16);
+            }
+            __syncwarp();
+
+            // ---------------- pass 2: canonical chains of the candidate pairs ----------------
+            float a_d1[TSLOTS], a_p1[TSLOTS], a_d2[TSLOTS], a_p2[TSLOTS];
+#pragma unroll
+            for (int i = 0; i < TSLOTS; ++i) a_d1[i] = a_p1[i] = a_d2[i] = a_p2[i] = 0.f;
+            for (int kb = 0; kb < KB; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
+                const uint8_t *sp = smem + stage * TSTAGE;
+#pragma unroll
+                for (int i = 0; i < TSLOTS; ++i) {
+                    if (4 * i < total) {  // warp-uniform
+                        const int idx = 4 * i + m;
+                        const uint32_t e = idx < total ? s_tl[rw * TTRIP + idx] : 0u;
+                        const int ra = e & 255u, r1 = (e >> 8) & 255u, r2 = (e >> 16) & 255u;
+                        const float4 xa = tc_ld_chunk(sp, ra, c), x1 = tc_ld_chunk(sp, r1, c), x2 = tc_ld_chunk(sp, r2, c);
+                        a_d1[i] = __fadd_rn(a_d1[i], tc_tree8_shfl(tc_sq4(xa, x1)));
+                        a_p1[i] = __fadd_rn(a_p1[i], tc_tree8_shfl(tc_dot4(xa, x1)));
+                        a_d2[i] = __fadd_rn(a_d2[i], tc_tree8_shfl(tc_sq4(xa, x2)));
+                        a_p2[i] = __fadd_rn(a_p2[i], tc_tree8_shfl(tc_dot4(xa, x2)));
+                    }
+                }
+                next_stage();
+            }
+#pragma unroll
+            for (int i = 0; i < TSLOTS; ++i) {
+                const int idx = 4 * i + m;
+                if (c == 0 && idx < total) s_res[rw * TTRIP + idx] = make_float4(a_d1[i], a_p1[i], a_d2[i], a_p2[i]);
+            }
+            __syncwarp();
+
+            // ---------------- exact decision among the candidates, per-anchor loss ----------------
+            int fp = -1, fn = -1;
+            float lterm = 0.f;
+            if (ntr > 0) {
+                const float4 *rs = s_res + rw * TTRIP + off;
+                int bq = 0;
+                if (ncp > 1) {
+                    float bd = 0.f;
+                    for (int t = 0; t < ncp; ++t) {
+                        const float dist = tc_pdist(na, s_nrm[(cpw >> (8 * t)) & 255u], rs[t].y, 1e-4f);
+                        if (t == 0 || dist > bd) {  // ascending row order: the first maximum wins
+                            bd = dist;
+                            bq = t;
+                        }
+                    }
+                }
+                fp = (int)((cpw >> (8 * bq)) & 255u);
+                const float d2p = rs[bq].x;
+                bq = 0;
+                if (ncn > 1) {
+                    float bd = 0.f;
+                    for (int t = 0; t < ncn; ++t) {
+                        const float dist = tc_pdist(na, s_nrm[(cnw >> (8 * t)) & 255u], rs[t].w, 1e-4f);
+                        if (t == 0 || dist < bd) {
+                            bd = dist;
+                            bq = t;
+                        }
+                    }
+                }
+                fn = (int)((cnw >> (8 * bq)) & 255u);
+                const float d2n = rs[bq].z;
+                const float v = __fadd_rn(__fsub_rn(d2p, d2n), p.margin);
+                lterm = v > 0.f ? v : 0.f;
+            }
+            s_tp[row] = fp;
+            s_tn[row] = fn;
+            s_lt[row] = lterm;
+            if (rvalid) {
+                int32_t *tr = p.trip + ((int64_t)g * B + row) * 3;
+                tr[0] = fp >= 0 ? row : -1;
+                tr[1] = fp;
+                tr[2] = fn;
+            }
+            named_bar_sync(1, TROWT);
+
+            // ---------------- loss mean (:379) and the gradient gather lists ----------------
+            const bool act = fp >= 0 && lterm > 0.f;
+            if (act) {
+                atomicAdd(&s_ecnt[row], 1);
+                atomicAdd(&s_ecnt[fp], 1);
+                atomicAdd(&s_ecnt[fn], 1);
+            }
+            if (threadIdx.x == 64) {  // sequential sum in triplet order, as the oracle
+                int T = 0;
+                float s = 0.f;
+                for (int t = 0; t < B; ++t)
+                    if (s_tp[t] >= 0) {
+                        ++T;
+                        s = __fadd_rn(s, s_lt[t]);
+                    }
+                s_misc[1] = T;
+                p.loss[g] = T > 0 ? __fdiv_rn(s, (float)T) : 0.f;
+            }
+            named_bar_sync(1, TROWT);
+            {   // exclusive scan of the per-row counts in row order
+                const int cnt = s_ecnt[row];
+                int inc2 = cnt;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const int v = __shfl_up_sync(0xffffffffu, inc2, o);
+                    if (lane >= o) inc2 += v;
+                }
+                if (lane == 31) s_misc[4 + (row >> 5)] = inc2;
+                named_bar_sync(1, TROWT);
+                int basep = 0;
+                for (int b = 0; b < (row >> 5); ++b) basep += s_misc[4 + b];
+                s_eoff[row] = basep + inc2 - cnt;
+                if (row == TB - 1) s_eoff[TB] = basep + inc2;
+                s_ecnt[row] = 0;
+            }
+            named_bar_sync(1, TROWT);
+            if (act) {  // entry = (triplet << 2 | role); sorted by triplet below
+                s_ent[s_eoff[row] + atomicAdd(&s_ecnt[row], 1)] = (uint16_t)((row << 2) | 0);
+                s_ent[s_eoff[fp] + atomicAdd(&s_ecnt[fp], 1)] = (uint16_t)((row << 2) | 1);
+                s_ent[s_eoff[fn] + atomicAdd(&s_ecnt[fn], 1)] = (uint16_t)((row << 2) | 2);
+            }
+            named_bar_sync(1, TROWT);
+            {   // each row: its triplets in order, rewritten as (u << 8 | v): contribution x_u - x_v
+                const int e0 = s_eoff[row], e1 = s_eoff[row + 1];
+                for (int i = e0 + 1; i < e1; ++i) {
+                    const uint16_t key = s_ent[i];
+                    int j = i - 1;
+                    while (j >= e0 && s_ent[j] > key) {
+                        s_ent[j + 1] = s_ent[j];
+                        --j;
+                    }
+                    s_ent[j + 1] = key;
+                }
+                for (int i = e0; i < e1; ++i) {
+                    const int t = s_ent[i] >> 2, role = s_ent[i] & 3;
+                    int u, v;
+                    if (role == 0) { u = s_tn[t]; v = s_tp[t]; }      // anchor:   2(n - p)/T
+                    else if (role == 1) { u = row; v = t; }           // positive: 2(p - a)/T
+                    else { u = t; v = row; }                          // negative: 2(a - n)/T
+                    s_ent[i] = (uint16_t)((u << 8) | v);
+                }
+            }
+            named_bar_sync(1, TROWT);
+            const int T = s_misc[1];
+            const float scale = T > 0 ? __fdiv_rn(2.0f, (float)T) : 0.f;
+
+            // ---------------- pass 3: gradient rows, 8 lanes x 16 bytes per row block ----------------
+            for (int kb = 0; kb < KB; ++kb) {
+                mbar_wait(&full_bar[stage], phase);
+                if (p.grad) {
+                    const uint8_t *sp = smem + stage * TSTAGE;
+                    const int col = kb * TKB + c * 4;
+#pragma unroll 1
+                    for (int rr = 0; rr < 8; ++rr) {
+                        const int r = row0 + m + 4 * rr;
+                        const int e0 = s_eoff[r], e1 = s_eoff[r + 1];
+                        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                        for (int e = e0; e < e1; ++e) {
+                            const int uv = s_ent[e];
+                            const float4 xu = tc_ld_chunk(sp, uv >> 8, c), xv = tc_ld_chunk(sp, uv & 255, c);
+                            acc.x = __fmaf_rn(scale, __fsub_rn(xu.x, xv.x), acc.x);
+                            acc.y = __fmaf_rn(scale, __fsub_rn(xu.y, xv.y), acc.y);
+                            acc.z = __fmaf_rn(scale, __fsub_rn(xu.z, xv.z), acc.z);
+                            acc.w = __fmaf_rn(scale, __fsub_rn(xu.w, xv.w), acc.w);
+                        }
+                        if (r < B && col < p.d)
+                            *reinterpret_cast<float4 *>(p.grad + ((int64_t)g * B + r) * p.d + col) = acc;
+                    }
+                }
+                next_stage();
+            }
+            if (threadIdx.x == 64 && s_misc[2]) p.bad_list[atomicAdd(p.bad_count, 1)] = g;
+            named_bar_sync(1, TROWT);  // shared lists are rebuilt by the next group
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+static int g_tc_grid = 0;
+
+int launch_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int64_t B, int d, float margin,
+                             float *loss, float *grad, int32_t *trip, float *scratch, int32_t *work, cudaStream_t st) {
+    if (G == 0 || B == 0) return VQ_OK;
+    const bool fused = B <= TB && d % 4 == 0 && d >= 4 && ((uintptr_t)emb & 15u) == 0 &&
+                       (!grad || ((uintptr_t)grad & 15u) == 0) && G * B < (1ll << 31) && !getenv("VQ_DEBUG_NO_TC_TRIPLET");
+    if (!fused) return launch_triplet_batchhard_simt(emb, labels, G, B, d, margin, loss, grad, trip, scratch, nullptr, nullptr, st);
+    CUtensorMap tm;
+    VQ_TRY(make_tensor_map_2d(&tm, emb, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (uint64_t)d, (uint64_t)(G * B), (uint64_t)d * 4,
+                              TKB, TB));
+    if (!g_tc_grid) {
+        int dev = 0, sms = 148;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        g_tc_grid = sms > 0 ? sms : 148;
+    }
+    VQ_CUDA(cudaMemsetAsync(work, 0, 4, st));
+    TripletTcParams p{};
+    p.labels = labels; p.G = (int)G; p.B = (int)B; p.d = d; p.margin = margin;
+    p.loss = loss; p.grad = grad; p.trip = trip; p.bad_count = work; p.bad_list = work + 1;
+    VQ_CUDA(cudaFuncSetAttribute(triplet_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TcLayout::TOTAL));
+    const int grid = (int)std::min<int64_t>(G, g_tc_grid);
+    triplet_tc_kernel<<<grid, TTHREADS, TcLayout::TOTAL, st>>>(tm, p);
+    VQ_CUDA(cudaGetLastError());
+    // groups handed back (capacity overflow): CUDA-core path over the device list, a few resident blocks
+    return launch_triplet_batchhard_simt(emb, labels, std::min<int64_t>(G, 8), B, d, margin, loss, grad, trip, scratch,
+                                         work + 1, work, st);
+}
+
+}  // namespace vq
