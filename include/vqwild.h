@@ -145,6 +145,8 @@ VQ_API int vq_nms1d_segmented(const double *dets, const int64_t *offsets, int64_
  *                       (extension; masks as :173-176) + backward.  G independent groups of B
  *                       rows: emb f32[G,B,d], labels int32[G,B] -> loss f32[G], grad f32[G,B,d],
  *                       trip int32[G,B,3] (a,p,n; -1 rows for skipped anchors), may be NULL.
+ *                       B <= 256 and d % 4 == 0 run the fused tensor-core kernel (TF32 Gram pre-filter,
+ *                       results identical to the CUDA-core path); other shapes the CUDA-core path.
  *   vq_triplet_given    same loss/backward for caller-sampled triplets int32[T,3] (the
  *                       reference's random/semihard/distance samplers run on the host).
  * All pointers host or device.
@@ -153,6 +155,9 @@ VQ_API int vq_pdist(const float *A, int64_t B, int d, float eps, float *dist, vo
 VQ_API int vq_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int64_t B,
                                 int d, float margin, float *loss, float *grad, int32_t *trip,
                                 void *stream);
+/* Diagnostics: groups of the last vq_triplet_batchhard call that the fused tensor-core kernel handed
+ * back to the CUDA-core path (candidate capacity exceeded); waits for the device. */
+VQ_API int vq_triplet_last_handed_back(void);
 VQ_API int vq_triplet_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T,
                             float margin, float *loss, float *grad, void *stream);
 

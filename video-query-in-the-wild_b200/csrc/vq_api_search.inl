@@ -437,6 +437,16 @@ int vq_pdist(const float *A, int64_t B, int d, float eps, float *dist, void *str
     return VQ_OK;
 }
 
+static int32_t *g_triplet_handed_back = nullptr;
+
+int vq_triplet_last_handed_back(void) {
+    int32_t h = 0;
+    if (!g_triplet_handed_back) return 0;
+    if (cudaDeviceSynchronize() != cudaSuccess || cudaMemcpy(&h, g_triplet_handed_back, 4, cudaMemcpyDeviceToHost) != cudaSuccess)
+        return VQ_ERR_CUDA;
+    return h;
+}
+
 int vq_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int64_t B, int d, float margin,
                          float *loss, float *grad, int32_t *trip, void *stream) {
     VQ_CHECK(emb && labels && loss, VQ_ERR_INVALID, "NULL argument");
@@ -459,8 +469,11 @@ int vq_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G, int
     }
     Tmp wk;
     VQ_TRY(wk.alloc((size_t)(G + 1) * 4, st));
+    VQ_CUDA(cudaMemsetAsync(wk.p, 0, 4, st));
     VQ_TRY(launch_triplet_batchhard(e.as<float>(), l.as<int32_t>(), G, B, d, margin, oL.as<float>(), oG.as<float>(),
                                     tdev, (float *)lt.p, (int32_t *)wk.p, st));
+    if (!g_triplet_handed_back) VQ_CUDA(cudaMalloc(&g_triplet_handed_back, 4));
+    VQ_CUDA(cudaMemcpyAsync(g_triplet_handed_back, wk.p, 4, cudaMemcpyDeviceToDevice, st));
     VQ_TRY(oL.finish(st));
     VQ_TRY(oG.finish(st));
     VQ_TRY(oT.finish(st));

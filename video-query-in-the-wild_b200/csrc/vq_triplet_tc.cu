@@ -17,9 +17,9 @@
 //           it (in triplet order), acc = fmaf(2/T, x_u - x_v, acc); written once, coalesced.
 //
 // Results are bit-identical to the CUDA-core path (vq_triplet.cu) and to the oracle whatever the
-// tensor cores rounded.  Groups that exceed a fixed capacity (more than 4 candidates for a role,
-// more than 64 candidate triples in a warp) are handed back through `bad_list` and recomputed by
-// the CUDA-core path.
+// tensor cores rounded.  Groups that exceed a fixed capacity (more than 8 candidates for a role,
+// more than 64 extra candidate pairs in a warp) are handed back through `bad_list` and recomputed
+// by the CUDA-core path.
 #include <stdlib.h>
 
 #include <algorithm>
@@ -35,9 +35,8 @@ static constexpr int TSTAGE = TB * TKB * 4;       // 32 KB
 static constexpr int TSTAGES = 5;
 static constexpr int TROWT = 256;                 // row threads (warps 2..9)
 static constexpr int TTHREADS = 64 + TROWT;
-static constexpr int TCAND = 4;                   // candidates kept per role and anchor
-static constexpr int TTRIP = 64;                  // candidate triples per warp
-static constexpr int TSLOTS = TTRIP / 4;
+static constexpr int TCAND = 8;                   // candidates kept per role and anchor
+static constexpr int TEXTRA = 64;                 // candidate pairs beyond the first of a role, per warp
 
 struct TcLayout {
     static constexpr int OFF_NRM = TSTAGES * TSTAGE;       // float[256]
@@ -45,9 +44,10 @@ struct TcLayout {
     static constexpr int OFF_TP = OFF_LAB + 1024;          // int[256] mined positive (-1: skipped anchor)
     static constexpr int OFF_TN = OFF_TP + 1024;           // int[256]
     static constexpr int OFF_LT = OFF_TN + 1024;           // float[256] per-anchor loss
-    static constexpr int OFF_TL = OFF_LT + 1024;           // uint32[8][64] candidate triples (a | j1<<8 | j2<<16)
-    static constexpr int OFF_RES = OFF_TL + 8 * TTRIP * 4;  // float4[8][64] (d2_1, prod_1, d2_2, prod_2)
-    static constexpr int OFF_EOFF = OFF_RES + 8 * TTRIP * 16;  // int[260] CSR offsets of the gradient gather lists
+    static constexpr int OFF_TL = OFF_LT + 1024;           // uint32[8][TEXTRA] extra candidate pairs (a | j<<8)
+    static constexpr int OFF_RES = OFF_TL + 8 * TEXTRA * 4;  // float4[8][32] primaries (d2_p, prod_p, d2_n, prod_n)
+    static constexpr int OFF_REX = OFF_RES + 8 * 32 * 16;    // float2[8][TEXTRA] extras (d2, prod)
+    static constexpr int OFF_EOFF = OFF_REX + 8 * TEXTRA * 8;  // int[260] CSR offsets of the gradient gather lists
     static constexpr int OFF_ECNT = OFF_EOFF + 1040;        // int[256] counters
     static constexpr int OFF_ENT = OFF_ECNT + 1024;         // uint16[768] entries
     static constexpr int OFF_MISC = OFF_ENT + 1536;         // int[16]
@@ -65,6 +65,7 @@ struct TripletTcParams {
     float *grad;     // [G,B,d] or null
     int32_t *trip;   // [G,B,3]
     int32_t *bad_count, *bad_list;
+    long long *dbg;  // optional [grid][8] phase clocks of the first group (VQ_DEBUG_TRIPLET_CLOCKS)
 };
 
 __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
@@ -134,6 +135,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
     float *s_lt = (float *)(smem + L::OFF_LT);
     uint32_t *s_tl = (uint32_t *)(smem + L::OFF_TL);
     float4 *s_res = (float4 *)(smem + L::OFF_RES);
+    float2 *s_rex = (float2 *)(smem + L::OFF_REX);
     int *s_eoff = (int *)(smem + L::OFF_EOFF);
     int *s_ecnt = (int *)(smem + L::OFF_ECNT);
     uint16_t *s_ent = (uint16_t *)(smem + L::OFF_ENT);
@@ -246,6 +248,8 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
         };
         for (int g = blockIdx.x; g < p.G; g += gridDim.x) {
             const bool rvalid = row < B;
+            long long tk[8];
+            tk[0] = clock64();
             // ---------------- pass 1: canonical |row|^2 from the stages the MMA reads ----------------
             float na = 0.f;
             for (int kb = 0; kb < KB; ++kb) {
@@ -260,6 +264,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 na = __fadd_rn(na, tc_tree8(t));
                 next_stage();
             }
+            tk[1] = clock64();
             s_nrm[row] = na;
             s_lab[row] = rvalid ? p.labels[(int64_t)g * B + row] : 0;
             s_ecnt[row] = 0;
@@ -280,6 +285,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             mbar_wait(tfull_bar, tphase);
             tphase ^= 1u;
             tc_fence_after();
+            tk[2] = clock64();
             float maxp = -INFINITY, minn = INFINITY;
 #pragma unroll 1
             for (int ch = 0; ch < TB / 32; ++ch) {
@@ -300,7 +306,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             const bool avalid = rvalid && maxp > -INFINITY && minn < INFINITY;
             const float thr_p = maxp < 1e-4f + 2.0f * eps ? -INFINITY : maxp - 2.0f * eps;  // clamp region: every positive ties
             const float thr_n = fmaxf(minn, 1e-4f) + 2.0f * eps;
-            uint32_t cpw = 0, cnw = 0;  // up to 4 candidate rows per role, one byte each, ascending row order
+            uint64_t cpw = 0, cnw = 0;  // up to 8 candidate rows per role, one byte each, ascending row order
             int ncp = 0, ncn = 0;
             if (__any_sync(0xffffffffu, avalid)) {
 #pragma unroll 1
@@ -316,11 +322,11 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                         const bool ok = avalid && j < B && j != row;
                         const bool same = s_lab[j] == la;
                         if (ok && same && cv >= thr_p) {
-                            if (ncp < TCAND) cpw |= (uint32_t)j << (8 * ncp);
+                            if (ncp < TCAND) cpw |= (uint64_t)j << (8 * ncp);
                             ++ncp;
                         }
                         if (ok && !same && cv <= thr_n) {
-                            if (ncn < TCAND) cnw |= (uint32_t)j << (8 * ncn);
+                            if (ncn < TCAND) cnw |= (uint64_t)j << (8 * ncn);
                             ++ncn;
                         }
                     }
@@ -329,45 +335,52 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar);  // TMEM may take the next group's Gram
+            tk[3] = clock64();
             bool bad = ncp > TCAND || ncn > TCAND;
             ncp = min(ncp, TCAND);
             ncn = min(ncn, TCAND);
 
-            // ---------------- candidate triples of this warp ----------------
-            int ntr = avalid ? max(ncp, ncn) : 0;
-            int incl = ntr;
+            // ---------------- work items of pass 2 ----------------
+            // primary triple of every anchor (row, first positive candidate, first negative candidate): kept in
+            // a register and fetched by shuffle; further candidates go to the warp's list of extra pairs
+            const uint32_t prim = avalid ? ((uint32_t)row | ((uint32_t)(cpw & 255u) << 8) | ((uint32_t)(cnw & 255u) << 16))
+                                         : ((uint32_t)row * 0x010101u);
+            int nex = avalid ? (ncp - 1) + (ncn - 1) : 0;
+            int incl = nex;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int v = __shfl_up_sync(0xffffffffu, incl, o);
                 if (lane >= o) incl += v;
             }
-            int total = __shfl_sync(0xffffffffu, incl, 31);
-            const int off = incl - ntr;
-            if (total > TTRIP) {  // warp-uniform
+            int nex_total = __shfl_sync(0xffffffffu, incl, 31);
+            const int exoff = incl - nex;
+            if (nex_total > TEXTRA) {  // warp-uniform
                 bad = true;
-                total = 0;
-                ntr = 0;
+                nex_total = 0;
+                nex = 0;
             }
             if (__any_sync(0xffffffffu, bad) && lane == 0) s_misc[2] = 1;
-            for (int t = 0; t < ntr; ++t) {
-                const uint32_t j1 = t < ncp ? (cpw >> (8 * t)) & 255u : (uint32_t)row;
-                const uint32_t j2 = t < ncn ? (cnw >> (8 * t)) & 255u : (uint32_t)row;
-                s_tl[rw * TTRIP + off + t] = (uint32_t)row | (j1 << 8) | (j2 << 16);
+            if (nex > 0) {
+                int w = exoff;
+                for (int t = 1; t < ncp; ++t) s_tl[rw * TEXTRA + w++] = (uint32_t)row | ((uint32_t)((cpw >> (8 * t)) & 255u) << 8);
+                for (int t = 1; t < ncn; ++t) s_tl[rw * TEXTRA + w++] = (uint32_t)row | ((uint32_t)((cnw >> (8 * t)) & 255u) << 8);
             }
+            const bool wvalid = __any_sync(0xffffffffu, avalid);
             __syncwarp();
 
             // ---------------- pass 2: canonical chains of the candidate pairs ----------------
-            float a_d1[TSLOTS], a_p1[TSLOTS], a_d2[TSLOTS], a_p2[TSLOTS];
+            float a_d1[8], a_p1[8], a_d2[8], a_p2[8], x_d[TEXTRA / 4], x_p[TEXTRA / 4];
 #pragma unroll
-            for (int i = 0; i < TSLOTS; ++i) a_d1[i] = a_p1[i] = a_d2[i] = a_p2[i] = 0.f;
+            for (int i = 0; i < 8; ++i) a_d1[i] = a_p1[i] = a_d2[i] = a_p2[i] = 0.f;
+#pragma unroll
+            for (int i = 0; i < TEXTRA / 4; ++i) x_d[i] = x_p[i] = 0.f;
             for (int kb = 0; kb < KB; ++kb) {
                 mbar_wait(&full_bar[stage], phase);
                 const uint8_t *sp = smem + stage * TSTAGE;
+                if (wvalid) {
 #pragma unroll
-                for (int i = 0; i < TSLOTS; ++i) {
-                    if (4 * i < total) {  // warp-uniform
-                        const int idx = 4 * i + m;
-                        const uint32_t e = idx < total ? s_tl[rw * TTRIP + idx] : 0u;
+                    for (int i = 0; i < 8; ++i) {  // primary triple of lane 4*i + m
+                        const uint32_t e = __shfl_sync(0xffffffffu, prim, 4 * i + m);
                         const int ra = e & 255u, r1 = (e >> 8) & 255u, r2 = (e >> 16) & 255u;
                         const float4 xa = tc_ld_chunk(sp, ra, c), x1 = tc_ld_chunk(sp, r1, c), x2 = tc_ld_chunk(sp, r2, c);
                         a_d1[i] = __fadd_rn(a_d1[i], tc_tree8_shfl(tc_sq4(xa, x1)));
@@ -375,47 +388,67 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                         a_d2[i] = __fadd_rn(a_d2[i], tc_tree8_shfl(tc_sq4(xa, x2)));
                         a_p2[i] = __fadd_rn(a_p2[i], tc_tree8_shfl(tc_dot4(xa, x2)));
                     }
+#pragma unroll
+                    for (int i = 0; i < TEXTRA / 4; ++i) {
+                        if (4 * i < nex_total) {  // warp-uniform
+                            const int idx = 4 * i + m;
+                            const uint32_t e = idx < nex_total ? s_tl[rw * TEXTRA + idx] : 0u;
+                            const int ra = e & 255u, r1 = (e >> 8) & 255u;
+                            const float4 xa = tc_ld_chunk(sp, ra, c), x1 = tc_ld_chunk(sp, r1, c);
+                            x_d[i] = __fadd_rn(x_d[i], tc_tree8_shfl(tc_sq4(xa, x1)));
+                            x_p[i] = __fadd_rn(x_p[i], tc_tree8_shfl(tc_dot4(xa, x1)));
+                        }
+                    }
                 }
                 next_stage();
             }
 #pragma unroll
-            for (int i = 0; i < TSLOTS; ++i) {
+            for (int i = 0; i < 8; ++i)
+                if (c == 0) s_res[rw * 32 + 4 * i + m] = make_float4(a_d1[i], a_p1[i], a_d2[i], a_p2[i]);
+#pragma unroll
+            for (int i = 0; i < TEXTRA / 4; ++i) {
                 const int idx = 4 * i + m;
-                if (c == 0 && idx < total) s_res[rw * TTRIP + idx] = make_float4(a_d1[i], a_p1[i], a_d2[i], a_p2[i]);
+                if (c == 0 && idx < nex_total) s_rex[rw * TEXTRA + idx] = make_float2(x_d[i], x_p[i]);
             }
             __syncwarp();
+            tk[4] = clock64();
 
             // ---------------- exact decision among the candidates, per-anchor loss ----------------
             int fp = -1, fn = -1;
             float lterm = 0.f;
-            if (ntr > 0) {
-                const float4 *rs = s_res + rw * TTRIP + off;
+            if (avalid) {  // (a group with a capacity overflow is recomputed by the CUDA-core path anyway)
+                const float4 pr = s_res[rw * 32 + lane];
+                const float2 *rx = s_rex + rw * TEXTRA + exoff;
+                // candidate t of a role: t == 0 the primary, t >= 1 the extras in list order
                 int bq = 0;
-                if (ncp > 1) {
-                    float bd = 0.f;
-                    for (int t = 0; t < ncp; ++t) {
-                        const float dist = tc_pdist(na, s_nrm[(cpw >> (8 * t)) & 255u], rs[t].y, 1e-4f);
-                        if (t == 0 || dist > bd) {  // ascending row order: the first maximum wins
+                float d2p = pr.x;
+                if (ncp > 1 && nex > 0) {
+                    float bd = tc_pdist(na, s_nrm[cpw & 255u], pr.y, 1e-4f);
+                    for (int t = 1; t < ncp; ++t) {
+                        const float dist = tc_pdist(na, s_nrm[(cpw >> (8 * t)) & 255u], rx[t - 1].y, 1e-4f);
+                        if (dist > bd) {  // ascending row order: the first maximum wins
                             bd = dist;
                             bq = t;
+                            d2p = rx[t - 1].x;
                         }
                     }
                 }
                 fp = (int)((cpw >> (8 * bq)) & 255u);
-                const float d2p = rs[bq].x;
                 bq = 0;
-                if (ncn > 1) {
-                    float bd = 0.f;
-                    for (int t = 0; t < ncn; ++t) {
-                        const float dist = tc_pdist(na, s_nrm[(cnw >> (8 * t)) & 255u], rs[t].w, 1e-4f);
-                        if (t == 0 || dist < bd) {
+                float d2n = pr.z;
+                if (ncn > 1 && nex > 0) {
+                    const float2 *rn = rx + (ncp - 1);
+                    float bd = tc_pdist(na, s_nrm[cnw & 255u], pr.w, 1e-4f);
+                    for (int t = 1; t < ncn; ++t) {
+                        const float dist = tc_pdist(na, s_nrm[(cnw >> (8 * t)) & 255u], rn[t - 1].y, 1e-4f);
+                        if (dist < bd) {
                             bd = dist;
                             bq = t;
+                            d2n = rn[t - 1].x;
                         }
                     }
                 }
                 fn = (int)((cnw >> (8 * bq)) & 255u);
-                const float d2n = rs[bq].z;
                 const float v = __fadd_rn(__fsub_rn(d2p, d2n), p.margin);
                 lterm = v > 0.f ? v : 0.f;
             }
@@ -495,6 +528,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             named_bar_sync(1, TROWT);
             const int T = s_misc[1];
             const float scale = T > 0 ? __fdiv_rn(2.0f, (float)T) : 0.f;
+            tk[5] = clock64();
 
             // ---------------- pass 3: gradient rows, 8 lanes x 16 bytes per row block ----------------
             for (int kb = 0; kb < KB; ++kb) {
@@ -522,6 +556,9 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 next_stage();
             }
             if (threadIdx.x == 64 && s_misc[2]) p.bad_list[atomicAdd(p.bad_count, 1)] = g;
+            tk[6] = clock64();
+            if (p.dbg && threadIdx.x == 64 && g == (int)blockIdx.x)
+                for (int i = 0; i < 7; ++i) p.dbg[blockIdx.x * 8 + i] = tk[i];
             named_bar_sync(1, TROWT);  // shared lists are rebuilt by the next group
         }
     }
@@ -555,10 +592,21 @@ int launch_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G,
     TripletTcParams p{};
     p.labels = labels; p.G = (int)G; p.B = (int)B; p.d = d; p.margin = margin;
     p.loss = loss; p.grad = grad; p.trip = trip; p.bad_count = work; p.bad_list = work + 1;
+    static long long *dbg_buf = nullptr;
+    if (getenv("VQ_DEBUG_TRIPLET_CLOCKS")) {
+        if (!dbg_buf) VQ_CUDA(cudaMalloc(&dbg_buf, 148 * 8 * 8));
+        p.dbg = dbg_buf;
+    }
     VQ_CUDA(cudaFuncSetAttribute(triplet_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TcLayout::TOTAL));
     const int grid = (int)std::min<int64_t>(G, g_tc_grid);
     triplet_tc_kernel<<<grid, TTHREADS, TcLayout::TOTAL, st>>>(tm, p);
     VQ_CUDA(cudaGetLastError());
+    if (p.dbg) {
+        long long h[8];
+        VQ_CUDA(cudaMemcpy(h, p.dbg, 64, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "triplet_tc clocks (CTA 0, first group): pass1 %lld  wait_gram %lld  mine %lld  pass2 %lld  lists %lld  pass3 %lld\n",
+                h[1] - h[0], h[2] - h[1], h[3] - h[2], h[4] - h[3], h[5] - h[4], h[6] - h[5]);
+    }
     // groups handed back (capacity overflow): CUDA-core path over the device list, a few resident blocks
     return launch_triplet_batchhard_simt(emb, labels, std::min<int64_t>(G, 8), B, d, margin, loss, grad, trip, scratch,
                                          work + 1, work, st);
