@@ -361,7 +361,10 @@ def run_b200(a):
 
     for _ in range(max(1, min(a.warmup, 2))):
         step_e2e()
-    e2e_ms, _, _ = timed(step_e2e, a.steps)
+    e2e_gemm_ms = []
+    sampler = ClockSampler(local) if rank == 0 else None
+    e2e_ms, t0, t1 = timed(step_e2e, a.steps, lambda: e2e_gemm_ms.append(index.last_timing()["gemm_topk_ms"]))
+    e2e_clocks = sampler.stop(t0, t1) if sampler else None
 
     pairs = float(a.nq) * float(a.n)
     ms_per_step = total_ms / a.steps
@@ -401,7 +404,9 @@ def run_b200(a):
                    "l2_policy": "inputs larger than L2 (gallery shard %.1f GB per rank)" % ((r1 - r0) * a.d * 2 / 1e9),
                    "tie_break": "d2 ascending, lowest gallery row first", "result": "canonical fp32 d2, verified top-k"},
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": a.nq * a.d * 2,
-                "d2h_bytes_per_step": a.nq * k * 12, "ms_per_step": e2e_ms / a.steps},
+                "d2h_bytes_per_step": a.nq * k * 12, "ms_per_step": e2e_ms / a.steps,
+                "gemm_topk_ms": sum(e2e_gemm_ms) / len(e2e_gemm_ms),
+                "sm_mhz": e2e_clocks["sm_mhz"] if e2e_clocks else None},
         "gpu_launches": (stats["launches"] + (1 if G > 1 else 0)) * a.steps,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                      "traffic": traffic, "kernel": "gemm_topk_pair_kernel<false> (cta_group::2)", "kernel_ms": g_ms,

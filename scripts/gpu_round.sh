@@ -22,3 +22,11 @@ timeout -s KILL 900 ncu --set full --clock-control none --import-source on -k re
     -f -o gpurun_out/prof_gemm_topk $PCMD > gpurun_out/ncu_full.log 2>&1
 echo "ncu full exit $?" | tee -a gpurun_out/status.log
 cat gpurun_out/plain_prof.log | tail -2
+# kernel (3): batched batch-hard triplet timing + phase clocks + one ncu --set full capture
+timeout -s KILL 300 python scripts/time_triplet.py > gpurun_out/time_triplet.log 2>&1
+echo "time_triplet exit $?" | tee -a gpurun_out/status.log
+cat gpurun_out/time_triplet.log
+timeout -s KILL 300 python scripts/clk_triplet.py > gpurun_out/clk_triplet.log 2>&1
+timeout -s KILL 600 ncu --set full --clock-control none --import-source on -k regex:triplet_tc -s 3 -c 1 \
+    -f -o gpurun_out/prof_triplet_tc python scripts/time_triplet.py > gpurun_out/ncu_full_triplet.log 2>&1
+echo "ncu triplet exit $?" | tee -a gpurun_out/status.log
