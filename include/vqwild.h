@@ -124,6 +124,26 @@ VQ_API int vq_index_eval_trimmed(vq_index *ix, const void *xq, int64_t nq, int d
                                  int n_ignore, double *ap, double *recall, int64_t *top_idx,
                                  void *stream);
 
+/* ------------------------------------------------------------------------------------
+ * a8. Moment retrieval evaluation: the per-query body of ARV_Retrieval_Moment.ranking
+ * (dataloader_baseline.py:1225-1330) = labelling (:1239-1261) + ranking of ALL moments
+ * (:1268-1281) + do_nms (:1283-1312: cluster by video in first-seen order, nms_cpu per cluster)
+ * + tp = IoU >= 0.5 (:1315-1319) + multiprocess_calculate (:386-402) on the grouped list.
+ *   vq_index_set_moments  per gallery row (host or device, [ntotal]): start_sec, end_sec (f32),
+ *                         closest_hit IoU (f32; 0 when there is no hit) and closest_hit label id
+ *                         (int32; -1 when there is none).  Requires vq_index_set_segments (one
+ *                         segment per video, <= 4096 moments each) and vq_index_set_meta (video).
+ *   vq_index_eval_moment  q_label int32[nq], ignore_video int32[nq,n_ignore];
+ *                         ap float64[nq], recall float64[nq,3]; optional n_kept int64[nq] (moments
+ *                         surviving NMS, before the ignore rule) and kept_mask uint8[nq,ntotal].
+ * ---------------------------------------------------------------------------------- */
+VQ_API int vq_index_set_moments(vq_index *ix, const float *start_sec, const float *end_sec,
+                                const float *iou, const int32_t *hit_label, void *stream);
+VQ_API int vq_index_eval_moment(vq_index *ix, const void *xq, int64_t nq, int dtype,
+                                const int32_t *q_label, const int32_t *ignore_video, int n_ignore,
+                                double nms_thresh, double *ap, double *recall, int64_t *n_kept,
+                                uint8_t *kept_mask, void *stream);
+
 /* sklearn.metrics.average_precision_score for a batch of lists (dataloader_baseline.py:391,
  * :461): lists are concatenated, list s = [offsets[s], offsets[s+1]).  y_true int32, y_score
  * float64 (any order; sorted internally, ties grouped).  host or device; ap float64[nlists]. */

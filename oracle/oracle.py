@@ -167,6 +167,25 @@ def eval_moment(q, g, g_video, g_start, g_end, g_iou, g_hit_label, q_label, q_ig
     return ap, rec
 
 
+def eval_moment_kept(q1, g, g_video, g_start, g_end, g_iou, g_hit_label, q_label, ignore_vids, nms_thresh=0.5):
+    """One query: (ap, recall[3], kept) with kept = the grouped, NMS-kept gallery rows in list order."""
+    q1, g = _f32(q1).reshape(1, -1), _f32(g)
+    n = g.shape[0]
+    D, I = search(q1, g, n)
+    order, d2 = np.ascontiguousarray(I[0]), np.ascontiguousarray(D[0])
+    gv, gs, ge = _i32(g_video), _f32(g_start), _f32(g_end)
+    gi, gh = _f32(g_iou), _i32(g_hit_label)
+    ig = _i32(ignore_vids).reshape(-1)
+    ap = C.c_double()
+    rec = np.empty(3, np.float64)
+    kept = np.empty(n, np.int64)
+    nk = C.c_int64()
+    lib().orc_eval_moment_ranked(_p(order), _p(d2), C.c_int64(n), _p(gv), _p(gs), _p(ge), _p(gi), _p(gh),
+                                 C.c_int32(int(q_label)), _p(ig), C.c_int(ig.shape[0]), C.c_double(nms_thresh),
+                                 C.byref(ap), _p(rec), _p(kept), C.byref(nk))
+    return ap.value, rec, kept[:nk.value]
+
+
 def segmax_topk(q, g, seg_start, k):
     q, g = _f32(q), _f32(g)
     ss = _i64(seg_start)

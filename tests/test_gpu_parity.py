@@ -187,6 +187,92 @@ def test_segmax_topk(vq, ragged):
     assert np.array_equal(D.view(np.uint32), Do.view(np.uint32))
 
 
+def _seg_of(video):
+    chg = np.flatnonzero(np.diff(video)) + 1
+    return np.concatenate([[0], chg, [len(video)]]).astype(np.int64)
+
+
+def test_eval_moment_golden(vq, golden):
+    """ARV_Retrieval_Moment.ranking (forked workers, do_nms, grouped R@N) as run by the reference."""
+    rows = golden["mo_q_list_rows"]
+    q = np.ascontiguousarray(golden["mo_qfeat"][rows[:, 0]])
+    ql = golden["mo_qlabel"][rows[:, 0]]
+    ign = golden["mo_qvideo"][rows]
+    ix = vq.IndexFlatL2(q.shape[1])
+    ix.add(golden["mo_feat"])
+    ix.set_meta(golden["mo_hit"], golden["mo_video"])
+    ix.set_segments(_seg_of(golden["mo_video"]))
+    ix.set_moments(golden["mo_start"], golden["mo_end"], golden["mo_iou"], golden["mo_hit"])
+    ap, rec, nk, km = ix.eval_moment(q, ql, ign, want_kept=True)
+    np.testing.assert_allclose(ap, golden["mo_ap"], rtol=0, atol=1e-9)
+    apo, reco = orc.eval_moment(q, golden["mo_feat"], golden["mo_video"], golden["mo_start"], golden["mo_end"],
+                                golden["mo_iou"], golden["mo_hit"], ql, ign)
+    np.testing.assert_allclose(ap, apo, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-12)
+    # aggregated exactly as the reference's get_result
+    names = [str(x) for x in golden["label_names"]]
+    cls = [names[i] for i in ql]
+    typ = ["base" if i < 6 else "novel" for i in ql]  # make_golden: 6 train + 5 test labels
+    ev = vq.evaluation_metric(None, [[{"label": c, "retrieval_type": t}] for c, t in zip(cls, typ)])
+    ev.update_arrays(cls, typ, ap, rec)
+    res = ev.get_result()
+    np.testing.assert_allclose([res["ap"], res["base_map"], res["novel_map"]], golden["mo_result"], rtol=0, atol=1e-9)
+    got = np.array([[res[k][str(n)] for n in (30, 50, 100)] for k in ("recall", "base_recall", "novel_recall")])
+    np.testing.assert_allclose(got, golden["mo_recall"], rtol=0, atol=1e-9)
+    for i in (0, 7, 33):
+        _, _, kept = orc.eval_moment_kept(q[i], golden["mo_feat"], golden["mo_video"], golden["mo_start"],
+                                          golden["mo_end"], golden["mo_iou"], golden["mo_hit"], ql[i], ign[i])
+        assert nk[i] == len(kept) and np.array_equal(np.flatnonzero(km[i]), np.sort(kept))
+
+
+@pytest.mark.parametrize("case", ["uniform64", "ragged", "large_videos", "ties"])
+def test_eval_moment_random(vq, case):
+    rng = np.random.default_rng({"uniform64": 1, "ragged": 2, "large_videos": 3, "ties": 4}[case])
+    d, nq, ncls = 64, 40, 12
+    if case == "uniform64":
+        lens = np.full(150, 64)
+    elif case == "large_videos":
+        lens = np.array([700, 3, 300, 257, 256, 1, 1200, 40])
+    else:
+        lens = rng.integers(1, 120, 90)
+    seg_start = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    n, nv = int(seg_start[-1]), len(lens)
+    video = np.repeat(np.arange(nv), lens).astype(np.int32) + 100
+    # sliding windows: start = 5 * s, length in {5, 10, ..., 130}
+    start = (5 * rng.integers(0, 60, n)).astype(np.float32)
+    end = start + (5 * rng.integers(1, 27, n)).astype(np.float32)
+    hit = rng.integers(-1, ncls, n).astype(np.int32)
+    iou = np.where(hit >= 0, rng.uniform(0, 1, n), 0).astype(np.float32)
+    iou[rng.random(n) < 0.05] = 0.5  # the >= boundary
+    g = _emb(rng, n, d)
+    if case == "ties":  # exact duplicate rows inside and across videos, duplicate windows
+        g[5:40] = g[0]
+        g[seg_start[3]:seg_start[3] + 5] = g[0]
+        start[5:20], end[5:20] = start[5], end[5]
+    q = _emb(rng, nq, d)
+    q[0] = g[seg_start[2]]
+    ql = rng.integers(0, ncls, nq).astype(np.int32)
+    ign = (rng.integers(0, nv, (nq, 5)) + 100).astype(np.int32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    ix.set_meta(hit, video)
+    ix.set_segments(seg_start)
+    ix.set_moments(start, end, iou, hit)
+    ap, rec, nk, km = ix.eval_moment(q, ql, ign, want_kept=True)
+    apo, reco = orc.eval_moment(q, g, video, start, end, iou, hit, ql, ign)
+    np.testing.assert_allclose(ap, apo, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-12)
+    for i in range(0, nq, 9):
+        _, _, kept = orc.eval_moment_kept(q[i], g, video, start, end, iou, hit, ql[i], ign[i])
+        assert nk[i] == len(kept) and np.array_equal(np.flatnonzero(km[i]), np.sort(kept))
+    # no ignore list, device-resident inputs, other NMS threshold
+    import torch
+    ap2, rec2, _, _ = ix.eval_moment(torch.from_numpy(q).cuda(), torch.from_numpy(ql).cuda(), None, nms_thresh=0.3)
+    apo2, reco2 = orc.eval_moment(q, g, video, start, end, iou, hit, ql, np.full((nq, 1), -7, np.int32), nms_thresh=0.3)
+    np.testing.assert_allclose(ap2.cpu().numpy(), apo2, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(rec2.cpu().numpy(), reco2, rtol=0, atol=1e-12)
+
+
 def _golden_trimmed(golden, query_num=1):
     feat, rows = golden["tr_feat"], golden["tr_q_list_rows"]
     acc = np.zeros((rows.shape[0], feat.shape[1]), np.float32)
@@ -234,6 +320,31 @@ def test_arv_retrieval_mirror_golden(vq, golden):
     np.testing.assert_allclose([res["ap"], res["base_map"], res["novel_map"]], golden["tr_result"], rtol=0, atol=1e-9)
     got = np.array([[res[k][str(n)] for n in (30, 50, 100)] for k in ("recall", "base_recall", "novel_recall")])
     np.testing.assert_allclose(got, golden["tr_recall"], rtol=0, atol=1e-9)
+
+
+def test_arv_retrieval_moment_mirror_golden(vq, golden):
+    """List-of-dict surface of ARV_Retrieval_Moment.ranking -> the reference's map05 dict."""
+    names = [str(x) for x in golden["label_names"]]
+    mom = []
+    for i in range(golden["mo_feat"].shape[0]):
+        h = int(golden["mo_hit"][i])
+        mom.append(dict(video_id="u_%03d" % golden["mo_video"][i], start_sec=float(golden["mo_start"][i]),
+                        end_sec=float(golden["mo_end"][i]), feat=golden["mo_feat"][i],
+                        closest_hit=None if h < 0 else dict(label=names[h], iou=float(golden["mo_iou"][i]))))
+    mq = [dict(label=names[golden["mo_qlabel"][i]], video_id="u_%03d" % golden["mo_qvideo"][i],
+               feat=golden["mo_qfeat"][i], qrow=i, retrieval_type="base" if golden["mo_qlabel"][i] < 6 else "novel")
+          for i in range(golden["mo_qfeat"].shape[0])]
+
+    class A:
+        query_num = 1
+        debug = False
+
+    ev = vq.ARV_Retrieval_Moment(A(), query_list=mq, gallery_list=mom)
+    res = ev.ranking()["map05"]
+    assert [[x["qrow"] for x in ql] for ql in ev.query_list] == golden["mo_q_list_rows"].tolist()
+    np.testing.assert_allclose([res["ap"], res["base_map"], res["novel_map"]], golden["mo_result"], rtol=0, atol=1e-9)
+    got = np.array([[res[k][str(n)] for n in (30, 50, 100)] for k in ("recall", "base_recall", "novel_recall")])
+    np.testing.assert_allclose(got, golden["mo_recall"], rtol=0, atol=1e-9)
 
 
 def test_eval_trimmed_random_with_ties(vq):

@@ -90,6 +90,15 @@ def as_i32(x):
     return np.ascontiguousarray(x, dtype=np.int32)
 
 
+def as_f32(x):
+    if x is None:
+        return None
+    if _is_torch(x):
+        import torch
+        return x.to(torch.float32).contiguous()
+    return np.ascontiguousarray(x, dtype=np.float32)
+
+
 def empty_like_kind(ref, shape, dtype):
     """Output buffer living where `ref` lives (torch CUDA tensor -> CUDA tensor, else numpy)."""
     if _is_torch(ref):

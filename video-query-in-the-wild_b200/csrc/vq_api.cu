@@ -183,6 +183,12 @@ struct vq_index {
     int32_t *seg_of_row = nullptr;  // [n]
     int64_t *seg_start_dev = nullptr;
     std::vector<int64_t> seg_start;  // host copy
+    // moment evaluation (a8): per-row moment metadata, videos split by size class for the NMS kernel
+    float *m_start = nullptr, *m_end = nullptr, *m_iou = nullptr;
+    int32_t *m_hit = nullptr;
+    int32_t *seg_small = nullptr, *seg_large = nullptr;
+    int n_seg_small = 0, n_seg_large = 0;
+    int64_t seg_max_len = 0;
     // search workspace (grown on demand)
     uint64_t *cand = nullptr;
     size_t cand_bytes = 0;
@@ -249,7 +255,8 @@ int vq_index_destroy(vq_index *ix) {
     cudaDeviceSynchronize();
     void *ptrs[] = {ix->raw,   ix->hi,         ix->lo,           ix->norm2,    ix->gmax_bits,
                     ix->label, ix->video,      ix->seg_of_row,   ix->seg_start_dev, ix->cand,     ix->cand_cnt,
-                    ix->cand_tau, ix->plan_rows_dev, ix->plan_ints_dev, ix->unproven, ix->unproven_count};
+                    ix->cand_tau, ix->plan_rows_dev, ix->plan_ints_dev, ix->unproven, ix->unproven_count,
+                    ix->m_start, ix->m_end, ix->m_iou, ix->m_hit, ix->seg_small, ix->seg_large};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (ix->stat_pinned) cudaFreeHost(ix->stat_pinned);
@@ -322,6 +329,8 @@ int vq_index_add(vq_index *ix, const void *xb, int64_t n, int dtype, void *strea
     if (ix->video) { cudaFree(ix->video); ix->video = nullptr; }
     if (ix->seg_of_row) { cudaFree(ix->seg_of_row); ix->seg_of_row = nullptr; }
     ix->seg_start.clear();
+    for (void **pp : {(void **)&ix->m_start, (void **)&ix->m_end, (void **)&ix->m_iou, (void **)&ix->m_hit})
+        if (*pp) { cudaFree(*pp); *pp = nullptr; }
     return VQ_OK;
 }
 
@@ -362,7 +371,43 @@ int vq_index_set_segments(vq_index *ix, const int64_t *seg_start, int64_t nseg, 
     VQ_CUDA(cudaMalloc(&ix->seg_start_dev, (size_t)(nseg + 1) * 8));
     VQ_CUDA(cudaMemcpyAsync(ix->seg_of_row, sor.data(), (size_t)ix->n * 4, cudaMemcpyHostToDevice, st));
     VQ_CUDA(cudaMemcpyAsync(ix->seg_start_dev, seg_start, (size_t)(nseg + 1) * 8, cudaMemcpyHostToDevice, st));
-    VQ_CUDA(cudaStreamSynchronize(st));  // sor is a stack-lifetime staging buffer
+    // size classes for the per-video NMS (vq_moment.cu)
+    std::vector<int32_t> small, large;
+    ix->seg_max_len = 0;
+    for (int64_t v = 0; v < nseg; ++v) {
+        const int64_t len = seg_start[v + 1] - seg_start[v];
+        ix->seg_max_len = std::max(ix->seg_max_len, len);
+        (len <= kMomentWarpCap ? small : large).push_back((int32_t)v);
+    }
+    if (ix->seg_small) { cudaFree(ix->seg_small); ix->seg_small = nullptr; }
+    if (ix->seg_large) { cudaFree(ix->seg_large); ix->seg_large = nullptr; }
+    ix->n_seg_small = (int)small.size();
+    ix->n_seg_large = (int)large.size();
+    if (!small.empty()) {
+        VQ_CUDA(cudaMalloc(&ix->seg_small, small.size() * 4));
+        VQ_CUDA(cudaMemcpyAsync(ix->seg_small, small.data(), small.size() * 4, cudaMemcpyHostToDevice, st));
+    }
+    if (!large.empty()) {
+        VQ_CUDA(cudaMalloc(&ix->seg_large, large.size() * 4));
+        VQ_CUDA(cudaMemcpyAsync(ix->seg_large, large.data(), large.size() * 4, cudaMemcpyHostToDevice, st));
+    }
+    VQ_CUDA(cudaStreamSynchronize(st));  // sor / small / large are stack-lifetime staging buffers
+    return VQ_OK;
+}
+
+int vq_index_set_moments(vq_index *ix, const float *start_sec, const float *end_sec, const float *iou,
+                         const int32_t *hit_label, void *stream) {
+    VQ_CHECK(ix && start_sec && end_sec && iou && hit_label, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(ix->n > 0, VQ_ERR_STATE, "vq_index_set_moments before vq_index_add");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t bytes = (size_t)ix->n * 4;
+    const void *src[4] = {start_sec, end_sec, iou, hit_label};
+    void **dst[4] = {(void **)&ix->m_start, (void **)&ix->m_end, (void **)&ix->m_iou, (void **)&ix->m_hit};
+    for (int i = 0; i < 4; ++i) {
+        if (*dst[i]) { cudaFree(*dst[i]); *dst[i] = nullptr; }
+        VQ_CUDA(cudaMalloc(dst[i], bytes));
+        VQ_CUDA(cudaMemcpyAsync(*dst[i], src[i], bytes, cudaMemcpyDefault, st));
+    }
     return VQ_OK;
 }
 

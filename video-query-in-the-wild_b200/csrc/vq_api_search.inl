@@ -375,6 +375,76 @@ int vq_index_eval_trimmed(vq_index *ix, const void *xq, int64_t nq, int dtype, c
     return VQ_OK;
 }
 
+int vq_index_eval_moment(vq_index *ix, const void *xq, int64_t nq, int dtype, const int32_t *q_label,
+                         const int32_t *ignore_video, int n_ignore, double nms_thresh, double *ap, double *recall,
+                         int64_t *n_kept, uint8_t *kept_mask, void *stream) {
+    VQ_TRY(check_search_args(ix, xq, nq, dtype, 1));
+    VQ_CHECK(q_label && ap && recall, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(ix->m_start, VQ_ERR_STATE, "vq_index_set_moments has not been called");
+    VQ_CHECK(!ix->seg_start.empty() && ix->seg_of_row, VQ_ERR_STATE, "vq_index_set_segments has not been called");
+    VQ_CHECK(ix->video, VQ_ERR_STATE, "vq_index_set_meta (video ids) has not been called");
+    VQ_CHECK(ix->seg_max_len <= kMomentBlockCap, VQ_ERR_CAPACITY, "a video has %lld moments (max %d)",
+             (long long)ix->seg_max_len, kMomentBlockCap);
+    VQ_CHECK(n_ignore >= 0 && n_ignore <= kMaxIgnore, VQ_ERR_INVALID, "n_ignore=%d (max %d)", n_ignore, kMaxIgnore);
+    const int n_ign = ignore_video ? n_ignore : 0;
+    if (nq == 0) return VQ_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t nseg = (int64_t)ix->seg_start.size() - 1;
+    In q, ql, ig;
+    Out oA, oR, oN, oK;
+    VQ_TRY(q.bind(xq, (size_t)nq * ix->d * esize(dtype), st));
+    VQ_TRY(ql.bind(q_label, (size_t)nq * 4, st));
+    VQ_TRY(ig.bind(ignore_video, (size_t)nq * n_ign * 4, st));
+    VQ_TRY(oA.bind(ap, (size_t)nq * 8, st));
+    VQ_TRY(oR.bind(recall, (size_t)nq * 3 * 8, st));
+    VQ_TRY(oN.bind(n_kept, (size_t)nq * 8, st));
+    VQ_TRY(oK.bind(kept_mask, (size_t)nq * ix->n, st));
+    int64_t tile_q = std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(1ll << 31) / std::max<int64_t>(1, ix->n * 4)));
+    tile_q = std::min<int64_t>(tile_q, 32768);  // grid.y of the NMS kernel
+    Tmp d2, kept, vbest, ovf;
+    VQ_TRY(d2.alloc((size_t)tile_q * ix->n * 4, st));
+    if (!kept_mask) VQ_TRY(kept.alloc((size_t)tile_q * ix->n, st));
+    VQ_TRY(vbest.alloc((size_t)tile_q * nseg * 8, st));
+    VQ_TRY(ovf.alloc(4, st));
+    int launches = 0;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        const int pcap2 = attempt == 0 ? 1024 : kMaxPositives;
+        VQ_CUDA(cudaMemsetAsync(ovf.p, 0, 4, st));
+        for (int64_t q0 = 0; q0 < nq; q0 += tile_q) {
+            const int64_t tq = std::min(tile_q, nq - q0);
+            const char *qt = (const char *)q.dev + (size_t)q0 * ix->d * esize(dtype);
+            uint8_t *kp = kept_mask ? oK.as<uint8_t>() + (size_t)q0 * ix->n : (uint8_t *)kept.p;
+            VQ_TRY(launch_l2sq_all(qt, ix->raw, dtype, tq, ix->n, ix->d, (float *)d2.p, st));
+            MomentNmsParams m{};
+            m.nq_tile = tq; m.n = ix->n; m.nseg = nseg; m.d2 = (const float *)d2.p; m.seg_start = ix->seg_start_dev;
+            m.start = ix->m_start; m.end = ix->m_end; m.thresh = nms_thresh; m.kept = kp; m.vbest = (uint64_t *)vbest.p;
+            VQ_TRY(launch_moment_nms(m, ix->seg_small, ix->n_seg_small, ix->seg_large, ix->n_seg_large, st));
+            ApRowsParams a{};
+            a.nq_tile = tq; a.n = ix->n; a.d2 = (const float *)d2.p; a.g_label = ix->m_hit; a.g_video = ix->video;
+            a.q_label = ql.as<int32_t>() + q0;
+            a.q_ignore = n_ign ? ig.as<int32_t>() + q0 * n_ign : nullptr;
+            a.n_ign = n_ign; a.ap = oA.as<double>() + q0; a.recall = oR.as<double>() + q0 * 3;
+            a.top_idx = nullptr; a.overflow = (int32_t *)ovf.p;
+            a.kept = kp; a.g_iou = ix->m_iou; a.vbest = (uint64_t *)vbest.p; a.seg_start = ix->seg_start_dev;
+            a.seg_of_row = ix->seg_of_row; a.nseg = nseg; a.n_kept = n_kept ? oN.as<int64_t>() + q0 : nullptr;
+            VQ_TRY(launch_ap_rows(a, pcap2, st));
+            launches += 2 + (ix->n_seg_small > 0) + (ix->n_seg_large > 0);
+        }
+        int32_t h = 0;
+        VQ_CUDA(cudaMemcpyAsync(&h, ovf.p, 4, cudaMemcpyDeviceToHost, st));
+        VQ_CUDA(cudaStreamSynchronize(st));
+        if (!h) break;
+        VQ_CHECK(attempt == 0, VQ_ERR_CAPACITY, "a query has more than %d positives in the gallery", kMaxPositives - 1);
+    }
+    ix->stats[5] = launches;
+    VQ_TRY(oA.finish(st));
+    VQ_TRY(oR.finish(st));
+    VQ_TRY(oN.finish(st));
+    VQ_TRY(oK.finish(st));
+    VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
 int vq_average_precision(const int32_t *y_true, const double *y_score, const int64_t *offsets, int64_t nlists,
                          double *ap, void *stream) {
     VQ_CHECK(y_true && y_score && offsets && ap, VQ_ERR_INVALID, "NULL argument");

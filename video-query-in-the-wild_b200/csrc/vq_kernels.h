@@ -124,7 +124,27 @@ struct ApRowsParams {
     double *recall;    // [nq_tile,3]
     int64_t *top_idx;  // [nq_tile,100] or null
     int32_t *overflow; // [1] set when a query has more positives than kMaxPositives
+    // moment mode (kept != null): g_label = closest-hit label of each moment
+    const uint8_t *kept;         // [nq_tile, n] survivors of the per-video NMS
+    const float *g_iou;          // [n]
+    uint64_t *vbest;             // [nq_tile, nseg] key of each video's best moment (ignored videos are blanked)
+    const int64_t *seg_start;    // [nseg+1]
+    const int32_t *seg_of_row;   // [n]
+    int64_t nseg;
+    int64_t *n_kept;             // [nq_tile] or null
 };
+struct MomentNmsParams {
+    int64_t nq_tile, n, nseg;
+    const float *d2;             // [nq_tile, n] canonical
+    const int64_t *seg_start;    // [nseg+1]
+    const float *start, *end;    // [n] seconds
+    double thresh;
+    uint8_t *kept;               // [nq_tile, n]
+    uint64_t *vbest;             // [nq_tile, nseg]
+};
+static constexpr int kMomentWarpCap = 256, kMomentBlockCap = 4096;
+int launch_moment_nms(const MomentNmsParams &p, const int32_t *small_list, int n_small, const int32_t *large_list,
+                      int n_large, cudaStream_t st);
 static constexpr int kMaxPositives = 8192;
 // pcap2: power-of-two capacity of the per-query positive list (<= kMaxPositives)
 int launch_ap_rows(const ApRowsParams &p, int pcap2, cudaStream_t st);

@@ -55,7 +55,13 @@ __device__ __forceinline__ bool is_ignored(int v, const int *ign, int n_ign) {
     return m;
 }
 
+// MOMENT (dataloader_baseline.py:1283-1330): survivors are additionally the moments kept by
+// the per-video NMS (p.kept), tp = closest-hit label match AND IoU >= 0.5 (:1249-1255, :1315-1319), and the list
+// handed to multiprocess_calculate (:386-402) is GROUPED: videos in the order of their best moment, kept moments
+// in ranked order inside a video.  AP depends on the (score, tp) multiset only, except for the forced positive
+// y_true[-1] (:389) = last kept moment of the last video; R@N counts positions in the grouped list.
 // dynamic smem: u64 pos[pcap2] | int cntA[pcap2+1] | int cntE[pcap2] | int gstart[pcap2] | int part[257] | misc
+template <bool MOMENT>
 __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams p, int pcap2) {
     extern __shared__ __align__(16) uint8_t sm[];
     uint64_t *pos = (uint64_t *)sm;
@@ -64,19 +70,25 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     int *gstart = cntE + pcap2;
     int *part = gstart + pcap2;
     int *misc = part + kApThreads + 1;  // [0]=npos [1]=nvalid, [8..16)=ignore list
-    unsigned long long *last_key = (unsigned long long *)(misc + 16);
-    double *res = (double *)(last_key + 1);  // [0]=ap
+    unsigned long long *last_key = (unsigned long long *)(misc + 16);  // [0] last survivor  [1] MOMENT: last video
+    double *res = (double *)(last_key + 2);  // [0]=ap
     int *topn = (int *)(res + 1);            // [3] true positives within rank 30/50/100
+    uint64_t *tv = (uint64_t *)(topn + 4);   // MOMENT: [128] best-moment keys of the first videos
+    int *tcnt = (int *)(tv + 128);           // MOMENT: [128] kept moments per such video, then their offsets
     const int tid = threadIdx.x;
     const int64_t q = blockIdx.x;
     const float *row = p.d2 + q * p.n;
+    const uint8_t *keptrow = MOMENT ? p.kept + q * p.n : nullptr;
     const int ql = p.q_label[q];
+    auto is_tp = [&](int64_t j) { return p.g_label[j] == ql && (!MOMENT || p.g_iou[j] >= 0.5f); };
 
     if (tid < kMaxIgnore) misc[8 + tid] = (p.q_ignore && tid < p.n_ign) ? p.q_ignore[q * p.n_ign + tid] : -1;
     if (tid == 0) {
         misc[0] = 0;
         misc[1] = 0;
-        *last_key = 0ull;
+        misc[2] = 0;
+        last_key[0] = 0ull;
+        last_key[1] = 0ull;
         topn[0] = topn[1] = topn[2] = 0;
     }
     for (int i = tid; i < pcap2; i += kApThreads) {
@@ -90,21 +102,58 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     const int n_ign = p.q_ignore ? p.n_ign : 0;
 
     // ---- pass 1: positives, survivor count, last-ranked survivor ----
-    int nvalid_t = 0;
+    int nvalid_t = 0, nkept_t = 0;
     unsigned long long lk = 0ull;
     for (int64_t j = tid; j < p.n; j += kApThreads) {
+        if (MOMENT) {
+            if (!keptrow[j]) continue;
+            ++nkept_t;
+        }
         if (n_ign && is_ignored(p.g_video[j], ign, n_ign)) continue;
         ++nvalid_t;
         const unsigned long long key = make_key_asc(row[j], (uint32_t)j);
         lk = key > lk ? key : lk;
-        if (p.g_label[j] == ql) {
+        if (is_tp(j)) {
             const int slot = atomicAdd(&misc[0], 1);
             if (slot < pcap2) pos[slot] = key;
         }
     }
     atomicAdd(&misc[1], nvalid_t);
-    atomicMax(last_key, lk);
+    if (MOMENT) atomicAdd(&misc[2], nkept_t);
+    if (!MOMENT) atomicMax(last_key, lk);
     __syncthreads();
+    int nvideos = 0;  // MOMENT: videos that are neither empty nor ignored
+    uint64_t *vb = MOMENT ? p.vbest + q * p.nseg : nullptr;
+    if (MOMENT) {
+        if (tid == 0 && p.n_kept) p.n_kept[q] = misc[2];
+        // last video of the grouped list = largest best-moment key; ignored videos leave the list (:387)
+        unsigned long long lv = 0ull;
+        int nv_t = 0;
+        for (int64_t v = tid; v < p.nseg; v += kApThreads) {
+            unsigned long long key = vb[v];
+            if (key == ~0ull) continue;
+            if (n_ign && is_ignored(p.g_video[(uint32_t)key], ign, n_ign)) {
+                vb[v] = ~0ull;
+                continue;
+            }
+            ++nv_t;
+            lv = key > lv ? key : lv;
+        }
+        atomicMax(last_key + 1, lv);
+        nvideos = block_sum(nv_t, part);
+        __syncthreads();
+        if (nvideos > 0) {  // its last kept moment
+            const int64_t v = p.seg_of_row[(uint32_t)last_key[1]];
+            unsigned long long lm = 0ull;
+            for (int64_t j = p.seg_start[v] + tid; j < p.seg_start[v + 1]; j += kApThreads)
+                if (keptrow[j]) {
+                    const unsigned long long key = make_key_asc(row[j], (uint32_t)j);
+                    lm = key > lm ? key : lm;
+                }
+            atomicMax(last_key, lm);
+        }
+        __syncthreads();
+    }
     const int ntrue = misc[0];
     const int nvalid = misc[1];
     if (ntrue + 1 > pcap2) {  // uniform
@@ -124,7 +173,7 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     }
     // forced positive: the last survivor in ranked order (dataloader_baseline.py:434), AP only
     const uint64_t lastk = *last_key;
-    const bool last_is_true = p.g_label[(uint32_t)lastk] == ql;
+    const bool last_is_true = is_tp((uint32_t)lastk);
     int npos = ntrue;
     if (!last_is_true) {
         if (tid == 0) pos[ntrue] = lastk;
@@ -136,6 +185,7 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
 
     // ---- pass 2: bucket every survivor against the sorted positive d2 values ----
     for (int64_t j = tid; j < p.n; j += kApThreads) {
+        if (MOMENT && !keptrow[j]) continue;
         if (n_ign && is_ignored(p.g_video[j], ign, n_ign)) continue;
         const uint32_t s = f32_to_ordered(row[j]);
         int lo = 0, hi = npos;  // lower bound: first i with pos_d2[i] >= s
@@ -173,8 +223,61 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     }
     __syncthreads();
 
+    if (MOMENT) {
+        // ---- R@N over the grouped list: the first <= 100 videos by best moment, their kept moments in order ----
+        const int K = nvideos < 100 ? nvideos : 100;
+        if (K > 0) {
+            const uint64_t kth = block_kth_smallest(vb, (int)p.nseg, K, part);
+            if (tid < 128) tv[tid] = ~0ull;
+            if (tid == 0) misc[3] = 0;
+            __syncthreads();
+            for (int64_t v = tid; v < p.nseg; v += kApThreads)
+                if (vb[v] <= kth) tv[atomicAdd(&misc[3], 1)] = vb[v];  // keys are distinct: exactly K of them
+            __syncthreads();
+            block_bitonic_sort(tv, 128);
+            const int warp = tid >> 5, lane = tid & 31;
+            for (int t = warp; t < K; t += kApThreads / 32) {
+                const int64_t v = p.seg_of_row[(uint32_t)tv[t]];
+                int c = 0;
+                for (int64_t j = p.seg_start[v] + lane; j < p.seg_start[v + 1]; j += 32) c += keptrow[j] ? 1 : 0;
+                c = __reduce_add_sync(0xffffffffu, c);
+                if (lane == 0) tcnt[t] = c;
+            }
+            __syncthreads();
+            if (tid == 0) {
+                int run = 0;
+                for (int t = 0; t < K; ++t) {
+                    const int c = tcnt[t];
+                    tcnt[t] = run;
+                    run += c;
+                }
+            }
+            __syncthreads();
+            for (int t = warp; t < K; t += kApThreads / 32) {
+                const int off = tcnt[t];
+                if (off >= 100) continue;
+                const int64_t v = p.seg_of_row[(uint32_t)tv[t]];
+                const int64_t s0 = p.seg_start[v], s1 = p.seg_start[v + 1];
+                for (int64_t jb = s0; jb < s1; jb += 32) {
+                    const int64_t j = jb + lane;
+                    const bool mine = j < s1 && keptrow[j] && is_tp(j);
+                    if (!__any_sync(0xffffffffu, mine)) continue;
+                    const unsigned long long key = mine ? make_key_asc(row[j], (uint32_t)j) : 0ull;
+                    int ahead = 0;  // kept moments of this video ranked before mine
+                    for (int64_t jj = s0; jj < s1; ++jj)
+                        if (keptrow[jj]) ahead += make_key_asc(row[jj], (uint32_t)jj) < key ? 1 : 0;
+                    if (mine) {
+                        const int rank = off + ahead + 1;
+                        if (rank <= 30) atomicAdd(&topn[0], 1);
+                        if (rank <= 50) atomicAdd(&topn[1], 1);
+                        if (rank <= 100) atomicAdd(&topn[2], 1);
+                    }
+                }
+            }
+        }
+    }
     // ---- R@N: exact rank of every TRUE positive under the (d2, row) order ----
-    for (int i = tid; i < npos; i += kApThreads) {
+    for (int i = tid; !MOMENT && i < npos; i += kApThreads) {
         const uint64_t key = pos[i];
         if (!last_is_true && key == lastk) continue;  // the forced one is not a true positive
         const int g = gstart[i];
@@ -205,15 +308,20 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
 }
 
 static size_t ap_rows_smem(int pcap2) {
-    return (size_t)pcap2 * 8 + (size_t)(pcap2 + 1) * 4 + (size_t)pcap2 * 4 * 2 + (kApThreads + 1) * 4 + 16 * 4 + 8 +
-           8 + 16 + 64;
+    return (size_t)pcap2 * 8 + (size_t)(pcap2 + 1) * 4 + (size_t)pcap2 * 4 * 2 + (kApThreads + 1) * 4 + 16 * 4 + 16 +
+           8 + 16 + 128 * 8 + 128 * 4 + 64;
 }
 
 int launch_ap_rows(const ApRowsParams &p, int pcap2, cudaStream_t st) {
     if (p.nq_tile == 0) return VQ_OK;
     const size_t smem = ap_rows_smem(pcap2);
-    VQ_CUDA(cudaFuncSetAttribute(ap_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    ap_rows_kernel<<<(unsigned)p.nq_tile, kApThreads, smem, st>>>(p, pcap2);
+    if (p.kept) {
+        VQ_CUDA(cudaFuncSetAttribute(ap_rows_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ap_rows_kernel<true><<<(unsigned)p.nq_tile, kApThreads, smem, st>>>(p, pcap2);
+    } else {
+        VQ_CUDA(cudaFuncSetAttribute(ap_rows_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ap_rows_kernel<false><<<(unsigned)p.nq_tile, kApThreads, smem, st>>>(p, pcap2);
+    }
     VQ_CUDA(cudaGetLastError());
     return VQ_OK;
 }

@@ -95,6 +95,30 @@ class IndexFlatL2:
                                               C.c_int(n_ign), L.ptr(ap), L.ptr(rec), L.ptr(top), L.stream_of(xq)))
         return ap, rec, top
 
+    def set_moments(self, start_sec, end_sec, iou, hit_label):
+        """Per-row moment metadata (candidate["start_sec"], ["end_sec"], closest_hit iou / label id,
+        dataloader_baseline.py:1239-1255); needs ``set_segments`` (one segment per video) and ``set_meta``."""
+        a = [L.as_f32(start_sec), L.as_f32(end_sec), L.as_f32(iou), L.as_i32(hit_label)]
+        L.check(L.lib().vq_index_set_moments(self._h, L.ptr(a[0]), L.ptr(a[1]), L.ptr(a[2]), L.ptr(a[3]),
+                                             L.stream_of(a[0])))
+
+    def eval_moment(self, xq, q_label, ignore_video=None, nms_thresh=0.5, want_kept=False):
+        """ARV_Retrieval_Moment.ranking's per-query numbers (dataloader_baseline.py:1225-1330): rank all
+        moments, per-video NMS in ranked order, tp = IoU >= 0.5, AP + R@30/50/100 over the grouped list.
+        Returns ap float64[nq], recall float64[nq,3], n_kept int64[nq], kept_mask uint8[nq,ntotal] or None."""
+        xq, dt = L.emb_dtype(xq)
+        nq = xq.shape[0]
+        ql, ign = L.as_i32(q_label), L.as_i32(ignore_video)
+        n_ign = 0 if ign is None else int(ign.shape[1])
+        ap = L.empty_like_kind(xq, (nq,), np.float64)
+        rec = L.empty_like_kind(xq, (nq, 3), np.float64)
+        nk = L.empty_like_kind(xq, (nq,), np.int64)
+        km = L.empty_like_kind(xq, (nq, self.ntotal), np.uint8) if want_kept else None
+        L.check(L.lib().vq_index_eval_moment(self._h, L.ptr(xq), C.c_int64(nq), C.c_int(dt), L.ptr(ql), L.ptr(ign),
+                                             C.c_int(n_ign), C.c_double(float(nms_thresh)), L.ptr(ap), L.ptr(rec),
+                                             L.ptr(nk), L.ptr(km), L.stream_of(xq)))
+        return ap, rec, nk, km
+
     def last_stats(self):
         out = (C.c_int64 * 6)()
         L.check(L.lib().vq_index_last_stats(self._h, out))

@@ -67,3 +67,70 @@ class ARV_Retrieval:
 
     def evaluation(self):
         return self.ranking()
+
+
+class ARV_Retrieval_Moment:
+    """``ARV_Retrieval_Moment.ranking`` (dataloader_baseline.py:1206-1371) over the reference's hand-off
+    lists: ``gallery_list`` = moments (``feat``, ``video_id``, ``start_sec``, ``end_sec``,
+    ``closest_hit`` = None or dict(label, iou)), built video by video (:1091-1151) so the moments of a
+    video are contiguous; ``query_list`` items carry ``feat``, ``label``, ``video_id``,
+    ``retrieval_type``.  The reference forks ``cpu_count()//4`` workers over the queries (:1334); here
+    all queries go to the device in one batched call from the parent process."""
+
+    def __init__(self, args, feat_extract_func=None, query_list=None, gallery_list=None):
+        self.args = args
+        self.feat_extract_func = feat_extract_func
+        self.query_list = query_list
+        self.gallery_list = gallery_list
+        self.faiss_index = None
+
+    def build_index(self):
+        """:1196-1204 plus the per-moment metadata the labelling loop reads (:1239-1261)."""
+        gl = self.gallery_list
+        xb = np.ascontiguousarray(np.stack([g["feat"].reshape(-1) for g in gl]), dtype=np.float32)
+        self._video_ids, self._video_table = _ids([g["video_id"] for g in gl])
+        chg = np.flatnonzero(np.diff(self._video_ids)) + 1
+        seg_start = np.concatenate([[0], chg, [len(gl)]]).astype(np.int64)
+        if len(seg_start) - 1 != len(self._video_table):
+            raise ValueError("gallery_list: the moments of a video must be contiguous")
+        self._label_table = {}
+        hit = np.full(len(gl), -1, np.int32)
+        iou = np.zeros(len(gl), np.float32)
+        for i, g in enumerate(gl):
+            ch = g["closest_hit"]
+            if ch is not None:
+                hit[i] = self._label_table.setdefault(ch["label"], len(self._label_table))
+                iou[i] = ch["iou"]
+        self.faiss_index = IndexFlatL2(xb.shape[1])
+        self.faiss_index.add(xb)
+        self.faiss_xb = xb
+        self.faiss_index.set_meta(hit, self._video_ids)
+        self.faiss_index.set_segments(seg_start)
+        self.faiss_index.set_moments(np.array([g["start_sec"] for g in gl], np.float32),
+                                     np.array([g["end_sec"] for g in gl], np.float32), iou, hit)
+
+    def ranking(self, nms_threshold=0.5):
+        if self.faiss_index is None:
+            self.build_index()
+        if getattr(self.args, "debug", False):                                   # :1213-1216
+            self.query_list = [[i] for i in self.query_list]
+        else:
+            self.query_list = generate_multi_query(self.query_list)
+        self.class_map_evaluation05 = evaluation_metric(self.args, self.query_list)
+        nq, qn = len(self.query_list), int(self.args.query_num)
+        xq = np.empty((nq, self.faiss_xb.shape[1]), np.float32)
+        for i, queries in enumerate(self.query_list):                            # :1263-1266
+            acc = 0
+            for j in range(qn):
+                acc = acc + queries[j]["feat"]
+            xq[i] = acc / qn
+        q_label, _ = _ids([q[0]["label"] for q in self.query_list], dict(self._label_table))
+        ign = np.stack([_ids([x["video_id"] for x in q], dict(self._video_table))[0] for q in self.query_list])
+        ap, rec, _, _ = self.faiss_index.eval_moment(xq, q_label, ign, nms_thresh=nms_threshold)
+        cls = [q[0]["label"] for q in self.query_list]
+        typ = [q[0]["retrieval_type"] for q in self.query_list]
+        self.class_map_evaluation05.update_arrays(cls, typ, ap, rec)
+        return dict(map05=self.class_map_evaluation05.get_result())
+
+    def evaluation(self):
+        return self.ranking()
