@@ -247,6 +247,58 @@ def aux_measurements(torch, vq):
         nbytes = G * (2 * 256 * 512 * 4 + 256 * 8 + 4)
         out["triplet_cfg1_G%d" % G] = {"workload": "configs[1]: batch-hard triplet fwd+bwd, %d x (256 x 512-d f32)" % G,
                                        "ms": ms, "algorithmic_bytes": nbytes, "GB_per_s": nbytes / ms / 1e6}
+    # configs[2]: untrimmed moment retrieval, 4096 queries x 20480 videos x 64 moments, 512-d f32: segment
+    # max-pool + top-100 videos (tensor cores) and the full moment evaluation (rank all, per-video NMS, AP, R@N)
+    try:
+        out.update(aux_moment(torch, vq))
+    except Exception as e:  # noqa: BLE001 -- a side measurement must not lose the headline line
+        out["moment_cfg2_error"] = repr(e)
+    return out
+
+
+def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
+    import numpy as np
+    dev, n, out = "cuda", V * S, {}
+    gen = torch.Generator(device=dev).manual_seed(0)
+    g = torch.randn(n, d, device=dev, generator=gen)
+    g = g / g.norm(dim=1, keepdim=True) * (0.6 + 0.4 * torch.rand(n, 1, device=dev, generator=gen))
+    q = torch.randn(nq, d, device=dev, generator=gen)
+    q = q / q.norm(dim=1, keepdim=True)
+    rng = np.random.default_rng(0)
+    s_in = np.arange(n) % S  # sliding moments: 1..6 clips of 5 s at stride 5 s (dataloader_baseline.py:1116-1137)
+    start = (5 * (s_in // 6)).astype(np.float32)
+    end = start + 5 * (1 + s_in % 6).astype(np.float32)
+    video = (np.arange(n) // S).astype(np.int32)
+    hit = rng.integers(-1, 180, n).astype(np.int32)
+    iou = np.where(hit >= 0, rng.uniform(0, 1, n), 0).astype(np.float32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    del g
+    ix.set_meta(hit, video)
+    ix.set_segments(np.arange(0, n + 1, S, dtype=np.int64))
+    ix.set_moments(start, end, iou, hit)
+    ql = torch.from_numpy(rng.integers(0, 180, nq).astype(np.int32)).to(dev)
+    ign = torch.from_numpy(rng.integers(0, V, (nq, 5)).astype(np.int32)).to(dev)
+
+    def wall(fn, reps):
+        ts = []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r = fn()
+            torch.cuda.synchronize()
+            ts.append(time.perf_counter() - t0)
+        return min(ts[1:]) if reps > 1 else ts[0], r
+
+    t, _ = wall(lambda: ix.search_segmax(q, 100), 3)
+    tm = ix.last_timing()
+    out["segmax_cfg2"] = {"workload": "configs[2]: %d queries x %d videos x %d moments x %d-d f32, per-video max + top-100 videos"
+                          % (nq, V, S, d), "wall_ms": t * 1e3, "pairs_per_s": nq * n / t,
+                          "gemm_topk_ms": tm["gemm_topk_ms"], "tflops_algorithmic": 2.0 * nq * n * d / tm["gemm_topk_ms"] / 1e9}
+    t, r = wall(lambda: ix.eval_moment(q, ql, ign), 2)
+    out["moment_eval_cfg2"] = {"workload": "configs[2]: full moment evaluation (rank all %d moments per query, per-video NMS, "
+                               "AP@tIoU0.5, grouped R@30/50/100), %d queries" % (n, nq), "wall_ms": t * 1e3,
+                               "ms_per_query": t * 1e3 / nq, "pairs_per_s": nq * n / t, "mAP": float(r[0].mean().item())}
     return out
 
 

@@ -50,7 +50,10 @@ struct TcLayout {
     static constexpr int OFF_EOFF = OFF_REX + 8 * TEXTRA * 8;  // int[260] CSR offsets of the gradient gather lists
     static constexpr int OFF_ECNT = OFF_EOFF + 1040;        // int[256] counters
     static constexpr int OFF_ENT = OFF_ECNT + 1024;         // uint16[768] entries
-    static constexpr int OFF_MISC = OFF_ENT + 1536;         // int[16]
+    static constexpr int OFF_PERM = OFF_ENT + 1536;         // uint8[256] rows by gather-list length, longest first
+    static constexpr int OFF_EN2 = OFF_PERM + 256;          // uint2[1024] gather entries of pass 3
+    static constexpr int OFF_NL = OFF_EN2 + 8192;           // float2[256] (|row|^2, label bits): one LDS.128 per two columns
+    static constexpr int OFF_MISC = OFF_NL + 2048;          // int[16]
     static constexpr int OFF_BAR = OFF_MISC + 64;           // full[S] empty[S] tfull tempty
     static constexpr int OFF_TMEM = OFF_BAR + (2 * TSTAGES + 2) * 8;
     static constexpr int TOTAL = OFF_TMEM + 16 + 1024;
@@ -139,6 +142,9 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
     int *s_eoff = (int *)(smem + L::OFF_EOFF);
     int *s_ecnt = (int *)(smem + L::OFF_ECNT);
     uint16_t *s_ent = (uint16_t *)(smem + L::OFF_ENT);
+    uint8_t *s_perm = smem + L::OFF_PERM;
+    float2 *s_nl = (float2 *)(smem + L::OFF_NL);
+    uint2 *s_en2 = (uint2 *)(smem + L::OFF_EN2);
     int *s_misc = (int *)(smem + L::OFF_MISC);  // [0] max |row|^2 bits  [1] T  [2] bad flag  [4..11] scan partials
     uint64_t *full_bar = (uint64_t *)(smem + L::OFF_BAR);
     uint64_t *empty_bar = full_bar + TSTAGES;
@@ -267,9 +273,11 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             tk[1] = clock64();
             s_nrm[row] = na;
             s_lab[row] = rvalid ? p.labels[(int64_t)g * B + row] : 0;
+            s_nl[row] = make_float2(na, __int_as_float(s_lab[row]));
             s_ecnt[row] = 0;
             if (threadIdx.x == 64) {
                 s_misc[0] = 0;
+                s_misc[1] = 0;
                 s_misc[2] = 0;
             }
             named_bar_sync(1, TROWT);
@@ -294,13 +302,17 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 tmem_ld32(taddr + ch * 32, r);
                 tmem_wait_ld();
 #pragma unroll
-                for (int i = 0; i < 32; ++i) {
-                    const int j = ch * 32 + i;
-                    const float cv = __fmaf_rn(-2.0f, __uint_as_float(r[i]), __fadd_rn(na, s_nrm[j]));
-                    const bool ok = j < B && j != row;
-                    const bool same = s_lab[j] == la;
-                    if (ok && same) maxp = fmaxf(maxp, cv);
-                    if (ok && !same) minn = fminf(minn, cv);
+                for (int i = 0; i < 32; i += 2) {
+                    const float4 nl = *reinterpret_cast<const float4 *>(&s_nl[ch * 32 + i]);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int j = ch * 32 + i + h;
+                        const float cv = __fmaf_rn(-2.0f, __uint_as_float(r[i + h]), __fadd_rn(na, h ? nl.z : nl.x));
+                        const bool ok = j < B && j != row;
+                        const bool same = __float_as_int(h ? nl.w : nl.y) == la;
+                        if (ok && same) maxp = fmaxf(maxp, cv);
+                        if (ok && !same) minn = fminf(minn, cv);
+                    }
                 }
             }
             const bool avalid = rvalid && maxp > -INFINITY && minn < INFINITY;
@@ -316,18 +328,22 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                     tmem_ld32(taddr + ch * 32, r);
                     tmem_wait_ld();
 #pragma unroll
-                    for (int i = 0; i < 32; ++i) {
-                        const int j = ch * 32 + i;
-                        const float cv = __fmaf_rn(-2.0f, __uint_as_float(r[i]), __fadd_rn(na, s_nrm[j]));
-                        const bool ok = avalid && j < B && j != row;
-                        const bool same = s_lab[j] == la;
-                        if (ok && same && cv >= thr_p) {
-                            if (ncp < TCAND) cpw |= (uint64_t)j << (8 * ncp);
-                            ++ncp;
-                        }
-                        if (ok && !same && cv <= thr_n) {
-                            if (ncn < TCAND) cnw |= (uint64_t)j << (8 * ncn);
-                            ++ncn;
+                    for (int i = 0; i < 32; i += 2) {
+                        const float4 nl = *reinterpret_cast<const float4 *>(&s_nl[ch * 32 + i]);
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const int j = ch * 32 + i + h;
+                            const float cv = __fmaf_rn(-2.0f, __uint_as_float(r[i + h]), __fadd_rn(na, h ? nl.z : nl.x));
+                            const bool ok = avalid && j < B && j != row;
+                            const bool same = __float_as_int(h ? nl.w : nl.y) == la;
+                            if (ok && same && cv >= thr_p) {
+                                if (ncp < TCAND) cpw |= (uint64_t)j << (8 * ncp);
+                                ++ncp;
+                            }
+                            if (ok && !same && cv <= thr_n) {
+                                if (ncn < TCAND) cnw |= (uint64_t)j << (8 * ncn);
+                                ++ncn;
+                            }
                         }
                     }
                 }
@@ -470,21 +486,26 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 atomicAdd(&s_ecnt[fp], 1);
                 atomicAdd(&s_ecnt[fn], 1);
             }
-            if (threadIdx.x == 64) {  // sequential sum in triplet order, as the oracle
-                int T = 0;
-                float s = 0.f;
-                for (int t = 0; t < B; ++t)
-                    if (s_tp[t] >= 0) {
-                        ++T;
-                        s = __fadd_rn(s, s_lt[t]);
-                    }
-                s_misc[1] = T;
-                p.loss[g] = T > 0 ? __fdiv_rn(s, (float)T) : 0.f;
+            {
+                const unsigned vb = __ballot_sync(0xffffffffu, fp >= 0);
+                if (lane == 0 && vb) atomicAdd(&s_misc[1], __popc(vb));
+            }
+            if (threadIdx.x == 64) {  // sequential sum in triplet order, as the oracle (skipped anchors hold +0)
+                float sum = 0.f;
+                for (int t = 0; t < TB; t += 4) {
+                    const float4 v = *reinterpret_cast<const float4 *>(&s_lt[t]);
+                    sum = __fadd_rn(__fadd_rn(__fadd_rn(__fadd_rn(sum, v.x), v.y), v.z), v.w);
+                }
+                s_misc[3] = __float_as_int(sum);
             }
             named_bar_sync(1, TROWT);
-            {   // exclusive scan of the per-row counts in row order
-                const int cnt = s_ecnt[row];
-                int inc2 = cnt;
+            const int T = s_misc[1];
+            if (threadIdx.x == 64) p.loss[g] = T > 0 ? __fdiv_rn(__int_as_float(s_misc[3]), (float)T) : 0.f;
+            const int cnt = s_ecnt[row];
+            {   // exclusive scan of the per-row list lengths in row order; a row without triplets gets one
+                // no-op entry (x_r - x_r) so that every gradient row is written by the same loop
+                const int len = cnt > 0 ? cnt : 1;
+                int inc2 = len;
 #pragma unroll
                 for (int o = 1; o < 32; o <<= 1) {
                     const int v = __shfl_up_sync(0xffffffffu, inc2, o);
@@ -494,63 +515,88 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 named_bar_sync(1, TROWT);
                 int basep = 0;
                 for (int b = 0; b < (row >> 5); ++b) basep += s_misc[4 + b];
-                s_eoff[row] = basep + inc2 - cnt;
+                s_eoff[row] = basep + inc2 - len;
                 if (row == TB - 1) s_eoff[TB] = basep + inc2;
                 s_ecnt[row] = 0;
             }
             named_bar_sync(1, TROWT);
-            if (act) {  // entry = (triplet << 2 | role); sorted by triplet below
+            if (act) {  // staging entry = (triplet << 2 | role); sorted by triplet below
                 s_ent[s_eoff[row] + atomicAdd(&s_ecnt[row], 1)] = (uint16_t)((row << 2) | 0);
                 s_ent[s_eoff[fp] + atomicAdd(&s_ecnt[fp], 1)] = (uint16_t)((row << 2) | 1);
                 s_ent[s_eoff[fn] + atomicAdd(&s_ecnt[fn], 1)] = (uint16_t)((row << 2) | 2);
             }
             named_bar_sync(1, TROWT);
-            {   // each row: its triplets in order, rewritten as (u << 8 | v): contribution x_u - x_v
-                const int e0 = s_eoff[row], e1 = s_eoff[row + 1];
-                for (int i = e0 + 1; i < e1; ++i) {
-                    const uint16_t key = s_ent[i];
-                    int j = i - 1;
-                    while (j >= e0 && s_ent[j] > key) {
-                        s_ent[j + 1] = s_ent[j];
-                        --j;
+            {   // each row: its triplets in order -> entries (byte offsets of rows u and v inside a stage, chunk 0
+                // after the swizzle; owner row; last-of-row flag): contribution x_u - x_v
+                const int e0 = s_eoff[row];
+                auto base_of = [](int r) { return (uint32_t)((r << 7) | ((r & 7) << 4)); };
+                if (cnt == 0) {
+                    s_en2[e0] = make_uint2(base_of(row) | (base_of(row) << 16), (uint32_t)row | 256u);
+                } else {
+                    for (int i = e0 + 1; i < e0 + cnt; ++i) {
+                        const uint16_t key = s_ent[i];
+                        int j = i - 1;
+                        while (j >= e0 && s_ent[j] > key) {
+                            s_ent[j + 1] = s_ent[j];
+                            --j;
+                        }
+                        s_ent[j + 1] = key;
                     }
-                    s_ent[j + 1] = key;
-                }
-                for (int i = e0; i < e1; ++i) {
-                    const int t = s_ent[i] >> 2, role = s_ent[i] & 3;
-                    int u, v;
-                    if (role == 0) { u = s_tn[t]; v = s_tp[t]; }      // anchor:   2(n - p)/T
-                    else if (role == 1) { u = row; v = t; }           // positive: 2(p - a)/T
-                    else { u = t; v = row; }                          // negative: 2(a - n)/T
-                    s_ent[i] = (uint16_t)((u << 8) | v);
+                    for (int i = e0; i < e0 + cnt; ++i) {
+                        const int t = s_ent[i] >> 2, role = s_ent[i] & 3;
+                        int u, v;
+                        if (role == 0) { u = s_tn[t]; v = s_tp[t]; }      // anchor:   2(n - p)/T
+                        else if (role == 1) { u = row; v = t; }           // positive: 2(p - a)/T
+                        else { u = t; v = row; }                          // negative: 2(a - n)/T
+                        s_en2[i] = make_uint2(base_of(u) | (base_of(v) << 16),
+                                              (uint32_t)row | (i == e0 + cnt - 1 ? 256u : 0u));
+                    }
                 }
             }
             named_bar_sync(1, TROWT);
-            const int T = s_misc[1];
             const float scale = T > 0 ? __fdiv_rn(2.0f, (float)T) : 0.f;
             tk[5] = clock64();
 
             // ---------------- pass 3: gradient rows, 8 lanes x 16 bytes per row block ----------------
+            // The entry array is cut at row boundaries into 32 near-equal pieces, one per 8-lane sub-group; a
+            // sub-group walks its piece with the chain acc = fmaf(2/T, x_u - x_v, acc) (triplet order inside a row),
+            // loads running two entries ahead of the chain, and writes a row when its last entry retires.
+            const int E = s_eoff[TB];
+            auto piece = [&](int sgi) {
+                if (sgi >= TROWT / 8) return E;
+                const int x = (sgi * E) / (TROWT / 8);
+                if (x == 0) return 0;
+                const int r = s_en2[x].y & 255u;
+                return s_eoff[r] == x ? x : s_eoff[r + 1];
+            };
+            const int eb = piece(rw * 4 + m), ee = piece(rw * 4 + m + 1);
+            const int nit = __reduce_max_sync(0xffffffffu, ee - eb);
+            const uint32_t cx = (uint32_t)c << 4;
             for (int kb = 0; kb < KB; ++kb) {
                 mbar_wait(&full_bar[stage], phase);
                 if (p.grad) {
                     const uint8_t *sp = smem + stage * TSTAGE;
                     const int col = kb * TKB + c * 4;
-#pragma unroll 1
-                    for (int rr = 0; rr < 8; ++rr) {
-                        const int r = row0 + m + 4 * rr;
-                        const int e0 = s_eoff[r], e1 = s_eoff[r + 1];
-                        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-                        for (int e = e0; e < e1; ++e) {
-                            const int uv = s_ent[e];
-                            const float4 xu = tc_ld_chunk(sp, uv >> 8, c), xv = tc_ld_chunk(sp, uv & 255, c);
-                            acc.x = __fmaf_rn(scale, __fsub_rn(xu.x, xv.x), acc.x);
-                            acc.y = __fmaf_rn(scale, __fsub_rn(xu.y, xv.y), acc.y);
-                            acc.z = __fmaf_rn(scale, __fsub_rn(xu.z, xv.z), acc.z);
-                            acc.w = __fmaf_rn(scale, __fsub_rn(xu.w, xv.w), acc.w);
+                    auto ldx = [&](uint32_t off) { return *reinterpret_cast<const float4 *>(sp + ((off & 0x7fffu) ^ cx)); };
+                    uint2 en0 = s_en2[min(eb, E - 1)], en1 = s_en2[min(eb + 1, E - 1)];
+                    float4 xu0 = ldx(en0.x), xv0 = ldx(en0.x >> 16);
+                    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int it = 0; it < nit; ++it) {
+                        const float4 xu1 = ldx(en1.x), xv1 = ldx(en1.x >> 16);
+                        const uint2 en2 = s_en2[min(eb + it + 2, E - 1)];
+                        if (eb + it < ee) {
+                            acc.x = __fmaf_rn(scale, __fsub_rn(xu0.x, xv0.x), acc.x);
+                            acc.y = __fmaf_rn(scale, __fsub_rn(xu0.y, xv0.y), acc.y);
+                            acc.z = __fmaf_rn(scale, __fsub_rn(xu0.z, xv0.z), acc.z);
+                            acc.w = __fmaf_rn(scale, __fsub_rn(xu0.w, xv0.w), acc.w);
+                            if (en0.y & 256u) {
+                                const int r = en0.y & 255u;
+                                if (r < B && col < p.d)
+                                    *reinterpret_cast<float4 *>(p.grad + ((int64_t)g * B + r) * p.d + col) = acc;
+                                acc = make_float4(0.f, 0.f, 0.f, 0.f);
+                            }
                         }
-                        if (r < B && col < p.d)
-                            *reinterpret_cast<float4 *>(p.grad + ((int64_t)g * B + r) * p.d + col) = acc;
+                        en0 = en1; xu0 = xu1; xv0 = xv1; en1 = en2;
                     }
                 }
                 next_stage();
