@@ -185,6 +185,16 @@ VQ_API int vq_triplet_given(const float *emb, int64_t B, int d, const int32_t *t
  * (dataloader_baseline.py:1481).  x f32[B,C,T] -> out f32[B,C]. */
 VQ_API int vq_pool_normalize(const float *x, int64_t B, int C, int T, float *out, void *stream);
 
+/* f1. Moment / clip window pooling, the step before the index build (garner_feat,
+ * dataloader_baseline.py:1125-1147 and :809-834: feat = np.mean(video_feat[:, lo:hi], axis=1) per window).
+ *   feat f32[C, Ttot]: per-frame features of V videos concatenated along time, video v = frames
+ *   [vid_t0[v], vid_t0[v+1]) (vid_t0 int64[V+1], HOST); windows grouped by video: video v owns windows
+ *   [win_start[v], win_start[v+1]) (int64[V+1], HOST); window w averages frames [lo[w], hi[w]) of its video
+ *   (int32, relative to the video's first frame, host or device).  out f32[n_windows, C] (host or device). */
+VQ_API int vq_window_means(const float *feat, int C, int64_t Ttot, const int64_t *vid_t0,
+                           const int64_t *win_start, int64_t V, const int32_t *lo, const int32_t *hi,
+                           float *out, void *stream);
+
 /* 8e. Merge per-shard top-k lists after the all-gather: d2 f32[G,nq,k], idx int64[G,nq,k]
  * (global row ids, -1 = empty) -> out [nq,k] by (d2 asc, idx asc). */
 VQ_API int vq_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k,

@@ -273,6 +273,37 @@ def test_eval_moment_random(vq, case):
     np.testing.assert_allclose(rec2.cpu().numpy(), reco2, rtol=0, atol=1e-12)
 
 
+@pytest.mark.parametrize("C,device_input", [(512, False), (64, True), (13, False)])
+def test_window_means_match_numpy_mean(vq, C, device_input):
+    """f1: every moment feature equals the reference's np.mean(feat[:, lo:hi], axis=1) (:1140-1143) to 1e-6."""
+    import torch
+    from vqwild_b200.retrieval import garner_moments
+    rng = np.random.RandomState(11)
+    vids = []
+    for v, T in enumerate([190, 33, 16, 2400 if C != 512 else 700, 5000 if C == 13 else 60, 455]):
+        f = rng.rand(C, T).astype(np.float32)
+        f /= np.linalg.norm(f, axis=0, keepdims=True)          # feat_func: unit norm per time step (main.py:232)
+        vids.append(dict(feat=f, video_id="v%d" % v, activitynet_duration=T / 3.0 + 0.4,
+                         annotations=[dict(segment=[1.0, T / 6.0], label="a")]))
+    gv = [dict(g, feat=torch.from_numpy(g["feat"]).cuda()) for g in vids] if device_input else vids
+    out = garner_moments(gv, ["a"])
+    feat = out["feat"].cpu().numpy() if device_input else out["feat"]
+    w = 0
+    for v, g in enumerate(vids):
+        T = g["feat"].shape[1]
+        for cpm in range(1, 27):
+            for st in range(0, int(g["activitynet_duration"]) - 5 * cpm, 5):
+                a, z = st * 3, (st + 5 * cpm) * 3
+                if z > T:
+                    continue
+                ref = np.mean(g["feat"][:, a:z], axis=1)
+                assert out["start_sec"][w] == st and out["end_sec"][w] == st + 5 * cpm and out["video_id"][w] == g["video_id"]
+                np.testing.assert_allclose(feat[w], ref, rtol=0, atol=1e-6)
+                w += 1
+        assert w == out["seg_start"][v + 1]
+    assert w == feat.shape[0]
+
+
 def _golden_trimmed(golden, query_num=1):
     feat, rows = golden["tr_feat"], golden["tr_q_list_rows"]
     acc = np.zeros((rows.shape[0], feat.shape[1]), np.float32)

@@ -141,3 +141,50 @@ def test_sharded_search_world2_gloo(tmp_path):
     mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     for r in range(2):
         assert open(os.path.join(str(tmp_path), "rank%d" % r)).read() == "ok"
+
+
+def _ref_garner(duration, feat_length, annotations, possible, fps=3, stride=1, clip_length_sec=5, max_cpm=26):
+    """Scalar restatement of garner_feat's loops (dataloader_baseline.py:1094-1147), feature means aside."""
+    def iou_(min1, max1, min2, max2):                                           # :1096-1098
+        overlap = max(0, min(max1, max2) - max(min1, min2))
+        return overlap * 1.0 / (max(max2, max1) - min(min1, min2))
+
+    out = []
+    for cpm in range(1, max_cpm + 1):                                            # :1116
+        for st in range(0, int(duration) - clip_length_sec * cpm, clip_length_sec):
+            dur = clip_length_sec * cpm
+            lf = [st * fps // stride, (st + dur) * fps // stride]
+            if lf[1] > feat_length:                                              # :1136
+                continue
+            best_iou, best = -1, None
+            for ann in annotations:                                              # :1103-1113
+                v = iou_(ann["segment"][0], ann["segment"][1], st, st + dur)
+                if v > best_iou and ann["label"] in possible:
+                    best, best_iou = (ann["label"], v), v
+            out.append((st, st + dur, lf[0], lf[1], best))
+    return out
+
+
+def test_moment_grid_and_closest_hit_match_reference_loops():
+    from vqwild_b200.retrieval import clip_grid, closest_hits, moment_grid
+    rng = np.random.RandomState(3)
+    possible = ["a", "b", "c"]
+    for trial in range(25):
+        duration = float(rng.uniform(4, 240))
+        feat_length = int(duration * 3) - int(rng.randint(0, 40))
+        anns = [dict(segment=sorted(rng.uniform(0, duration, 2).tolist()), label=str(rng.choice(["a", "b", "c", "zzz"])))
+                for _ in range(int(rng.randint(0, 5)))]
+        if trial == 0:
+            anns = [dict(segment=[0.0, 10.0], label="a"), dict(segment=[0.0, 10.0], label="b")]  # exact IoU tie: first wins
+        ref = _ref_garner(duration, feat_length, anns, possible)
+        s, e, lo, hi = moment_grid(duration, feat_length)
+        assert [tuple(x) for x in np.stack([s, e, lo, hi], 1).tolist()] == [r[:4] for r in ref]
+        lab, iou = closest_hits(s, e, anns, possible)
+        for i, r in enumerate(ref):
+            if r[4] is None:
+                assert lab[i] is None and iou[i] == 0.0
+            else:
+                assert lab[i] == r[4][0] and iou[i] == r[4][1]  # same float64 operations: bit-equal
+        cs, ce, clo, chi = clip_grid(duration, feat_length)
+        ref_c = [(c, c + 6, c * 3, (c + 6) * 3) for c in range(0, int(duration), 6) if (c + 6) * 3 <= feat_length]  # :809-817
+        assert [tuple(x) for x in np.stack([cs, ce, clo, chi], 1).tolist()] == ref_c

@@ -493,6 +493,37 @@ int vq_nms1d_segmented(const double *dets, const int64_t *offsets, int64_t nseg,
     return VQ_OK;
 }
 
+int vq_window_means(const float *feat, int C, int64_t Ttot, const int64_t *vid_t0, const int64_t *win_start, int64_t V,
+                    const int32_t *lo, const int32_t *hi, float *out, void *stream) {
+    VQ_CHECK(feat && vid_t0 && win_start && lo && hi && out, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(!is_device_ptr(vid_t0) && !is_device_ptr(win_start), VQ_ERR_INVALID, "vid_t0 / win_start must be host memory");
+    VQ_CHECK(C >= 1 && V >= 0 && Ttot >= 0, VQ_ERR_INVALID, "bad sizes");
+    VQ_TRY(check_device());
+    if (V == 0) return VQ_OK;
+    VQ_CHECK(vid_t0[0] == 0 && vid_t0[V] == Ttot && win_start[0] == 0, VQ_ERR_INVALID, "offsets must start at 0 and cover Ttot");
+    int64_t Tmax = 0;
+    for (int64_t v = 0; v < V; ++v) {
+        VQ_CHECK(vid_t0[v] <= vid_t0[v + 1] && win_start[v] <= win_start[v + 1], VQ_ERR_INVALID, "offsets not monotone at %lld",
+                 (long long)v);
+        Tmax = std::max(Tmax, vid_t0[v + 1] - vid_t0[v]);
+    }
+    const int64_t nw = win_start[V];
+    cudaStream_t st = (cudaStream_t)stream;
+    In f, t0, ws, l, h;
+    Out o;
+    VQ_TRY(f.bind(feat, (size_t)C * Ttot * 4, st));
+    VQ_TRY(t0.bind(vid_t0, (size_t)(V + 1) * 8, st));
+    VQ_TRY(ws.bind(win_start, (size_t)(V + 1) * 8, st));
+    VQ_TRY(l.bind(lo, (size_t)nw * 4, st));
+    VQ_TRY(h.bind(hi, (size_t)nw * 4, st));
+    VQ_TRY(o.bind(out, (size_t)nw * C * 4, st));
+    VQ_TRY(launch_window_means(f.as<float>(), C, Ttot, t0.as<int64_t>(), ws.as<int64_t>(), V, Tmax, l.as<int32_t>(),
+                               h.as<int32_t>(), o.as<float>(), st));
+    VQ_TRY(o.finish(st));
+    VQ_CUDA(cudaStreamSynchronize(st));  // vid_t0 / win_start staging copies read host memory
+    return VQ_OK;
+}
+
 int vq_pdist(const float *A, int64_t B, int d, float eps, float *dist, void *stream) {
     VQ_CHECK(A && dist, VQ_ERR_INVALID, "NULL argument");
     VQ_TRY(check_device());

@@ -142,6 +142,8 @@ struct MomentNmsParams {
     uint8_t *kept;               // [nq_tile, n]
     uint64_t *vbest;             // [nq_tile, nseg]
 };
+int launch_window_means(const float *feat, int C, int64_t Ttot, const int64_t *vid_t0, const int64_t *win_start, int64_t V,
+                        int64_t Tmax, const int32_t *lo, const int32_t *hi, float *out, cudaStream_t st);
 static constexpr int kMomentWarpCap = 256, kMomentBlockCap = 4096;
 int launch_moment_nms(const MomentNmsParams &p, const int32_t *small_list, int n_small, const int32_t *large_list,
                       int n_large, cudaStream_t st);

@@ -50,8 +50,7 @@ struct TcLayout {
     static constexpr int OFF_EOFF = OFF_REX + 8 * TEXTRA * 8;  // int[260] CSR offsets of the gradient gather lists
     static constexpr int OFF_ECNT = OFF_EOFF + 1040;        // int[256] counters
     static constexpr int OFF_ENT = OFF_ECNT + 1024;         // uint16[768] entries
-    static constexpr int OFF_PERM = OFF_ENT + 1536;         // uint8[256] rows by gather-list length, longest first
-    static constexpr int OFF_EN2 = OFF_PERM + 256;          // uint2[1024] gather entries of pass 3
+    static constexpr int OFF_EN2 = OFF_ENT + 1536;          // uint2[1024] gather entries of pass 3
     static constexpr int OFF_NL = OFF_EN2 + 8192;           // float2[256] (|row|^2, label bits): one LDS.128 per two columns
     static constexpr int OFF_MISC = OFF_NL + 2048;          // int[16]
     static constexpr int OFF_BAR = OFF_MISC + 64;           // full[S] empty[S] tfull tempty
@@ -142,7 +141,6 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
     int *s_eoff = (int *)(smem + L::OFF_EOFF);
     int *s_ecnt = (int *)(smem + L::OFF_ECNT);
     uint16_t *s_ent = (uint16_t *)(smem + L::OFF_ENT);
-    uint8_t *s_perm = smem + L::OFF_PERM;
     float2 *s_nl = (float2 *)(smem + L::OFF_NL);
     uint2 *s_en2 = (uint2 *)(smem + L::OFF_EN2);
     int *s_misc = (int *)(smem + L::OFF_MISC);  // [0] max |row|^2 bits  [1] T  [2] bad flag  [4..11] scan partials

@@ -134,3 +134,78 @@ class ARV_Retrieval_Moment:
 
     def evaluation(self):
         return self.ranking()
+
+
+# ---------------------------------------------------------------------------------------------
+# the gallery builders that run right before the index build
+# ---------------------------------------------------------------------------------------------
+def moment_grid(duration, feat_length, fps=3, temporal_stride=1, clip_length_sec=5, max_clip_per_moment=26):
+    """The sliding-moment grid of garner_feat (dataloader_baseline.py:1116-1137): for every
+    clips_per_moment in 1..max and every start in range(0, int(duration) - 5*cpm, 5) whose frame window
+    fits the features.  Returns (start_sec, end_sec, lo, hi) int arrays in the reference's order."""
+    ss, ee, lo, hi = [], [], [], []
+    for cpm in range(1, max_clip_per_moment + 1):
+        st = np.arange(0, int(duration) - clip_length_sec * cpm, clip_length_sec, dtype=np.int64)
+        if st.size == 0:
+            continue
+        a = st * fps // temporal_stride
+        z = (st + clip_length_sec * cpm) * fps // temporal_stride
+        keep = z <= feat_length                                                   # :1136
+        ss.append(st[keep]), ee.append(st[keep] + clip_length_sec * cpm), lo.append(a[keep]), hi.append(z[keep])
+    if not ss:
+        e = np.zeros(0, np.int64)
+        return e, e, e, e
+    return tuple(np.concatenate(x) for x in (ss, ee, lo, hi))
+
+
+def clip_grid(duration, feat_length, fps=3, temporal_stride=1, clip_sec=6):
+    """Non-overlapping clip grid of ARV_Retrieval_Clip's garner_feat (:809-817)."""
+    st = np.arange(0, int(duration), clip_sec, dtype=np.int64)
+    a, z = st * fps // temporal_stride, (st + clip_sec) * fps // temporal_stride
+    keep = z <= feat_length
+    return st[keep], st[keep] + clip_sec, a[keep], z[keep]
+
+
+def closest_hits(start_sec, end_sec, annotations, possible_classes):
+    """calculate_closest_hit (:1100-1114) for every window of one video, vectorised over the windows with the
+    same float64 operations: best-IoU annotation among ``possible_classes`` (first wins on ties; an
+    annotation outside the classes never becomes the hit).  Returns (label list or None, iou float64[n])."""
+    n = len(start_sec)
+    best_iou = np.full(n, -1.0)
+    best_lab = np.full(n, -1, np.int64)
+    s = np.asarray(start_sec, np.float64)
+    e = np.asarray(end_sec, np.float64)
+    for k, ann in enumerate(annotations):
+        g0, g1 = float(ann["segment"][0]), float(ann["segment"][1])
+        overlap = np.maximum(0.0, np.minimum(g1, e) - np.maximum(g0, s))
+        iou = overlap * 1.0 / (np.maximum(e, g1) - np.minimum(g0, s))
+        better = (iou > best_iou) & (ann["label"] in possible_classes)
+        best_iou = np.where(better, iou, best_iou)
+        best_lab = np.where(better, k, best_lab)
+    labels = [annotations[k]["label"] if k >= 0 else None for k in best_lab]
+    return labels, np.where(best_lab >= 0, best_iou, 0.0)
+
+
+def garner_moments(gallery_videos, possible_classes, fps=3, temporal_stride=1, clip_length_sec=5, max_clip_per_moment=26):
+    """All moments of all untrimmed videos in one device pass (the reference loops garner_feat over the
+    videos on the host, :1153-1172).  ``gallery_videos``: dicts with ``feat`` [C, T_v] (numpy or CUDA tensor),
+    ``video_id``, ``activitynet_duration``, ``annotations``.  Returns dict(feat [n, C] where the features
+    live, video_id list, start_sec, end_sec, hit_label list, iou, seg_start) ready for ``IndexFlatL2``."""
+    from . import ops
+    t0, ws, los, his, ss, ee, vids, labs, ious = [0], [0], [], [], [], [], [], [], []
+    for g in gallery_videos:
+        T = int(g["feat"].shape[1])
+        s, e, lo, hi = moment_grid(g["activitynet_duration"], T, fps, temporal_stride, clip_length_sec, max_clip_per_moment)
+        lab, iou = closest_hits(s, e, g["annotations"], possible_classes)
+        t0.append(t0[-1] + T), ws.append(ws[-1] + len(s))
+        los.append(lo), his.append(hi), ss.append(s), ee.append(e), labs.extend(lab), ious.append(iou)
+        vids.extend([g["video_id"]] * len(s))
+    feats = [g["feat"] for g in gallery_videos]
+    if feats and type(feats[0]).__module__.startswith("torch"):
+        import torch
+        cat = torch.cat(feats, dim=1).contiguous()
+    else:
+        cat = np.ascontiguousarray(np.concatenate(feats, axis=1), dtype=np.float32)
+    out = ops.window_means(cat, t0, ws, np.concatenate(los).astype(np.int32), np.concatenate(his).astype(np.int32))
+    return dict(feat=out, video_id=vids, start_sec=np.concatenate(ss), end_sec=np.concatenate(ee), hit_label=labs,
+                iou=np.concatenate(ious), seg_start=np.asarray(ws, np.int64))
