@@ -181,6 +181,35 @@ VQ_API int vq_triplet_last_handed_back(void);
 VQ_API int vq_triplet_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T,
                             float margin, float *loss, float *grad, void *stream);
 
+/* ------------------------------------------------------------------------------------
+ * f4. The other criteria of misc_utils/metric_learning_loss.py on the tuples the host samplers drew
+ * (same forward(batch, labels) modules on the Python side); f3. the memory-distance logits of the
+ * VA / VASA heads.  fp32; all pointers host or device; gradients may be NULL (forward only).
+ *   vq_margin_given   MarginLoss.forward :520-565 (nu = 0): trip int32[T,3], beta_t f32[T] = the margin
+ *                     parameter of each triplet's anchor class (:543-547) or the constant; outputs loss f32[1],
+ *                     grad f32[B,d], grad_beta_t f32[T] (scatter to classes on the caller's side), pair_count
+ *                     f32[1] = triplets with an active term (:552-554: bool + bool is a logical or).
+ *   vq_npair_given    NPairLoss.forward :397-457: tuples int32[P, 2+N] = (anchor, positive, N negatives).
+ *   vq_proxynca       ProxyNCALoss.forward :593-635: emb f32[B,d], proxies f32[C,d], labels int32[B].
+ *   vq_sphere_weights Sampler.inverse_sphere_distances :291-324 for every anchor: dist f32[B,B] (pdist clamped
+ *                     at the lower cutoff, :215), labels int32[B], dim = embedding size -> q f32[B,B], rows sum to 1.
+ *   vq_memory_logits  models/resnet18_va.py:172-184, resnet18_vasa.py:198-206, :217-229:
+ *                     logits[b,k] = -|normalize(x_b) - mem_k|_2 / temperature (f32[B,K]); with grad_logits
+ *                     f32[B,K] also grad_x f32[B,d] (through the normalisation) and/or grad_mem f32[K,d].
+ * ---------------------------------------------------------------------------------- */
+VQ_API int vq_margin_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T,
+                           const float *beta_t, float margin, float *loss, float *grad,
+                           float *grad_beta_t, float *pair_count, void *stream);
+VQ_API int vq_npair_given(const float *emb, int64_t B, int d, const int32_t *tuples, int64_t P, int N,
+                          float l2, float *loss, float *grad, void *stream);
+VQ_API int vq_proxynca(const float *emb, const float *proxies, const int32_t *labels, int64_t B,
+                       int64_t C, int d, float *loss, float *grad_emb, float *grad_proxies, void *stream);
+VQ_API int vq_sphere_weights(const float *dist, const int32_t *labels, int64_t B, int dim, float *q,
+                             void *stream);
+VQ_API int vq_memory_logits(const float *x, const float *mem, int64_t B, int64_t K, int d,
+                            float temperature, float *logits, const float *grad_logits, float *grad_x,
+                            float *grad_mem, void *stream);
+
 /* a1. Pre-match pooling: F.normalize(p=2, dim=1) per time step (main.py:232) + temporal mean
  * (dataloader_baseline.py:1481).  x f32[B,C,T] -> out f32[B,C]. */
 VQ_API int vq_pool_normalize(const float *x, int64_t B, int C, int T, float *out, void *stream);

@@ -11,10 +11,11 @@ from .retrieval import ARV_Retrieval, ARV_Retrieval_Moment
 
 
 def __getattr__(name):  # torch-dependent pieces are imported lazily
-    if name in ("TripletLoss", "Sampler", "loss_select", "pdist"):
+    if name in ("TripletLoss", "Sampler", "loss_select", "pdist", "MarginLoss", "NPairLoss", "ProxyNCALoss", "CEClassLoss",
+                "memory_logits"):
         from . import loss
         return getattr(loss, name)
-    if name in ("pool_normalize", "topk_merge", "l2sq", "sharded_search"):
+    if name in ("pool_normalize", "topk_merge", "l2sq", "sharded_search", "window_means"):
         from . import ops
         return getattr(ops, name)
     raise AttributeError(name)

@@ -524,6 +524,125 @@ int vq_window_means(const float *feat, int C, int64_t Ttot, const int64_t *vid_t
     return VQ_OK;
 }
 
+int vq_margin_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T, const float *beta_t, float margin,
+                    float *loss, float *grad, float *grad_beta_t, float *pair_count, void *stream) {
+    VQ_CHECK(emb && trip && beta_t && loss, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(B >= 1 && d >= 1 && T >= 0, VQ_ERR_INVALID, "bad sizes");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In e, tr, be;
+    Out oL, oG, oB, oP;
+    Tmp sc;
+    VQ_TRY(e.bind(emb, (size_t)B * d * 4, st));
+    VQ_TRY(tr.bind(trip, (size_t)T * 12, st));
+    VQ_TRY(be.bind(beta_t, (size_t)T * 4, st));
+    VQ_TRY(oL.bind(loss, 4, st));
+    VQ_TRY(oG.bind(grad, (size_t)B * d * 4, st));
+    VQ_TRY(oB.bind(grad_beta_t, (size_t)T * 4, st));
+    VQ_TRY(oP.bind(pair_count, 4, st));
+    VQ_TRY(sc.alloc((size_t)(4 * T + 4) * 4, st));
+    VQ_TRY(launch_margin_given(e.as<float>(), B, d, tr.as<int32_t>(), T, be.as<float>(), 1, margin, oL.as<float>(),
+                               grad ? oG.as<float>() : nullptr, grad_beta_t ? oB.as<float>() : nullptr,
+                               pair_count ? oP.as<float>() : nullptr, (float *)sc.p, st));
+    VQ_TRY(oL.finish(st));
+    VQ_TRY(oG.finish(st));
+    VQ_TRY(oB.finish(st));
+    VQ_TRY(oP.finish(st));
+    if (oL.host || oG.host || oB.host || oP.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_npair_given(const float *emb, int64_t B, int d, const int32_t *tuples, int64_t P, int N, float l2, float *loss,
+                   float *grad, void *stream) {
+    VQ_CHECK(emb && tuples && loss, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(B >= 1 && d >= 1 && P >= 0 && N >= 0 && P <= 65535, VQ_ERR_INVALID, "bad sizes");
+    VQ_CHECK(((size_t)d + N) * 4 <= 200 * 1024, VQ_ERR_CAPACITY, "d + N too large for one block");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In e, tu;
+    Out oL, oG;
+    Tmp sc;
+    VQ_TRY(e.bind(emb, (size_t)B * d * 4, st));
+    VQ_TRY(tu.bind(tuples, (size_t)P * (2 + N) * 4, st));
+    VQ_TRY(oL.bind(loss, 4, st));
+    VQ_TRY(oG.bind(grad, (size_t)B * d * 4, st));
+    VQ_TRY(sc.alloc(((size_t)P * N + 3 * P + 4) * 4, st));
+    VQ_TRY(launch_npair_given(e.as<float>(), B, d, tu.as<int32_t>(), (int)P, N, l2, oL.as<float>(),
+                              grad ? oG.as<float>() : nullptr, (float *)sc.p, st));
+    VQ_TRY(oL.finish(st));
+    VQ_TRY(oG.finish(st));
+    if (oL.host || oG.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_proxynca(const float *emb, const float *proxies, const int32_t *labels, int64_t B, int64_t C, int d, float *loss,
+                float *grad_emb, float *grad_proxies, void *stream) {
+    VQ_CHECK(emb && proxies && labels && loss, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(B >= 1 && C >= 2 && d >= 1 && d <= 12288 && B <= (1 << 20) && C <= (1 << 20), VQ_ERR_INVALID, "bad sizes");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In e, pr, la;
+    Out oL, oG, oP;
+    Tmp sc;
+    VQ_TRY(e.bind(emb, (size_t)B * d * 4, st));
+    VQ_TRY(pr.bind(proxies, (size_t)C * d * 4, st));
+    VQ_TRY(la.bind(labels, (size_t)B * 4, st));
+    VQ_TRY(oL.bind(loss, 4, st));
+    VQ_TRY(oG.bind(grad_emb, (size_t)B * d * 4, st));
+    VQ_TRY(oP.bind(grad_proxies, (size_t)C * d * 4, st));
+    VQ_TRY(sc.alloc(proxynca_scratch_floats((int)B, (int)C, d) * 4, st));
+    VQ_TRY(launch_proxynca(e.as<float>(), pr.as<float>(), la.as<int32_t>(), (int)B, (int)C, d, oL.as<float>(),
+                           grad_emb ? oG.as<float>() : nullptr, grad_proxies ? oP.as<float>() : nullptr, (float *)sc.p, st));
+    VQ_TRY(oL.finish(st));
+    VQ_TRY(oG.finish(st));
+    VQ_TRY(oP.finish(st));
+    if (oL.host || oG.host || oP.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_sphere_weights(const float *dist, const int32_t *labels, int64_t B, int dim, float *q, void *stream) {
+    VQ_CHECK(dist && labels && q, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(B >= 1 && B <= 65535 && dim >= 1, VQ_ERR_INVALID, "bad sizes");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In di, la;
+    Out o;
+    VQ_TRY(di.bind(dist, (size_t)B * B * 4, st));
+    VQ_TRY(la.bind(labels, (size_t)B * 4, st));
+    VQ_TRY(o.bind(q, (size_t)B * B * 4, st));
+    VQ_TRY(launch_sphere_weights(di.as<float>(), la.as<int32_t>(), (int)B, dim, o.as<float>(), st));
+    VQ_TRY(o.finish(st));
+    if (o.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_memory_logits(const float *x, const float *mem, int64_t B, int64_t K, int d, float temperature, float *logits,
+                     const float *grad_logits, float *grad_x, float *grad_mem, void *stream) {
+    VQ_CHECK(x && mem && (logits || grad_logits), VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(B >= 1 && K >= 1 && d >= 1 && d <= 12288 && B <= (1 << 20) && K <= (1 << 20), VQ_ERR_INVALID, "bad sizes");
+    VQ_CHECK(temperature > 0.f, VQ_ERR_INVALID, "temperature must be positive");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In xi, mi, gi;
+    Out oL, oX, oM;
+    Tmp sc;
+    VQ_TRY(xi.bind(x, (size_t)B * d * 4, st));
+    VQ_TRY(mi.bind(mem, (size_t)K * d * 4, st));
+    VQ_TRY(gi.bind(grad_logits, (size_t)B * K * 4, st));
+    VQ_TRY(oL.bind(logits, (size_t)B * K * 4, st));
+    VQ_TRY(oX.bind(grad_x, (size_t)B * d * 4, st));
+    VQ_TRY(oM.bind(grad_mem, (size_t)K * d * 4, st));
+    VQ_TRY(sc.alloc(memory_logits_scratch_floats((int)B, (int)K, d) * 4, st));
+    VQ_TRY(launch_memory_logits(xi.as<float>(), mi.as<float>(), (int)B, (int)K, d, temperature,
+                                logits ? oL.as<float>() : nullptr, gi.as<float>(), grad_x ? oX.as<float>() : nullptr,
+                                grad_mem ? oM.as<float>() : nullptr, (float *)sc.p, st));
+    VQ_TRY(oL.finish(st));
+    VQ_TRY(oX.finish(st));
+    VQ_TRY(oM.finish(st));
+    if (oL.host || oX.host || oM.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
 int vq_pdist(const float *A, int64_t B, int d, float eps, float *dist, void *stream) {
     VQ_CHECK(A && dist, VQ_ERR_INVALID, "NULL argument");
     VQ_TRY(check_device());

@@ -144,6 +144,19 @@ struct MomentNmsParams {
 };
 int launch_window_means(const float *feat, int C, int64_t Ttot, const int64_t *vid_t0, const int64_t *win_start, int64_t V,
                         int64_t Tmax, const int32_t *lo, const int32_t *hi, float *out, cudaStream_t st);
+// vq_losses.cu (f3 / f4)
+int launch_memory_logits(const float *x, const float *mem, int B, int K, int d, float temperature, float *logits,
+                         const float *G, float *gx, float *gmem, float *scratch, cudaStream_t st);
+size_t memory_logits_scratch_floats(int B, int K, int d);
+int launch_proxynca(const float *emb, const float *proxies, const int32_t *labels, int B, int C, int d, float *loss,
+                    float *gemb, float *gprox, float *scratch, cudaStream_t st);
+size_t proxynca_scratch_floats(int B, int C, int d);
+int launch_margin_given(const float *emb, int64_t B, int d, const int32_t *trip, int64_t T, const float *beta_t,
+                        int beta_stride, float margin, float *loss, float *grad, float *gbeta, float *pair_count,
+                        float *scratch, cudaStream_t st);
+int launch_npair_given(const float *emb, int64_t B, int d, const int32_t *tup, int P, int N, float l2, float *loss,
+                       float *grad, float *scratch, cudaStream_t st);
+int launch_sphere_weights(const float *dist, const int32_t *labels, int B, int dim, float *q, cudaStream_t st);
 static constexpr int kMomentWarpCap = 256, kMomentBlockCap = 4096;
 int launch_moment_nms(const MomentNmsParams &p, const int32_t *small_list, int n_small, const int32_t *large_list,
                       int n_large, cudaStream_t st);
