@@ -188,3 +188,38 @@ def test_moment_grid_and_closest_hit_match_reference_loops():
         cs, ce, clo, chi = clip_grid(duration, feat_length)
         ref_c = [(c, c + 6, c * 3, (c + 6) * 3) for c in range(0, int(duration), 6) if (c + 6) * 3 <= feat_length]  # :809-817
         assert [tuple(x) for x in np.stack([cs, ce, clo, chi], 1).tolist()] == ref_c
+
+
+def test_columnar_feature_cache_round_trip(tmp_path):
+    """f2: the reference's feat_cache.pkl (dataloader_baseline.py:1447-1500) -> columnar npz -> the same lists."""
+    import pickle
+    from vqwild_b200 import cache
+    rng = np.random.RandomState(0)
+    gallery = [dict(feat=rng.rand(16).astype(np.float32), label=["a", "b", "noise"][i % 3], video_id="v_%03d" % (i // 2),
+                    is_query=int(i % 4 == 0), retrieval_type=["base", "novel", "noise"][i % 3], frame_info=[i, i + 5],
+                    border=(1.5, 2.5)) for i in range(30)]
+    queries = [g for g in gallery if g["label"] != "noise"]           # a filter of the gallery, as :1486-1491
+    pkl = tmp_path / "feat_cache.pkl"
+    with open(pkl, "wb") as f:
+        pickle.dump(dict(query_list=queries, gallery_list=gallery), f)
+    npz = cache.convert_feat_cache(str(pkl), str(tmp_path / "feat_cache.npz"))
+    q2, g2 = cache.load_feat_cache(npz)
+    assert len(g2) == 30 and len(q2) == len(queries)
+    for a, b in zip(gallery, g2):
+        assert np.array_equal(a["feat"], b["feat"]) and a["label"] == b["label"] and a["video_id"] == b["video_id"]
+        assert a["is_query"] == b["is_query"] and a["retrieval_type"] == b["retrieval_type"]
+        assert b["frame_info"] == a["frame_info"] and tuple(b["border"]) == a["border"]
+    assert all(q is g2[i] for q, i in zip(q2, [k for k, g in enumerate(gallery) if g["label"] != "noise"]))
+    cols = cache.load_columns(npz, "gallery")
+    assert cols["feat"].shape == (30, 16) and cols["feat"].flags["C_CONTIGUOUS"] and cols["label"].dtype == np.int32
+    qc = cache.load_columns(npz, "query")
+    assert qc["feat"].shape[0] == len(queries)
+    # moment gallery (:1140-1147): closest_hit dicts / None, separate query items
+    mom = [dict(feat=rng.rand(8).astype(np.float32), video_id="u%d" % (i // 5), start_sec=5 * (i % 5), end_sec=5 * (i % 5) + 10,
+                closest_hit=None if i % 3 == 0 else dict(label="a", iou=0.1 * (i % 7), gt=[1.0, 2.0], pred=[0, 5])) for i in range(20)]
+    mq = [dict(feat=rng.rand(8).astype(np.float32), label="a", video_id="q%d" % i, retrieval_type="base") for i in range(4)]
+    cache.save_feat_cache(str(tmp_path / "m.npz"), mq, mom)
+    q3, g3 = cache.load_feat_cache(str(tmp_path / "m.npz"))
+    assert [m["closest_hit"] for m in g3] == [m["closest_hit"] for m in mom]
+    assert [(m["start_sec"], m["end_sec"], m["video_id"]) for m in g3] == [(m["start_sec"], m["end_sec"], m["video_id"]) for m in mom]
+    assert [q["label"] for q in q3] == ["a"] * 4 and np.array_equal(q3[2]["feat"], mq[2]["feat"])
