@@ -126,6 +126,17 @@ def _worker(rank, world, port, tmp):
                                 merge=lambda a, b: orc.topk_merge(a.numpy(), b.numpy()))
     Do, Io = orc.search(q, g, k)
     ok = np.array_equal(Im, Io) and np.array_equal(np.asarray(Dm).view(np.uint32), Do.view(np.uint32))
+    # query-sharded evaluation: per-rank slice -> one all-gather of [ap, R@30, R@50, R@100] rows
+    gl_, gv_ = rng.integers(0, 9, n).astype(np.int32), (np.arange(n) // 3).astype(np.int32)
+    ql_, qi_ = rng.integers(0, 9, nq).astype(np.int32), rng.integers(0, n // 3, (nq, 5)).astype(np.int32)
+
+    def eval_fn(q0, q1):
+        ap, rec, _, _ = orc.eval_trimmed(q[q0:q1], g, gl_, gv_, ql_[q0:q1], qi_[q0:q1])   # stand-in for the CUDA eval
+        return ap, rec
+
+    ap, rec = ops.sharded_eval(eval_fn, nq)
+    apo, reco, _, _ = orc.eval_trimmed(q, g, gl_, gv_, ql_, qi_)
+    ok = ok and np.array_equal(ap.numpy(), apo) and np.array_equal(rec.numpy(), reco)
     open(os.path.join(tmp, "rank%d" % rank), "w").write("ok" if ok else "mismatch")
     dist.barrier()
     dist.destroy_process_group()

@@ -82,3 +82,35 @@ def window_means(feat, vid_t0, win_start, lo, hi):
     L.check(L.lib().vq_window_means(L.ptr(feat), C.c_int(nch), C.c_int64(Ttot), L.ptr(t0), L.ptr(ws),
                                     C.c_int64(len(t0) - 1), L.ptr(lo_), L.ptr(hi_), L.ptr(out), L.stream_of(feat)))
     return out
+
+
+def query_slice(nq, group=None):
+    """Queries [q0, q1) of this rank when an evaluation is sharded by query."""
+    import torch.distributed as dist
+    ws, r = dist.get_world_size(group), dist.get_rank(group)
+    return r * nq // ws, (r + 1) * nq // ws
+
+
+def sharded_eval(eval_fn, nq, group=None, device=None):
+    """mAP evaluation over several GPUs.  The evaluators rank the FULL gallery for every query (k = ntotal,
+    dataloader_baseline.py:1594), and a trimmed / moment gallery (tens of MB to a few GB) fits every GPU, so the
+    evaluation shards by QUERY: rank r runs ``eval_fn(q0, q1) -> (ap[q1-q0], recall[q1-q0,3])`` on its slice
+    against its full local index and ONE all-gather of the per-query [ap, R@30, R@50, R@100] rows (32 bytes per
+    query) puts the complete vectors on every rank.  No score ever crosses NVLink."""
+    import torch
+    import torch.distributed as dist
+    ws = dist.get_world_size(group)
+    q0, q1 = query_slice(nq, group)
+    ap, rec = eval_fn(q0, q1)
+    ap, rec = torch.as_tensor(ap), torch.as_tensor(rec)
+    dev = device if device is not None else ap.device
+    qmax = (nq + ws - 1) // ws + 1
+    mine = torch.zeros((qmax, 4), dtype=torch.float64, device=dev)
+    mine[:q1 - q0, 0] = ap.to(dev)
+    mine[:q1 - q0, 1:] = rec.to(dev)
+    allr = torch.empty((ws * qmax, 4), dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(allr, mine, group=group)
+    allr = allr.view(ws, qmax, 4)
+    parts = [allr[r, :(r + 1) * nq // ws - r * nq // ws] for r in range(ws)]
+    out = torch.cat(parts, 0)
+    return out[:, 0].contiguous(), out[:, 1:].contiguous()
