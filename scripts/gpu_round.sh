@@ -27,6 +27,6 @@ timeout -s KILL 300 python scripts/time_triplet.py > gpurun_out/time_triplet.log
 echo "time_triplet exit $?" | tee -a gpurun_out/status.log
 cat gpurun_out/time_triplet.log
 timeout -s KILL 300 python scripts/clk_triplet.py > gpurun_out/clk_triplet.log 2>&1
-timeout -s KILL 600 ncu --set full --clock-control none --import-source on -k regex:triplet_tc -s 3 -c 1 \
+timeout -s KILL 600 ncu --set full --clock-control none --import-source on -k regex:triplet_tc -s 48 -c 1 \
     -f -o gpurun_out/prof_triplet_tc python scripts/time_triplet.py > gpurun_out/ncu_full_triplet.log 2>&1
 echo "ncu triplet exit $?" | tee -a gpurun_out/status.log

@@ -58,13 +58,39 @@ static bool is_device_ptr(const void *p) {
     return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
+// The library's own stream-ordered pool, one per device.  Freed blocks stay in the pool (release threshold =
+// max): the default pool hands its memory back to the OS at every synchronisation, which put a fresh
+// physical allocation of every staging buffer (~10 ms per 100 MB) on the host's critical path of each call.
+static cudaMemPool_t g_pool[64] = {};
+static int scratch_pool(cudaMemPool_t *out) {
+    int dev = 0;
+    VQ_CUDA(cudaGetDevice(&dev));
+    VQ_CHECK(dev >= 0 && dev < 64, VQ_ERR_INVALID, "device ordinal %d", dev);
+    if (!g_pool[dev]) {
+        cudaMemPoolProps props = {};
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = dev;
+        cudaMemPool_t pool = nullptr;
+        VQ_CUDA(cudaMemPoolCreate(&pool, &props));
+        uint64_t keep = UINT64_MAX;
+        VQ_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+        g_pool[dev] = pool;
+    }
+    *out = g_pool[dev];
+    return VQ_OK;
+}
+
 // Stream-ordered temporary device buffer.
 struct Tmp {
     void *p = nullptr;
     cudaStream_t st = nullptr;
     int alloc(size_t bytes, cudaStream_t s) {
         st = s;
-        VQ_CUDA(cudaMallocAsync(&p, bytes ? bytes : 16, s));
+        cudaMemPool_t pool = nullptr;
+        VQ_TRY(scratch_pool(&pool));
+        VQ_CUDA(cudaMallocFromPoolAsync(&p, bytes ? bytes : 16, pool, s));
         return VQ_OK;
     }
     ~Tmp() {
