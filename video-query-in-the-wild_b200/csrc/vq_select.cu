@@ -25,6 +25,9 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
     uint32_t *aux = (uint32_t *)(ex + ksort);            // [ksort] segmax: video per exact key slot
     float *qs = (float *)(aux + ksort);                  // [d]
     int *scratch = (int *)(qs + p.d);                    // [40]
+    int *cnts = scratch + 40;                            // [nsg] candidates taken from each segment
+    int *offs = cnts + p.segs_per_group;                 // [nsg + 1]
+    int64_t *urs = (int64_t *)(offs + p.segs_per_group + 1 + ((p.d + 1) & 1));  // [nsg] candidate-list rows (8-byte aligned)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t q = blockIdx.x;
     const int qb = (int)(q / kTileM), r = (int)(q % kTileM);
@@ -34,25 +37,50 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
     const int E = nsg * p.kprime;
     const T *qrow = (const T *)p.q + q * p.d;
 
-    // ---- 1. gather ----
+    // ---- 1. gather: per-segment counts first, then one flattened copy with independent loads (the lists of the
+    // later segments are nearly empty once tau has tightened, so the compacted total is a small multiple of k') ----
     for (int i = tid; i < p.d; i += kSelThreads) qs[i] = to_f32<T>(qrow[i]);
     float tau = -INFINITY;
-    int total = 0;
-    for (int c = 0; c < nsg; ++c) {
+    for (int c = tid; c < nsg; c += kSelThreads) {
         const int64_t ur = ((int64_t)segs[c] * p.group_size + member) * kTileM + r;
-        const int cnt = p.cand_cnt[ur];
+        cnts[c] = min(p.cand_cnt[ur], p.kprime);
+        urs[c] = ur;
         tau = fmaxf(tau, p.cand_tau[ur]);
-        total += cnt;
-        const uint64_t *src = p.cand + ur * kCandCap;
-        for (int i = tid; i < p.kprime; i += kSelThreads) keys[c * p.kprime + i] = i < cnt ? src[i] : 0ull;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) tau = fmaxf(tau, __shfl_xor_sync(0xffffffffu, tau, o));
+    if (lane == 0) scratch[32 + warp] = __float_as_int(tau);
+    __syncthreads();
+    tau = fmaxf(fmaxf(__int_as_float(scratch[32]), __int_as_float(scratch[33])),
+                fmaxf(__int_as_float(scratch[34]), __int_as_float(scratch[35])));
+    if (warp == 0) {  // exclusive scan of the counts
+        int run = 0;
+        for (int c0 = 0; c0 < nsg; c0 += 32) {
+            const int v = c0 + lane < nsg ? cnts[c0 + lane] : 0;
+            int inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += u;
+            }
+            if (c0 + lane < nsg) offs[c0 + lane] = run + inc - v;
+            run += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        if (lane == 0) offs[nsg] = run;
     }
     __syncthreads();
-    int m = total;
-    if (total > p.kprime) {
+    for (int idx = tid; idx < E; idx += kSelThreads) {
+        const int c = idx / p.kprime, i = idx - c * p.kprime;
+        if (i < cnts[c]) keys[offs[c] + i] = p.cand[urs[c] * kCandCap + i];
+    }
+    __syncthreads();
+    int m = offs[nsg];
+    if (m > p.kprime) {
         // keep the k' best coarse keys; ties at the cut resolved by the full key (score, then row)
-        const uint32_t Th = block_kth_largest_hi(keys, E, p.kprime, scratch);
+        const int M0 = m;
+        const uint32_t Th = block_kth_largest_hi(keys, M0, p.kprime, scratch);
         int gt = 0;
-        for (int i = tid; i < E; i += kSelThreads) gt += (uint32_t)(keys[i] >> 32) > Th ? 1 : 0;
+        for (int i = tid; i < M0; i += kSelThreads) gt += (uint32_t)(keys[i] >> 32) > Th ? 1 : 0;
         gt = block_sum(gt, scratch);
         // among hi == Th keep the (k' - gt) largest full keys: find that key by a second bisection
         const int need_eq = p.kprime - gt;
@@ -60,7 +88,7 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
         for (int bit = 31; bit >= 0; --bit) {
             const uint32_t cnd = Tl | (1u << bit);
             int cn = 0;
-            for (int i = tid; i < E; i += kSelThreads)
+            for (int i = tid; i < M0; i += kSelThreads)
                 cn += ((uint32_t)(keys[i] >> 32) == Th && (uint32_t)keys[i] >= cnd) ? 1 : 0;
             cn = block_sum(cn, scratch);
             if (cn >= need_eq) Tl = cnd;
@@ -72,9 +100,9 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
         // compact through registers (E <= kSelThreads * 64 guaranteed by the host)
         uint64_t mine[64];
         int nmine = 0;
-        for (int i = tid; i < E; i += kSelThreads) {
+        for (int i = tid; i < M0; i += kSelThreads) {
             uint64_t kk = keys[i];
-            if (kk >= cut && kk != 0ull && nmine < 64) mine[nmine++] = kk;
+            if (kk >= cut && nmine < 64) mine[nmine++] = kk;
         }
         __syncthreads();
         int base = atomicAdd(&scratch[36], nmine);
@@ -82,22 +110,6 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
         __syncthreads();
         m = scratch[36];
         tau = fmaxf(tau, ordered_to_f32(Th));
-    } else {
-        // compact away the empty slots (order irrelevant: exact keys are sorted below)
-        __syncthreads();
-        if (tid == 0) scratch[36] = 0;
-        __syncthreads();
-        uint64_t mine[64];
-        int nmine = 0;
-        for (int i = tid; i < E; i += kSelThreads) {
-            uint64_t kk = keys[i];
-            if (kk != 0ull && nmine < 64) mine[nmine++] = kk;
-        }
-        __syncthreads();
-        int base = atomicAdd(&scratch[36], nmine);
-        for (int i = 0; i < nmine; ++i) keys[base + i] = mine[i];
-        __syncthreads();
-        m = scratch[36];
     }
 
     // ---- 2. canonical re-scoring ----
@@ -177,7 +189,8 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
 size_t select_smem_bytes(const SelectParams &p) {
     const size_t E = (size_t)p.segs_per_group * p.kprime;
     const size_t ks = (size_t)next_pow2(p.kprime);
-    return E * 8 + ks * 8 + ks * 4 + (size_t)p.d * 4 + 40 * 4 + 16;
+    return E * 8 + ks * 8 + ks * 4 + (size_t)p.d * 4 + 40 * 4 + ((size_t)2 * p.segs_per_group + 2) * 4 +
+           (size_t)p.segs_per_group * 8 + 16;
 }
 
 template <typename T, bool SEGMAX>
