@@ -321,6 +321,7 @@ def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
     iou = np.where(hit >= 0, rng.uniform(0, 1, n), 0).astype(np.float32)
     ix = vq.IndexFlatL2(d)
     ix.add(g)
+    gsrc = [g]
     del g
     ix.set_meta(hit, video)
     ix.set_segments(np.arange(0, n + 1, S, dtype=np.int64))
@@ -343,6 +344,16 @@ def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
     out["segmax_cfg2"] = {"workload": "configs[2]: %d queries x %d videos x %d moments x %d-d f32, per-video max + top-100 videos"
                           % (nq, V, S, d), "wall_ms": t * 1e3, "pairs_per_s": nq * n / t,
                           "gemm_topk_ms": tm["gemm_topk_ms"], "tflops_algorithmic": 2.0 * nq * n * d / tm["gemm_topk_ms"] / 1e9}
+    # the same gallery held in bf16 (north_star's bf16-input mode): CTA-pair kernel, one MMA pass
+    ixb = vq.IndexFlatL2(d)
+    ixb.add(torch.cat([ix_rows.to(torch.bfloat16) for ix_rows in gsrc]))
+    ixb.set_segments(np.arange(0, n + 1, S, dtype=np.int64))
+    qb = q.to(torch.bfloat16)
+    t, _ = wall(lambda: ixb.search_segmax(qb, 100), 3)
+    tm = ixb.last_timing()
+    out["segmax_cfg2_bf16"] = {"workload": "configs[2] with bf16 gallery and queries", "wall_ms": t * 1e3, "pairs_per_s": nq * n / t,
+                               "gemm_topk_ms": tm["gemm_topk_ms"], "tflops_algorithmic": 2.0 * nq * n * d / tm["gemm_topk_ms"] / 1e9}
+    del ixb, gsrc
     t, r = wall(lambda: ix.eval_moment(q, ql, ign), 2)
     out["moment_eval_cfg2"] = {"workload": "configs[2]: full moment evaluation (rank all %d moments per query, per-video NMS, "
                                "AP@tIoU0.5, grouped R@30/50/100), %d queries" % (n, nq), "wall_ms": t * 1e3,

@@ -81,7 +81,23 @@ template <>
 __device__ __forceinline__ float canon_d2_row<float>(const float *qs, const float *g, int d) {
     float acc = 0.f;
     int i = 0;
-    if ((((uintptr_t)g) & 15) == 0) {
+    if ((((uintptr_t)g) & 15) == 0 && (((uintptr_t)qs) & 15) == 0) {
+        // eight independent 16-byte loads in flight before the (sequential) chain consumes them: a row gathered at
+        // random from HBM costs one memory latency per batch instead of one per load; the query is read as
+        // LDS.128 (one shared-memory instruction per four chain steps: the MIO queue was the limiter)
+        for (; i + 32 <= d; i += 32) {
+            float4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldg(reinterpret_cast<const float4 *>(g + i) + u);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float4 qv = *reinterpret_cast<const float4 *>(qs + i + 4 * u);
+                acc = canon_step(acc, qv.x, v[u].x);
+                acc = canon_step(acc, qv.y, v[u].y);
+                acc = canon_step(acc, qv.z, v[u].z);
+                acc = canon_step(acc, qv.w, v[u].w);
+            }
+        }
         for (; i + 4 <= d; i += 4) {
             const float4 v = *reinterpret_cast<const float4 *>(g + i);
             acc = canon_step(acc, qs[i], v.x);
@@ -98,7 +114,25 @@ template <>
 __device__ __forceinline__ float canon_d2_row<__nv_bfloat16>(const float *qs, const __nv_bfloat16 *g, int d) {
     float acc = 0.f;
     int i = 0;
-    if ((((uintptr_t)g) & 15) == 0) {
+    if ((((uintptr_t)g) & 15) == 0 && (((uintptr_t)qs) & 15) == 0) {
+        for (; i + 64 <= d; i += 64) {  // eight 16-byte loads in flight and LDS.128 query reads, as above
+            uint4 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldg(reinterpret_cast<const uint4 *>(g + i) + u);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const float4 qa = *reinterpret_cast<const float4 *>(qs + i + 8 * u);
+                const float4 qb = *reinterpret_cast<const float4 *>(qs + i + 8 * u + 4);
+                acc = canon_step(acc, qa.x, __uint_as_float(v[u].x << 16));
+                acc = canon_step(acc, qa.y, __uint_as_float(v[u].x & 0xffff0000u));
+                acc = canon_step(acc, qa.z, __uint_as_float(v[u].y << 16));
+                acc = canon_step(acc, qa.w, __uint_as_float(v[u].y & 0xffff0000u));
+                acc = canon_step(acc, qb.x, __uint_as_float(v[u].z << 16));
+                acc = canon_step(acc, qb.y, __uint_as_float(v[u].z & 0xffff0000u));
+                acc = canon_step(acc, qb.z, __uint_as_float(v[u].w << 16));
+                acc = canon_step(acc, qb.w, __uint_as_float(v[u].w & 0xffff0000u));
+            }
+        }
         for (; i + 8 <= d; i += 8) {
             const uint4 v = *reinterpret_cast<const uint4 *>(g + i);
             const uint32_t w[4] = {v.x, v.y, v.z, v.w};
