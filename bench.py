@@ -175,7 +175,7 @@ def run_reference(a):
     if rank != 0:
         return
     v, cores, sample, ms = cpu_sample(a, max(1, a.steps), max(0, min(a.warmup, 1)))
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "query-gallery pairs/sec (512-d)", "value": v, "unit": "pairs/s",
         "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -185,7 +185,7 @@ def run_reference(a):
         "gpu_launches": 0,
         "note": "reference is pure Python and absent on the GPU box; this is the OpenMP C port of its matching stage "
                 "(oracle/vq_oracle.c), a faster baseline than the reference's own per-query Python loop",
-    }))
+    })
 
 
 # ---------------------------------------------------------------------------------------------
@@ -558,12 +558,22 @@ def run_b200(a):
     if G > 1:
         dist.barrier()
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if G > 1:
         dist.destroy_process_group()
 
 
+def emit(obj):
+    """The ONE JSON line goes to the process's original stdout; everything else that writes to fd 1 while the
+    bench runs (NCCL prints its version banner there) has been pointed at stderr."""
+    _REAL_STDOUT.write(json.dumps(obj) + "\n")
+    _REAL_STDOUT.flush()
+
+
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse()
     if args.impl == "reference":
         run_reference(args)
