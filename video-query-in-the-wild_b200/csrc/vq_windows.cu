@@ -64,9 +64,9 @@ __global__ void __launch_bounds__(256) window_means_kernel(const float *__restri
         const int w = i / CH, ch = i % CH;
         const int c = c0 + ch;
         if (c >= C) continue;
-        const int a = lo[w0 + w], z = hi[w0 + w];
+        const int a = min(max(lo[w0 + w], 0), T), z = min(max(hi[w0 + w], a), T);  // windows are clipped to the video
         const double s = P[ch * pitch + z] - P[ch * pitch + a];
-        out[(w0 + w) * (int64_t)C + c] = (float)(s / (double)(z - a));
+        out[(w0 + w) * (int64_t)C + c] = z > a ? (float)(s / (double)(z - a)) : 0.f;
     }
 }
 
