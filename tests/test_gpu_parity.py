@@ -587,3 +587,72 @@ def test_full_size_cfg1_properties(vq):
     sub = rng.choice(nq, 48, replace=False)
     Do, Io = orc.search(q[sub], g, k)
     assert np.array_equal(I[sub], Io) and np.array_equal(D[sub].view(np.uint32), Do.view(np.uint32))
+
+
+def test_cfg4_elmo_1024d_k_sweep(vq):
+    """BASELINE configs[4]: 1024-d unit-norm embeddings (ELMo word space), 4096 x 20480, top-100 exact + the
+    k sweep {5, 30, 50, 100} (R@k as the reference's :475-481; AP@k as defined in metrics.ap_at_k)."""
+    rng = np.random.default_rng(31)
+    nq, n, d, k = 4096, 20480, 1024, 100
+    label = rng.integers(0, 200, n).astype(np.int32)              # 40 + 20 + 140 classes
+    g = _emb(rng, n, d, 200, label, scale=False)
+    qrow = rng.choice(n, nq, replace=False)
+    q = np.ascontiguousarray(g[qrow] + 0.05 * _emb(rng, nq, d, scale=False), np.float32)
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    video = np.arange(n, dtype=np.int32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    ix.set_meta(label, video)
+    ign = video[qrow][:, None].astype(np.int32)                   # the query's own item leaves the list
+    D, I = ix.search(q, k, ignore_video=ign)
+    print(ix.last_stats())
+    sub = rng.choice(nq, 40, replace=False)
+    Do, Io = orc.search(q[sub], g, k + 1)
+    for a, s in enumerate(sub):                                   # oracle list with the ignored row removed
+        keep = Io[a] != qrow[s]
+        assert np.array_equal(I[s], Io[a][keep][:k])
+        assert np.array_equal(D[s].view(np.uint32), Do[a][keep][:k].view(np.uint32))
+    ref64 = ((q[sub][:, None, :].astype(np.float64) - g[I[sub]].astype(np.float64)) ** 2).sum(-1)
+    assert np.max(np.abs(D[sub] - ref64) / np.maximum(ref64, 1e-12)) < 1e-5   # fp32 scores: 1e-5 relative (north_star)
+    tp = (label[I] == label[qrow][:, None]).astype(np.int32)
+    n_pos = np.array([(label == label[r]).sum() - 1 for r in qrow])
+    rk, apk = vq.recall_at_k(tp, n_pos), vq.ap_at_k(tp, n_pos)
+    for kk in (5, 30, 50, 100):
+        ref_r = np.array([tp[i, :kk].sum() / (n_pos[i] + 1e-10) for i in range(0, nq, 97)])
+        np.testing.assert_allclose(rk[kk][::97], ref_r, rtol=0, atol=1e-12)
+        ref_ap = []
+        for i in range(0, nq, 97):
+            hits = np.flatnonzero(tp[i, :kk])
+            den = min(n_pos[i], kk)
+            ref_ap.append(sum((j2 + 1) / (h + 1) for j2, h in enumerate(hits)) / den if den else 0.0)
+        np.testing.assert_allclose(apk[kk][::97], ref_ap, rtol=0, atol=1e-12)
+    assert rk[100].mean() >= rk[5].mean()
+    # full-list AP + R@30/50/100 with the reference semantics on the same 1024-d index
+    ap, rec, _ = ix.eval_trimmed(q[sub], label[qrow][sub], ign[sub])
+    apo, reco, _, _ = orc.eval_trimmed(q[sub], g, label, video, label[qrow][sub], ign[sub])
+    np.testing.assert_allclose(ap, apo, rtol=0, atol=1e-9)
+    np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-9)
+    np.testing.assert_allclose(rec[:, 0], rk[30][sub], rtol=0, atol=1e-9)
+
+
+def test_wordembed_topk_mirror(vq):
+    """word_embed/wordembed_retrieval_test.py:9-23 restated with numpy (LA.norm on normalised vectors)."""
+    rng = np.random.default_rng(32)
+    video_embed = {"act_%d" % i: rng.standard_normal(1024).tolist() for i in range(30)}
+    openset = {"k700_%d" % i: rng.standard_normal(1024).tolist() for i in range(700)}
+    got = vq.wordembed_topk(video_embed, openset, k=5)
+    for key, value in video_embed.items():
+        v = np.array(value).reshape(1, -1)
+        v = v / np.linalg.norm(v)
+        res = []
+        for ck, cv in openset.items():
+            c = np.array(cv).reshape(1, -1)
+            c = c / np.linalg.norm(c)
+            res.append((ck, -np.linalg.norm(c - v)))
+        res.sort(key=lambda x: x[1], reverse=True)
+        np.testing.assert_allclose([x[1] for x in got[key]], [x[1] for x in res[:5]], rtol=0, atol=1e-5)
+        # the index works on float32 copies of the float64-normalised vectors: labels agree except where two
+        # float64 scores are closer than float32 resolution
+        true = dict(res)
+        for (lab, _), (_, ref_score) in zip(got[key], res[:5]):
+            assert abs(true[lab] - ref_score) < 1e-5

@@ -157,3 +157,29 @@ class evaluation_metric:
                        pass_content=list(pass_content))
         return dict(ap=o2_hmean, base_map=base_map, novel_map=novel_map, recall=self.full_retrieval_top,
                     base_recall=self.base_retrieval_top, novel_recall=self.novel_retrieval_top, cm_dict=cm_dict)
+
+
+# ---------------------------------------------------------------------------------------------
+# BASELINE.json configs[4]: k-sweep on top-k search results (ELMo 1024-d split 40_20_140)
+# ---------------------------------------------------------------------------------------------
+def recall_at_k(tp_ranked, n_pos, ks=(5, 30, 50, 100)):
+    """R@k as the reference defines it (dataloader_baseline.py:475-481): sum_{i<k} tp_i / (n_pos + 1e-10), for every
+    k of the sweep (5 from word_embed/wordembed_retrieval_test.py:20; 30/50/100 from r_at_n :332).
+    tp_ranked [nq, K] 0/1 in rank order (survivors only), n_pos [nq] = positives in the whole list."""
+    tp = np.asarray(tp_ranked, np.float64)
+    den = np.asarray(n_pos, np.float64) + 1e-10
+    return {int(k): tp[:, :k].sum(1) / den for k in ks}
+
+
+def ap_at_k(tp_ranked, n_pos, ks=(5, 30, 50, 100)):
+    """AP@k.  The reference has no mAP@k (its AP is over the full list, :461); BASELINE.json configs[4] asks for a
+    sweep, so it is DEFINED here: AP@k = sum_{i<=k} P(i) * rel_i / min(n_pos, k), P(i) = precision
+    at rank i; 0 for queries without positives."""
+    tp = np.asarray(tp_ranked, np.float64)
+    prec = np.cumsum(tp, 1) / np.arange(1, tp.shape[1] + 1)
+    npos = np.asarray(n_pos, np.float64)
+    out = {}
+    for k in ks:
+        den = np.minimum(npos, k)
+        out[int(k)] = np.where(den > 0, (prec[:, :k] * tp[:, :k]).sum(1) / np.maximum(den, 1), 0.0)
+    return out

@@ -209,3 +209,20 @@ def garner_moments(gallery_videos, possible_classes, fps=3, temporal_stride=1, c
     out = ops.window_means(cat, t0, ws, np.concatenate(los).astype(np.int32), np.concatenate(his).astype(np.int32))
     return dict(feat=out, video_id=vids, start_sec=np.concatenate(ss), end_sec=np.concatenate(ee), hit_label=labs,
                 iou=np.concatenate(ious), seg_start=np.asarray(ws, np.int64))
+
+
+def wordembed_topk(video_embed, openset_embed, k=5):
+    """word_embed/wordembed_retrieval_test.py:9-23 for ALL keys in one search: both sides L2-normalised
+    (sklearn.preprocessing.normalize), score = -||c - v||_2, best k labels per key.  On unit vectors the squared-L2
+    ranking of IndexFlatL2 is the same order; scores are -sqrt(D).  Returns {key: [(label, score), ...]}."""
+    keys, ckeys = list(video_embed.keys()), list(openset_embed.keys())
+
+    def norm(rows):
+        x = np.asarray(rows, np.float64).reshape(len(rows), -1)
+        return np.ascontiguousarray(x / np.maximum(np.linalg.norm(x, axis=1, keepdims=True), 1e-12), np.float32)
+
+    xq, xb = norm([video_embed[x] for x in keys]), norm([openset_embed[x] for x in ckeys])
+    index = IndexFlatL2(xb.shape[1])
+    index.add(xb)
+    D, I = index.search(xq, min(k, len(ckeys)))
+    return {key: [(ckeys[int(j)], -float(np.sqrt(dd))) for dd, j in zip(D[i], I[i]) if j >= 0] for i, key in enumerate(keys)}
