@@ -11,7 +11,10 @@
 
 namespace vq {
 
-// CH channels per block; dynamic smem: double P[CH][Tmax + 1]
+// CH channels per block; dynamic smem: double P[CH][pitch].  Warp w owns channels w, w+8, ...: the frames are
+// staged coalesced, each lane sums its contiguous slice, a shuffle scan gives the slice offsets, and the slice is
+// rewritten as running sums -- no block-wide serial step.  Windows: one thread per window, CH consecutive channels
+// (one 32-byte sector per window and tile), one reciprocal per window.
 template <int CH>
 __global__ void __launch_bounds__(256) window_means_kernel(const float *__restrict__ feat, int C, int64_t Ttot,
                                                            const int64_t *__restrict__ vid_t0,
@@ -20,53 +23,56 @@ __global__ void __launch_bounds__(256) window_means_kernel(const float *__restri
                                                            float *__restrict__ out, int pitch) {
     extern __shared__ __align__(16) uint8_t sm_raw[];
     double *P = (double *)sm_raw;
-    __shared__ double part[CH][257];
-    const int v = blockIdx.x, c0 = blockIdx.y * CH, tid = threadIdx.x;
+    // channel tiles of one video are neighbours in launch order: their 32-byte pieces of a window row reach L2 together
+    const int ntile = (C + CH - 1) / CH;
+    const int v = blockIdx.x / ntile, c0 = (blockIdx.x % ntile) * CH, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t t0 = vid_t0[v];
     const int T = (int)(vid_t0[v + 1] - t0);
-    const int per = (T + 255) / 256;
-    const int b = min(T, tid * per), e = min(T, b + per);
-    // local inclusive sums of this thread's slice, then the block-wide offsets
-#pragma unroll
-    for (int ch = 0; ch < CH; ++ch) {
+    // stage: P[ch][t + 1] = frame value (coalesced along t)
+    for (int ch = warp; ch < CH; ch += 8) {
         const int c = c0 + ch;
-        double run = 0.0;
+        double *row = P + ch * pitch;
         if (c < C) {
             const float *src = feat + (int64_t)c * Ttot + t0;
-            for (int t = b; t < e; ++t) {
-                run += (double)src[t];
-                P[ch * pitch + t + 1] = run;
-            }
+            for (int t = lane; t < T; t += 32) row[t + 1] = (double)__ldg(src + t);
+        } else {
+            for (int t = lane; t < T; t += 32) row[t + 1] = 0.0;
         }
-        part[ch][tid] = run;
-    }
-    __syncthreads();
-    if (tid < CH) {
-        double run = 0.0;
-        for (int i = 0; i < 256; ++i) {
-            const double x = part[tid][i];
-            part[tid][i] = run;
-            run += x;
-        }
-        P[tid * pitch] = 0.0;
-    }
-    __syncthreads();
+        if (lane == 0) row[0] = 0.0;
+        __syncwarp();
+        const int per = (T + 31) / 32, b = min(T, lane * per), e = min(T, b + per);
+        double tot = 0.0;
+        for (int t = b; t < e; ++t) tot += row[t + 1];
+        double inc = tot;
 #pragma unroll
-    for (int ch = 0; ch < CH; ++ch) {
-        const double off = part[ch][tid];
-        for (int t = b; t < e; ++t) P[ch * pitch + t + 1] += off;
+        for (int o = 1; o < 32; o <<= 1) {
+            const double u = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += u;
+        }
+        double run = inc - tot;  // sum of the slices before mine
+        for (int t = b; t < e; ++t) {
+            run += row[t + 1];
+            row[t + 1] = run;
+        }
     }
     __syncthreads();
-    // windows of this video: thread <-> (window, channel), CH consecutive channels per window (>= one 32-byte sector)
     const int64_t w0 = win_start[v];
     const int nw = (int)(win_start[v + 1] - w0);
-    for (int i = tid; i < nw * CH; i += 256) {
-        const int w = i / CH, ch = i % CH;
-        const int c = c0 + ch;
-        if (c >= C) continue;
+    for (int w = tid; w < nw; w += 256) {
         const int a = min(max(lo[w0 + w], 0), T), z = min(max(hi[w0 + w], a), T);  // windows are clipped to the video
-        const double s = P[ch * pitch + z] - P[ch * pitch + a];
-        out[(w0 + w) * (int64_t)C + c] = z > a ? (float)(s / (double)(z - a)) : 0.f;
+        const double rl = z > a ? 1.0 / (double)(z - a) : 0.0;
+        float r[CH];
+#pragma unroll
+        for (int ch = 0; ch < CH; ++ch) r[ch] = (float)((P[ch * pitch + z] - P[ch * pitch + a]) * rl);
+        float *dst = out + (w0 + w) * (int64_t)C + c0;
+        if (CH % 4 == 0 && c0 + CH <= C && (C & 3) == 0 && (((uintptr_t)out) & 15) == 0) {
+#pragma unroll
+            for (int ch = 0; ch < CH; ch += 4) *reinterpret_cast<float4 *>(dst + ch) = make_float4(r[ch], r[ch + 1], r[ch + 2], r[ch + 3]);
+        } else {
+#pragma unroll
+            for (int ch = 0; ch < CH; ++ch)
+                if (c0 + ch < C) dst[ch] = r[ch];
+        }
     }
 }
 
@@ -77,7 +83,7 @@ int launch_window_means(const float *feat, int C, int64_t Ttot, const int64_t *v
     auto go = [&](auto kern, int CH) {
         const size_t smem = (size_t)CH * pitch * 8;
         VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        kern<<<dim3((unsigned)V, (unsigned)((C + CH - 1) / CH)), 256, smem, st>>>(feat, C, Ttot, vid_t0, win_start, lo, hi, out,
+        kern<<<(unsigned)(V * ((C + CH - 1) / CH)), 256, smem, st>>>(feat, C, Ttot, vid_t0, win_start, lo, hi, out,
                                                                                pitch);
         VQ_CUDA(cudaGetLastError());
         return VQ_OK;
