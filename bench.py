@@ -195,6 +195,11 @@ def aux_measurements(torch, vq):
     import numpy as np
     dev = "cuda"
     out = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks_hbm = json.load(f).get("hbm_gbs")
+    except (OSError, ValueError):
+        peaks_hbm = None
     # configs[0]: trimmed retrieval eval, 4096 x 20480 x 512 f32, full-list AP + R@N
     rng = np.random.default_rng(0)
     n, nq, d = 20480, 4096, 512
@@ -223,6 +228,18 @@ def aux_measurements(torch, vq):
     out["map_eval_cfg0"] = {"workload": "configs[0]: 4096 queries x 20480 gallery x 512-d f32, full-list AP + R@30/50/100",
                             "wall_ms": min(ts[1:]) * 1e3, "mAP": float(ap.double().mean().item()),
                             "pairs_per_s": nq * n / min(ts[1:])}
+    # the same evaluation by the CPU port (oracle, all host threads) on a bounded sample of the queries
+    try:
+        from oracle import oracle as orc
+        ns = 4 * orc.num_threads()
+        t0 = time.perf_counter()
+        apc, _, _, _ = orc.eval_trimmed(g[qrow[:ns]], g, label, video, label[qrow[:ns]], ign[:ns])
+        dt = time.perf_counter() - t0
+        out["map_eval_cfg0"]["cpu_port"] = {"sample": "%d of the %d queries x full gallery, %d threads" % (ns, nq, orc.num_threads()),
+                                            "wall_ms_sample": dt * 1e3, "wall_ms_extrapolated": dt * 1e3 * nq / ns,
+                                            "max_abs_ap_diff_vs_gpu": float(np.abs(apc - ap[:ns].double().cpu().numpy()).max())}
+    except Exception as e:  # noqa: BLE001
+        out["map_eval_cfg0"]["cpu_port"] = {"error": repr(e)}
     del ix, gd
     # configs[1]: batch-hard triplet fwd+bwd, B=256 D=512 (latency bound) and 4096 such groups (HBM bound)
     from vqwild_b200.loss import TripletLoss
@@ -247,13 +264,69 @@ def aux_measurements(torch, vq):
         nbytes = G * (2 * 256 * 512 * 4 + 256 * 8 + 4)
         out["triplet_cfg1_G%d" % G] = {"workload": "configs[1]: batch-hard triplet fwd+bwd, %d x (256 x 512-d f32)" % G,
                                        "ms": ms, "algorithmic_bytes": nbytes, "GB_per_s": nbytes / ms / 1e6}
+        if G == 1:
+            try:  # the CPU port of the same group (oracle: canonical pdist + mining + loss + gradient gather)
+                from oracle import oracle as orc
+                e_np, l_np = x.detach().cpu().numpy(), lb.cpu().numpy()
+                orc.batchhard_triplet(e_np, l_np, 1.0)
+                t0 = time.perf_counter()
+                orc.batchhard_triplet(e_np, l_np, 1.0)
+                out["triplet_cfg1_G1"]["cpu_port_ms"] = (time.perf_counter() - t0) * 1e3
+            except Exception as e:  # noqa: BLE001
+                out["triplet_cfg1_G1"]["cpu_port_ms"] = repr(e)
+        elif peaks_hbm:
+            out["triplet_cfg1_G%d" % G]["roofline"] = {"bound": "hbm", "achieved": nbytes / ms / 1e6, "peak": peaks_hbm,
+                                                      "unit": "GB/s", "frac": nbytes / ms / 1e6 / peaks_hbm}
     # configs[2]: untrimmed moment retrieval, 4096 queries x 20480 videos x 64 moments, 512-d f32: segment
     # max-pool + top-100 videos (tensor cores) and the full moment evaluation (rank all, per-video NMS, AP, R@N)
     try:
         out.update(aux_moment(torch, vq))
     except Exception as e:  # noqa: BLE001 -- a side measurement must not lose the headline line
         out["moment_cfg2_error"] = repr(e)
+    # f1: sliding-moment pooling (garner_feat) at untrimmed-gallery scale, HBM-bound
+    try:
+        out["window_means_f1"] = aux_windows(torch, peaks_hbm)
+    except Exception as e:  # noqa: BLE001
+        out["window_means_f1"] = {"error": repr(e)}
     return out
+
+
+def aux_windows(torch, peaks_hbm, V=2048, T=600, C=512):
+    import numpy as np
+    from vqwild_b200 import ops
+    from vqwild_b200.retrieval import moment_grid
+    s, e, lo, hi = moment_grid(T / 3.0 + 0.4, T)
+    nw = len(s)
+    t0, ws = np.arange(V + 1, dtype=np.int64) * T, np.arange(V + 1, dtype=np.int64) * nw
+    feat = torch.rand(C, V * T, device="cuda")
+    lo_d = torch.from_numpy(np.tile(lo, V).astype(np.int32)).cuda()
+    hi_d = torch.from_numpy(np.tile(hi, V).astype(np.int32)).cuda()
+    for _ in range(2):
+        ops.window_means(feat, t0, ws, lo_d, hi_d)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(5):
+        o = ops.window_means(feat, t0, ws, lo_d, hi_d)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 5
+    nbytes = 4.0 * C * V * T + 4.0 * C * V * nw
+    # the reference's host loop (np.mean per window, dataloader_baseline.py:1140-1143) on a few videos
+    fh = feat[:, :4 * T].cpu().numpy()
+    tc = time.perf_counter()
+    for v in range(4):
+        for a, z in zip(lo, hi):
+            np.mean(fh[:, v * T + a:v * T + z], axis=1)
+    cpu_ms = (time.perf_counter() - tc) * 1e3 / 4 * V
+    r = {"workload": "f1: %d videos x %d frames x %d-d, %d sliding moments per video (garner_feat grid)" % (V, T, C, nw),
+         "ms": ms, "algorithmic_bytes": nbytes, "GB_per_s": nbytes / ms / 1e6,
+         "numpy_loop_ms_extrapolated": cpu_ms, "numpy_sample": "4 of the %d videos, 1 thread" % V}
+    if peaks_hbm:
+        r["roofline"] = {"bound": "hbm", "achieved": nbytes / ms / 1e6, "peak": peaks_hbm, "unit": "GB/s",
+                         "frac": nbytes / ms / 1e6 / peaks_hbm}
+    del feat, o
+    return r
 
 
 def cfg0_problem(np, n=20480, nq=4096, d=512):
@@ -322,6 +395,7 @@ def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
     ix = vq.IndexFlatL2(d)
     ix.add(g)
     gsrc = [g]
+    gsrc_host = g.cpu().numpy()
     del g
     ix.set_meta(hit, video)
     ix.set_segments(np.arange(0, n + 1, S, dtype=np.int64))
@@ -355,7 +429,20 @@ def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
                                "gemm_topk_ms": tm["gemm_topk_ms"], "tflops_algorithmic": 2.0 * nq * n * d / tm["gemm_topk_ms"] / 1e9}
     del ixb, gsrc
     t, r = wall(lambda: ix.eval_moment(q, ql, ign), 2)
-    out["moment_eval_cfg2"] = {"workload": "configs[2]: full moment evaluation (rank all %d moments per query, per-video NMS, "
+    cpu = None
+    try:  # CPU port on a bounded sample: one query per host thread against the full moment gallery
+        from oracle import oracle as orc
+        ns = orc.num_threads()
+        gh = gsrc_host
+        t0 = time.perf_counter()
+        apc, _ = orc.eval_moment(q[:ns].cpu().numpy(), gh, video, start, end, iou, hit, ql[:ns].cpu().numpy(), ign[:ns].cpu().numpy())
+        dt = time.perf_counter() - t0
+        cpu = {"sample": "%d of the %d queries x all %d moments, %d threads" % (ns, nq, n, ns), "wall_ms_sample": dt * 1e3,
+               "wall_ms_extrapolated": dt * 1e3 * nq / ns,
+               "max_abs_ap_diff_vs_gpu": float(np.abs(apc - r[0][:ns].cpu().numpy()).max())}
+    except Exception as e:  # noqa: BLE001
+        cpu = {"error": repr(e)}
+    out["moment_eval_cfg2"] = {"cpu_port": cpu,"workload": "configs[2]: full moment evaluation (rank all %d moments per query, per-video NMS, "
                                "AP@tIoU0.5, grouped R@30/50/100), %d queries" % (n, nq), "wall_ms": t * 1e3,
                                "ms_per_query": t * 1e3 / nq, "pairs_per_s": nq * n / t, "mAP": float(r[0].mean().item())}
     return out
