@@ -262,18 +262,36 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                 if (SEGMAX) {
                     // cur_maxh tracks the best element ABOVE tau of the current video; elements
                     // <= tau can never make a video a candidate and are skipped wholesale.
-                    if (m32 > tauh) {
+                    // Video boundaries inside these 32 columns are common to all rows: one coalesced load of the
+                    // columns' video ids and a ballot give them as a bit mask (bit i: column i opens a new video).
+                    const int colL = ch * 32 + lane;
+                    const int sgL = colL < ncols ? __ldg(p.col_seg + j0 + colL) : 0x7fffffff;
+                    int sgP = __shfl_up_sync(0xffffffffu, sgL, 1);
+                    if (lane == 0) sgP = cur_seg;
+                    const uint32_t bnd = __ballot_sync(0xffffffffu, colL < ncols && sgL != sgP);
+                    const int last = min(31, ncols - 1 - ch * 32);
+                    const int seg_first = __shfl_sync(0xffffffffu, sgL, 0), seg_last = __shfl_sync(0xffffffffu, sgL, last);
+                    auto flush_to = [&](int sg, int col) {
+                        if (cur_maxh > tauh && !grp_masked) append(2.0f * cur_maxh, cur_arg);
+                        cur_seg = sg;
+                        cur_maxh = -INFINITY;
+                        grp_masked = p.n_ign > 0 ? is_ignored(row, __ldg(p.col_video + j0 + col)) : false;
+                    };
+                    if ((bnd & ~1u) == 0u) {  // warp-uniform: the 32 columns belong to one video
+                        if (bnd & 1u) flush_to(seg_first, ch * 32);
+                        if (m32 > tauh && m32 > cur_maxh) {  // the step's maximum, first column that attains it
+                            int arg = 31;
+#pragma unroll
+                            for (int i = 30; i >= 0; --i) arg = v[i] == m32 ? i : arg;
+                            cur_maxh = m32;
+                            cur_arg = jbase + (uint32_t)(ch * 32 + arg);
+                        }
+                    } else if (m32 > tauh) {
 #pragma unroll
                         for (int i = 0; i < 32; ++i) {
                             const int col = ch * 32 + i;
                             if (col < ncols) {  // warp-uniform
-                                const int sg = __ldg(p.col_seg + j0 + col);
-                                if (sg != cur_seg) {  // warp-uniform
-                                    if (cur_maxh > tauh && !grp_masked) append(2.0f * cur_maxh, cur_arg);
-                                    cur_seg = sg;
-                                    cur_maxh = -INFINITY;
-                                    grp_masked = p.n_ign > 0 ? is_ignored(row, __ldg(p.col_video + j0 + col)) : false;
-                                }
+                                if ((bnd >> i) & 1u) flush_to(__ldg(p.col_seg + j0 + col), col);
                                 if (v[i] > tauh && v[i] > cur_maxh) {
                                     cur_maxh = v[i];
                                     cur_arg = jbase + col;
@@ -281,14 +299,7 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                             }
                         }
                     } else {
-                        const int col = min(ch * 32 + 31, ncols - 1);
-                        const int sg = __ldg(p.col_seg + j0 + col);
-                        if (sg != cur_seg) {  // a video boundary inside (or at the head of) these columns
-                            if (cur_maxh > tauh && !grp_masked) append(2.0f * cur_maxh, cur_arg);
-                            cur_seg = sg;
-                            cur_maxh = -INFINITY;
-                            grp_masked = p.n_ign > 0 ? is_ignored(row, __ldg(p.col_video + j0 + col)) : false;
-                        }
+                        flush_to(seg_last, ch * 32 + last);  // boundaries, but nothing above tau in this row
                     }
                     const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
                     if (need) compact_rows(need, keep_max);
