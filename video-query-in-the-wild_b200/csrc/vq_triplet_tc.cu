@@ -383,25 +383,49 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             __syncwarp();
 
             // ---------------- pass 2: canonical chains of the candidate pairs ----------------
-            float a_d1[8], a_p1[8], a_d2[8], a_p2[8], x_d[TEXTRA / 4], x_p[TEXTRA / 4];
+            // The 8 primaries a sub-group works on (lanes 4*i + m) give 32 partial sums per lane and k-block (4 chains x 8
+            // primaries), each to be summed over the 8 lanes in the oracle's tree order (c^4, c^2, c^1).  A transposing
+            // butterfly does that with 28 shuffles instead of 96: at every step a lane keeps the half of its values whose
+            // index bit matches its own lane bit and hands the other half to its partner.  Lane c ends up with the four
+            // sums of primary i = c, which it alone accumulates.  The swizzled stage offsets are k-block invariant.
+            float acc4[4] = {0.f, 0.f, 0.f, 0.f}, x_d[TEXTRA / 4], x_p[TEXTRA / 4];
+            uint32_t po[8], po2[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a_d1[i] = a_p1[i] = a_d2[i] = a_p2[i] = 0.f;
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t e = __shfl_sync(0xffffffffu, prim, 4 * i + m);
+                const uint32_t ra = e & 255u, r1 = (e >> 8) & 255u, r2 = (e >> 16) & 255u;
+                auto off = [&](uint32_t r) { return (r << 7) | (((uint32_t)c ^ (r & 7u)) << 4); };
+                po[i] = off(ra) | (off(r1) << 16);
+                po2[i] = off(r2);
+            }
 #pragma unroll
             for (int i = 0; i < TEXTRA / 4; ++i) x_d[i] = x_p[i] = 0.f;
+            const bool b4 = (c & 4) != 0, b2 = (c & 2) != 0, b1 = (c & 1) != 0;
             for (int kb = 0; kb < KB; ++kb) {
                 mbar_wait(&full_bar[stage], phase);
                 const uint8_t *sp = smem + stage * TSTAGE;
                 if (wvalid) {
+                    float v[32];
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {  // primary triple of lane 4*i + m
-                        const uint32_t e = __shfl_sync(0xffffffffu, prim, 4 * i + m);
-                        const int ra = e & 255u, r1 = (e >> 8) & 255u, r2 = (e >> 16) & 255u;
-                        const float4 xa = tc_ld_chunk(sp, ra, c), x1 = tc_ld_chunk(sp, r1, c), x2 = tc_ld_chunk(sp, r2, c);
-                        a_d1[i] = __fadd_rn(a_d1[i], tc_tree8_shfl(tc_sq4(xa, x1)));
-                        a_p1[i] = __fadd_rn(a_p1[i], tc_tree8_shfl(tc_dot4(xa, x1)));
-                        a_d2[i] = __fadd_rn(a_d2[i], tc_tree8_shfl(tc_sq4(xa, x2)));
-                        a_p2[i] = __fadd_rn(a_p2[i], tc_tree8_shfl(tc_dot4(xa, x2)));
+                        const float4 xa = *reinterpret_cast<const float4 *>(sp + (po[i] & 0xffffu));
+                        const float4 x1 = *reinterpret_cast<const float4 *>(sp + (po[i] >> 16));
+                        const float4 x2 = *reinterpret_cast<const float4 *>(sp + po2[i]);
+                        v[4 * i] = tc_sq4(xa, x1);
+                        v[4 * i + 1] = tc_dot4(xa, x1);
+                        v[4 * i + 2] = tc_sq4(xa, x2);
+                        v[4 * i + 3] = tc_dot4(xa, x2);
                     }
+                    float w[16], u[8];
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        w[j] = __fadd_rn(b4 ? v[16 + j] : v[j], __shfl_xor_sync(0xffffffffu, b4 ? v[j] : v[16 + j], 4));
+#pragma unroll
+                    for (int j = 0; j < 8; ++j)
+                        u[j] = __fadd_rn(b2 ? w[8 + j] : w[j], __shfl_xor_sync(0xffffffffu, b2 ? w[j] : w[8 + j], 2));
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        acc4[j] = __fadd_rn(acc4[j], __fadd_rn(b1 ? u[4 + j] : u[j], __shfl_xor_sync(0xffffffffu, b1 ? u[j] : u[4 + j], 1)));
 #pragma unroll
                     for (int i = 0; i < TEXTRA / 4; ++i) {
                         if (4 * i < nex_total) {  // warp-uniform
@@ -416,9 +440,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 }
                 next_stage();
             }
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
-                if (c == 0) s_res[rw * 32 + 4 * i + m] = make_float4(a_d1[i], a_p1[i], a_d2[i], a_p2[i]);
+            s_res[rw * 32 + 4 * c + m] = make_float4(acc4[0], acc4[1], acc4[2], acc4[3]);  // primary i = c is lane 4*c + m
 #pragma unroll
             for (int i = 0; i < TEXTRA / 4; ++i) {
                 const int idx = 4 * i + m;
