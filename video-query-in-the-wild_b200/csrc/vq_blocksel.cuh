@@ -147,6 +147,98 @@ __device__ __forceinline__ float canon_d2_row<__nv_bfloat16>(const float *qs, co
     return acc;
 }
 
+// ---------------------------------------------------------------------------------------
+// Warp-cooperative canonical re-scoring of 32 gathered rows (one per lane).
+// canon_d2_row has every lane walk its own row: a warp-wide 16-byte load then touches 32 different 128-byte lines
+// and the L1 tag stage, not HBM, sets the pace (ncu: lsu data-pipe wavefronts 56-81 % with 29 sectors per request).
+// Here the warp copies the 32 rows 128 bytes at a time with cp.async -- eight lanes per row, so a request covers four
+// full lines -- into a swizzled 4 KB shared-memory tile (two stages), and every lane then reads its own row's 128
+// bytes back as eight conflict-free LDS.128.  The chain itself is unchanged (sequential in i, oracle bits).
+// Needs d * sizeof(T) % 128 == 0 and 16-byte aligned rows; `tile` = this warp's 2 x 4096 bytes, 128-byte aligned.
+// Lanes without a row pass any valid row pointer and ignore the result.
+// ---------------------------------------------------------------------------------------
+static constexpr int kRescoreTileBytes = 2 * 4096;  // per warp
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+template <typename T>
+__device__ __forceinline__ float canon_chunk128(float acc, const float *qs, const uint4 (&v)[8]);
+template <>
+__device__ __forceinline__ float canon_chunk128<float>(float acc, const float *qs, const uint4 (&v)[8]) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {  // 32 floats
+        const float4 qv = *reinterpret_cast<const float4 *>(qs + 4 * u);
+        acc = canon_step(acc, qv.x, __uint_as_float(v[u].x));
+        acc = canon_step(acc, qv.y, __uint_as_float(v[u].y));
+        acc = canon_step(acc, qv.z, __uint_as_float(v[u].z));
+        acc = canon_step(acc, qv.w, __uint_as_float(v[u].w));
+    }
+    return acc;
+}
+template <>
+__device__ __forceinline__ float canon_chunk128<__nv_bfloat16>(float acc, const float *qs, const uint4 (&v)[8]) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {  // 64 bf16
+        const float4 qa = *reinterpret_cast<const float4 *>(qs + 8 * u);
+        const float4 qb = *reinterpret_cast<const float4 *>(qs + 8 * u + 4);
+        acc = canon_step(acc, qa.x, __uint_as_float(v[u].x << 16));
+        acc = canon_step(acc, qa.y, __uint_as_float(v[u].x & 0xffff0000u));
+        acc = canon_step(acc, qa.z, __uint_as_float(v[u].y << 16));
+        acc = canon_step(acc, qa.w, __uint_as_float(v[u].y & 0xffff0000u));
+        acc = canon_step(acc, qb.x, __uint_as_float(v[u].z << 16));
+        acc = canon_step(acc, qb.y, __uint_as_float(v[u].z & 0xffff0000u));
+        acc = canon_step(acc, qb.z, __uint_as_float(v[u].w << 16));
+        acc = canon_step(acc, qb.w, __uint_as_float(v[u].w & 0xffff0000u));
+    }
+    return acc;
+}
+
+template <typename T>
+__device__ __forceinline__ float warp_canon_d2_rows(const float *qs, const T *myrow, int d, uint8_t *tile, int lane) {
+    constexpr int EPC = 128 / (int)sizeof(T);  // elements per 128-byte chunk
+    const int nch = d / EPC;
+    const uint32_t tb = smem_u32(tile);
+    const int sub = lane >> 3, pc = lane & 7;
+    // step j of a chunk copies piece pc of tile rows 4*j + sub
+    const uint8_t *src[8];
+    uint32_t dst[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int rt = 4 * j + sub;
+        src[j] = (const uint8_t *)__shfl_sync(0xffffffffu, (unsigned long long)myrow, rt) + pc * 16;
+        dst[j] = tb + rt * 128 + ((pc ^ (rt & 7)) << 4);
+    }
+    auto issue = [&](int ch) {
+        const uint32_t so = (ch & 1) * 4096;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) cp_async16(dst[j] + so, src[j] + (size_t)ch * 128);
+        cp_async_commit();
+    };
+    __syncwarp();  // the tile's previous users are done
+    issue(0);
+    if (nch > 1) issue(1);
+    float acc = 0.f;
+    const uint8_t *mine = tile + lane * 128;
+    for (int ch = 0; ch < nch; ++ch) {
+        if (ch + 1 < nch) cp_async_wait<1>(); else cp_async_wait<0>();
+        __syncwarp();
+        uint4 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) v[u] = *reinterpret_cast<const uint4 *>(mine + (ch & 1) * 4096 + ((u ^ (lane & 7)) << 4));
+        __syncwarp();  // everyone has read the stage: it may be refilled
+        if (ch + 2 < nch) issue(ch + 2);
+        acc = canon_chunk128<T>(acc, qs + ch * EPC, v);
+    }
+    return acc;
+}
+
 template <typename T>
 __device__ __forceinline__ float to_f32(T v);
 template <>

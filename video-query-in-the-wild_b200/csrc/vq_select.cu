@@ -16,12 +16,20 @@ namespace vq {
 
 static constexpr int kSelThreads = 128;
 
+// gather buffer: every candidate key of the query's segments; once the cut has kept k' of them the rest of the
+// buffer holds the four warps' re-score tiles (128-byte aligned), so it is at least that large
+__host__ __device__ __forceinline__ size_t select_keys_bytes(int segs_per_group, int kprime) {
+    const size_t gather = (size_t)segs_per_group * kprime * 8;
+    const size_t rescore = (size_t)kprime * 8 + 128 + (size_t)(kSelThreads / 32) * kRescoreTileBytes;
+    return ((gather > rescore ? gather : rescore) + 15) & ~(size_t)15;
+}
+
 template <typename T, bool SEGMAX>
 __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams p) {
     extern __shared__ __align__(16) uint8_t sm[];
     const int ksort = next_pow2(p.kprime);
-    uint64_t *keys = (uint64_t *)sm;                     // [segs_per_group * k'] coarse keys
-    uint64_t *ex = keys + p.segs_per_group * p.kprime;  // [ksort] exact keys
+    uint64_t *keys = (uint64_t *)sm;                     // [segs_per_group * k'] coarse keys; after the cut: k' keys + re-score tiles
+    uint64_t *ex = (uint64_t *)(sm + select_keys_bytes(p.segs_per_group, p.kprime));  // [ksort] exact keys
     uint32_t *aux = (uint32_t *)(ex + ksort);            // [ksort] segmax: video per exact key slot
     float *qs = (float *)(aux + ksort);                  // [d]
     int *scratch = (int *)(qs + p.d);                    // [40]
@@ -118,11 +126,41 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
         aux[i] = 0xffffffffu;
     }
     __syncthreads();
-    if (!SEGMAX) {
+    // rows are re-scored 32 at a time through this warp's shared-memory tile (coalesced copies, vq_blocksel.cuh)
+    // when they are whole 128-byte chunks; the space is the part of the gather buffer the cut has freed
+    const bool tiled = ((size_t)p.d * sizeof(T)) % 128 == 0 && (((uintptr_t)p.g) & 15) == 0;
+    uint8_t *tile = (uint8_t *)((((uintptr_t)(keys + p.kprime)) + 127) & ~(uintptr_t)127) + warp * kRescoreTileBytes;
+    if (!SEGMAX && tiled) {
+        for (int i0 = warp * 32; i0 < m; i0 += kSelThreads) {
+            const int i = i0 + lane;
+            const uint32_t row = key_desc_idx(keys[i < m ? i : i0]);
+            const float d2 = warp_canon_d2_rows<T>(qs, (const T *)p.g + (int64_t)row * p.d, p.d, tile, lane);
+            if (i < m) ex[i] = make_key_asc(d2, row);
+        }
+    } else if (!SEGMAX) {
         for (int i = tid; i < m; i += kSelThreads) {
             const uint32_t row = key_desc_idx(keys[i]);
             const float d2 = canon_d2_row<T>(qs, (const T *)p.g + (int64_t)row * p.d, p.d);
             ex[i] = make_key_asc(d2, row);
+        }
+    } else if (tiled) {
+        for (int i = warp; i < m; i += kSelThreads / 32) {
+            const uint32_t arow = key_desc_idx(keys[i]);
+            const int v = p.seg_of_row[arow];
+            const int64_t s0 = p.seg_start[v], s1 = p.seg_start[v + 1];
+            uint64_t best = ~0ull;
+            for (int64_t r0 = s0; r0 < s1; r0 += 32) {
+                const int64_t rr = r0 + lane;
+                const float d2 = warp_canon_d2_rows<T>(qs, (const T *)p.g + (rr < s1 ? rr : r0) * p.d, p.d, tile, lane);
+                const uint64_t kk = rr < s1 ? make_key_asc(d2, (uint32_t)rr) : ~0ull;
+                best = kk < best ? kk : best;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+                const uint64_t other = __shfl_xor_sync(0xffffffffu, best, o);
+                best = other < best ? other : best;
+            }
+            if (lane == 0) ex[i] = best;
         }
     } else {
         for (int i = warp; i < m; i += kSelThreads / 32) {
@@ -187,9 +225,8 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
 }
 
 size_t select_smem_bytes(const SelectParams &p) {
-    const size_t E = (size_t)p.segs_per_group * p.kprime;
     const size_t ks = (size_t)next_pow2(p.kprime);
-    return E * 8 + ks * 8 + ks * 4 + (size_t)p.d * 4 + 40 * 4 + ((size_t)2 * p.segs_per_group + 2) * 4 +
+    return select_keys_bytes(p.segs_per_group, p.kprime) + ks * 8 + ks * 4 + (size_t)p.d * 4 + 40 * 4 + ((size_t)2 * p.segs_per_group + 2) * 4 +
            (size_t)p.segs_per_group * 8 + 16;
 }
 
