@@ -36,7 +36,7 @@ ix.set_segments(np.arange(0, n + 1, S, dtype=np.int64))
 ix.set_moments(start, end, iou, hit)
 ql = torch.from_numpy(rng.integers(0, 180, nq).astype(np.int32)).to(dev)
 ign = torch.from_numpy(rng.integers(0, V, (nq, 5)).astype(np.int32)).to(dev)
-for it in range(3):
+for it in range(6):
     torch.cuda.synchronize()
     t0 = time.perf_counter()
     ap, rec, nk, _ = ix.eval_moment(q, ql, ign)

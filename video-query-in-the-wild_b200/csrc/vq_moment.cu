@@ -21,8 +21,33 @@ __device__ __forceinline__ void grp_sync() {
     if (NT == 32) __syncwarp(); else __syncthreads();
 }
 
+// nms_cpu's test for one pair (utils_models.py:165-172): ovr = inter / (la + lb - inter); the later moment is
+// suppressed unless ovr < thresh.  No division on the common paths, same answer bit for bit:
+//   r = fma(thresh, union, -inter) has the exact sign of thresh*union - inter (one rounding, zero only if equal);
+//   r <= 0: the exact quotient is >= thresh, and rounding is monotonic with thresh representable -> suppressed
+//           (covers the ties of regular window grids, IoU exactly = thresh);
+//   r > 2^-50 * thresh * union: the exact quotient is more than an ulp below thresh -> rounds below it -> kept;
+//   the sliver in between (and union <= 0 / NaN inputs) forms the quotient as the reference does.
+__device__ __noinline__ bool nms_quotient(double inter, double uni, double thresh) {  // rare: keep it out of line
+    const double ovr = inter / uni;
+    return !(ovr < thresh);
+}
+__device__ __forceinline__ bool nms_suppressed(double xa1, double xa2, double la, double xb1, double xb2, double lb,
+                                               double thresh) {
+    const double xx1 = xa1 > xb1 ? xa1 : xb1, xx2 = xa2 < xb2 ? xa2 : xb2;
+    double inter = xx2 - xx1 + 1.0;
+    inter = inter < 0.0 ? 0.0 : inter;
+    const double uni = la + lb - inter;
+    if (uni > 0.0 && thresh > 0.0) {
+        const double r = fma(thresh, uni, -inter);
+        if (r <= 0.0) return true;
+        if (r > 0x1p-50 * (thresh * uni)) return false;
+    }
+    return nms_quotient(inter, uni, thresh);
+}
+
 template <int NT, int CAP>
-__global__ void __launch_bounds__(256) moment_nms_kernel(const MomentNmsParams p, const int32_t *__restrict__ seg_list,
+__global__ void __launch_bounds__(256, NT == 32 ? 4 : 1) moment_nms_kernel(const MomentNmsParams p, const int32_t *__restrict__ seg_list,
                                                          int nlist, int per_group) {
     extern __shared__ __align__(16) uint8_t sm_raw[];
     constexpr int GPB = 256 / NT;
@@ -49,13 +74,44 @@ __global__ void __launch_bounds__(256) moment_nms_kernel(const MomentNmsParams p
         int n2 = 1;
         while (n2 < S) n2 <<= 1;
         grp_sync<NT>();  // the previous segment's arrays are free
-        for (int i = t; i < n2; i += NT) keys[i] = i < S ? make_key_asc(row[s0 + i], (uint32_t)i) : ~0ull;
-        for (int k = 2; k <= n2; k <<= 1)
-            for (int j = k >> 1; j > 0; j >>= 1) {
-                grp_sync<NT>();
-                for (int i = t; i < n2; i += NT) {
-                    const int ixj = i ^ j;
-                    if (ixj > i) {
+        if (NT == 32 && S <= 64) {
+            // two keys per lane (ranks t and t + 32), bitonic network on registers: partners below 32 apart are a
+            // shuffle away, the 32-apart partner is the lane's other register
+            uint64_t k0 = t < S ? make_key_asc(row[s0 + t], (uint32_t)t) : ~0ull;
+            uint64_t k1 = t + 32 < S ? make_key_asc(row[s0 + t + 32], (uint32_t)(t + 32)) : ~0ull;
+            auto cx = [&](uint64_t &x, int j, bool asc) {
+                const uint64_t o = __shfl_xor_sync(0xffffffffu, x, j);
+                const bool takemin = ((t & j) == 0) == asc;
+                x = ((o < x) == takemin) ? o : x;
+            };
+#pragma unroll
+            for (int k = 2; k <= 32; k <<= 1) {
+                const bool a0 = k < 32 ? (t & k) == 0 : true, a1 = k < 32 ? a0 : false;
+#pragma unroll
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    cx(k0, j, a0);
+                    cx(k1, j, a1);
+                }
+            }
+            if (k1 < k0) {
+                const uint64_t tmp = k0;
+                k0 = k1;
+                k1 = tmp;
+            }
+#pragma unroll
+            for (int j = 16; j > 0; j >>= 1) {
+                cx(k0, j, true);
+                cx(k1, j, true);
+            }
+            keys[t] = k0;
+            keys[t + 32] = k1;
+        } else {
+            for (int i = t; i < n2; i += NT) keys[i] = i < S ? make_key_asc(row[s0 + i], (uint32_t)i) : ~0ull;
+            for (int k = 2; k <= n2; k <<= 1)
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    grp_sync<NT>();
+                    for (int h = t; h < (n2 >> 1); h += NT) {  // pair h: i = h with a zero inserted at bit j
+                        const int i = ((h & ~(j - 1)) << 1) | (h & (j - 1)), ixj = i | j;
                         const uint64_t a = keys[i], b = keys[ixj];
                         if ((a > b) == ((i & k) == 0)) {
                             keys[i] = b;
@@ -63,7 +119,7 @@ __global__ void __launch_bounds__(256) moment_nms_kernel(const MomentNmsParams p
                         }
                     }
                 }
-            }
+        }
         grp_sync<NT>();
         for (int i = t; i < S; i += NT) {
             const int64_t r = s0 + (uint32_t)keys[i];
@@ -73,24 +129,57 @@ __global__ void __launch_bounds__(256) moment_nms_kernel(const MomentNmsParams p
         }
         grp_sync<NT>();
         // greedy NMS in ranked order (nms_cpu :159-173; equal scores: earlier rank first)
-        for (int a = 0; a < S; ++a) {
-            if (dead[a]) continue;
-            const double xa1 = (double)x1[a], xa2 = (double)x2[a], la = xa2 - xa1 + 1.0;
-            bool wrote = false;
-            for (int b = a + 1 + t; b < S; b += NT) {
-                if (dead[b]) continue;
-                const double xb1 = (double)x1[b], xb2 = (double)x2[b], lb = xb2 - xb1 + 1.0;
-                const double xx1 = xa1 > xb1 ? xa1 : xb1, xx2 = xa2 < xb2 ? xa2 : xb2;
-                double inter = xx2 - xx1 + 1.0;
-                inter = inter < 0.0 ? 0.0 : inter;
-                const double ovr = inter / (la + lb - inter);
-                if (!(ovr < p.thresh)) {
-                    dead[b] = 1;
-                    wrote = true;
+        if (NT == 32) {
+            // warp form: lane t owns ranks t, t+32, ... and keeps their dead bits in a register; the survivors of
+            // the current 32-rank chunk are a ballot, so a round costs no shared-memory flag traffic and no barrier
+            uint32_t mydead = 0;
+            const int nchunk = (S + 31) >> 5;
+            constexpr int RC = 2;  // the lane's first RC ranks stay in registers as doubles (videos of <= 64 moments: all)
+            double bx1[RC], bx2[RC], blb[RC];
+#pragma unroll
+            for (int jj = 0; jj < RC; ++jj) {
+                const int b = 32 * jj + t;
+                bx1[jj] = b < S ? (double)x1[b] : 0.0;
+                bx2[jj] = b < S ? (double)x2[b] : 0.0;
+                blb[jj] = bx2[jj] - bx1[jj] + 1.0;
+            }
+            for (int j = 0; j < nchunk; ++j) {
+                const uint32_t valid = (S - 32 * j) >= 32 ? 0xffffffffu : ((1u << (S - 32 * j)) - 1u);
+                uint32_t todo = ~__ballot_sync(0xffffffffu, (mydead >> j) & 1u) & valid;
+                while (todo) {
+                    const int al = __ffs(todo) - 1, a = 32 * j + al;
+                    const double xa1 = (double)x1[a], xa2 = (double)x2[a], la = xa2 - xa1 + 1.0;
+#pragma unroll
+                    for (int jj = 0; jj < RC; ++jj) {
+                        const int b = 32 * jj + t;
+                        if (jj >= j && b > a && b < S && !((mydead >> jj) & 1u) &&
+                            nms_suppressed(xa1, xa2, la, bx1[jj], bx2[jj], blb[jj], p.thresh))
+                            mydead |= 1u << jj;
+                    }
+                    for (int jj = j > RC ? j : RC; jj < nchunk; ++jj) {
+                        const int b = 32 * jj + t;
+                        if (b > a && b < S && !((mydead >> jj) & 1u)) {
+                            const double xb1 = (double)x1[b], xb2 = (double)x2[b];
+                            if (nms_suppressed(xa1, xa2, la, xb1, xb2, xb2 - xb1 + 1.0, p.thresh)) mydead |= 1u << jj;
+                        }
+                    }
+                    todo = ~__ballot_sync(0xffffffffu, (mydead >> j) & 1u) & valid & ~((2u << al) - 1u);
                 }
             }
-            (void)wrote;
+            for (int jj = 0; jj < nchunk; ++jj)
+                if (32 * jj + t < S) dead[32 * jj + t] = (mydead >> jj) & 1u;
             grp_sync<NT>();
+        } else {
+            for (int a = 0; a < S; ++a) {
+                if (dead[a]) continue;
+                const double xa1 = (double)x1[a], xa2 = (double)x2[a], la = xa2 - xa1 + 1.0;
+                for (int b = a + 1 + t; b < S; b += NT) {
+                    if (dead[b]) continue;
+                    const double xb1 = (double)x1[b], xb2 = (double)x2[b];
+                    if (nms_suppressed(xa1, xa2, la, xb1, xb2, xb2 - xb1 + 1.0, p.thresh)) dead[b] = 1;
+                }
+                grp_sync<NT>();
+            }
         }
         for (int i = t; i < S; i += NT) kept[s0 + (uint32_t)keys[i]] = dead[i] ? 0 : 1;
         if (t == 0) p.vbest[q * p.nseg + v] = (keys[0] & 0xffffffff00000000ull) | (uint64_t)(s0 + (uint32_t)keys[0]);
