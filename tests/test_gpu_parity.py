@@ -225,6 +225,38 @@ def test_eval_moment_golden(vq, golden):
         assert nk[i] == len(kept) and np.array_equal(np.flatnonzero(km[i]), np.sort(kept))
 
 
+@pytest.mark.parametrize("thresh", [0.1, 0.2, 0.3, 1.0 / 3.0, 0.6, 0.7])
+def test_eval_moment_nms_threshold_ties(vq, thresh):
+    """Small integer windows: IoU = inter/union hits the threshold's decimal value exactly in real arithmetic all the
+    time (1/10, 3/10, 7/10 ... are not doubles), so the kernel's division-free test and its quotient sliver must land
+    on the side nms_cpu's float64 `ovr < thresh` does (utils_models.py:165-172)."""
+    rng = np.random.default_rng(int(thresh * 1000))
+    d, nq = 32, 12
+    lens = np.concatenate([np.full(20, 64), rng.integers(1, 64, 20), [65, 130, 256, 300]])
+    seg_start = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    n, nv = int(seg_start[-1]), len(lens)
+    video = np.repeat(np.arange(nv), lens).astype(np.int32)
+    start = rng.integers(0, 20, n).astype(np.float32)
+    end = start + rng.integers(0, 10, n).astype(np.float32)      # inclusive lengths 1..10
+    hit = rng.integers(-1, 6, n).astype(np.int32)
+    iou = np.where(hit >= 0, rng.uniform(0, 1, n), 0).astype(np.float32)
+    g, q = _emb(rng, n, d), _emb(rng, nq, d)
+    ql = rng.integers(0, 6, nq).astype(np.int32)
+    ign = rng.integers(0, nv, (nq, 2)).astype(np.int32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    ix.set_meta(hit, video)
+    ix.set_segments(seg_start)
+    ix.set_moments(start, end, iou, hit)
+    ap, rec, nk, km = ix.eval_moment(q, ql, ign, nms_thresh=thresh, want_kept=True)
+    apo, reco = orc.eval_moment(q, g, video, start, end, iou, hit, ql, ign, nms_thresh=thresh)
+    np.testing.assert_allclose(ap, apo, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-12)
+    for i in range(nq):
+        _, _, kept = orc.eval_moment_kept(q[i], g, video, start, end, iou, hit, ql[i], ign[i], nms_thresh=thresh)
+        assert nk[i] == len(kept) and np.array_equal(np.flatnonzero(km[i]), np.sort(kept))
+
+
 @pytest.mark.parametrize("case", ["uniform64", "ragged", "large_videos", "ties"])
 def test_eval_moment_random(vq, case):
     rng = np.random.default_rng({"uniform64": 1, "ragged": 2, "large_videos": 3, "ties": 4}[case])

@@ -597,25 +597,31 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 if (p.grad) {
                     const uint8_t *sp = smem + stage * TSTAGE;
                     const int col = kb * TKB + c * 4;
-                    auto ldx = [&](uint32_t off) { return *reinterpret_cast<const float4 *>(sp + ((off & 0x7fffu) ^ cx)); };
-                    uint2 en0 = s_en2[min(eb, E - 1)], en1 = s_en2[min(eb + 1, E - 1)];
+                    auto ldx = [&](uint32_t off) { return *reinterpret_cast<const float4 *>(sp + ((off & 0x7ff0u) ^ cx)); };
+                    // E <= 768 of the 1024 slots: reading two entries past a piece's end stays inside the array, and
+                    // whatever is there only feeds loads inside the stage (offsets are masked) and a chain nobody stores
+                    float *gb = p.grad + ((int64_t)g * B) * p.d + col;
+                    const uint32_t rlim = col < p.d ? (uint32_t)B : 0u;
+                    uint2 en0 = s_en2[eb], en1 = s_en2[eb + 1];
                     float4 xu0 = ldx(en0.x), xv0 = ldx(en0.x >> 16);
                     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
                     for (int it = 0; it < nit; ++it) {
                         const float4 xu1 = ldx(en1.x), xv1 = ldx(en1.x >> 16);
-                        const uint2 en2 = s_en2[min(eb + it + 2, E - 1)];
-                        if (eb + it < ee) {
-                            acc.x = __fmaf_rn(scale, __fsub_rn(xu0.x, xv0.x), acc.x);
-                            acc.y = __fmaf_rn(scale, __fsub_rn(xu0.y, xv0.y), acc.y);
-                            acc.z = __fmaf_rn(scale, __fsub_rn(xu0.z, xv0.z), acc.z);
-                            acc.w = __fmaf_rn(scale, __fsub_rn(xu0.w, xv0.w), acc.w);
-                            if (en0.y & 256u) {
-                                const int r = en0.y & 255u;
-                                if (r < B && col < p.d)
-                                    *reinterpret_cast<float4 *>(p.grad + ((int64_t)g * B + r) * p.d + col) = acc;
-                                acc = make_float4(0.f, 0.f, 0.f, 0.f);
-                            }
-                        }
+                        const uint2 en2 = s_en2[eb + it + 2];
+                        acc.x = __fmaf_rn(scale, __fsub_rn(xu0.x, xv0.x), acc.x);
+                        acc.y = __fmaf_rn(scale, __fsub_rn(xu0.y, xv0.y), acc.y);
+                        acc.z = __fmaf_rn(scale, __fsub_rn(xu0.z, xv0.z), acc.z);
+                        acc.w = __fmaf_rn(scale, __fsub_rn(xu0.w, xv0.w), acc.w);
+                        // straight-line tail: the four sub-groups of a warp finish their rows at different entries
+                        const uint32_t r = en0.y & 255u;
+                        const bool last = (en0.y & 256u) != 0u;
+                        float4 *dst = reinterpret_cast<float4 *>(gb + (size_t)(r * (uint32_t)p.d));
+                        if (last && eb + it < ee && r < rlim) *dst = acc;
+                        acc.x = last ? 0.f : acc.x;
+                        acc.y = last ? 0.f : acc.y;
+                        acc.z = last ? 0.f : acc.z;
+                        acc.w = last ? 0.f : acc.w;
                         en0 = en1; xu0 = xu1; xv0 = xv1; en1 = en2;
                     }
                 }
