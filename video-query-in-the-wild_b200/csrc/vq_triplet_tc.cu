@@ -271,7 +271,8 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             tk[1] = clock64();
             s_nrm[row] = na;
             s_lab[row] = rvalid ? p.labels[(int64_t)g * B + row] : 0;
-            s_nl[row] = make_float2(na, __int_as_float(s_lab[row]));
+            // rows past B carry a NaN norm: their coarse value is NaN and drops out of every extreme / band test of the mine
+            s_nl[row] = make_float2(rvalid ? na : __int_as_float(0x7fc00000), __int_as_float(s_lab[row]));
             s_ecnt[row] = 0;
             if (threadIdx.x == 64) {
                 s_misc[0] = 0;
@@ -293,29 +294,36 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             tc_fence_after();
             tk[2] = clock64();
             float maxp = -INFINITY, minn = INFINITY;
+            // the anchor's own column becomes NaN too (the chunk that holds it is warp-uniform: row >> 5 == rw)
+            auto blank_diag = [&](uint32_t (&r)[32], int ch) {
+                if (ch == (row >> 5)) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) r[i] = i == (row & 31) ? 0x7fc00000u : r[i];
+                }
+            };
 #pragma unroll 1
             for (int ch = 0; ch < TB / 32; ++ch) {
                 if (ch * 32 >= B) break;
                 uint32_t r[32];
                 tmem_ld32(taddr + ch * 32, r);
                 tmem_wait_ld();
+                blank_diag(r, ch);
 #pragma unroll
                 for (int i = 0; i < 32; i += 2) {
                     const float4 nl = *reinterpret_cast<const float4 *>(&s_nl[ch * 32 + i]);
 #pragma unroll
                     for (int h = 0; h < 2; ++h) {
-                        const int j = ch * 32 + i + h;
                         const float cv = __fmaf_rn(-2.0f, __uint_as_float(r[i + h]), __fadd_rn(na, h ? nl.z : nl.x));
-                        const bool ok = j < B && j != row;
                         const bool same = __float_as_int(h ? nl.w : nl.y) == la;
-                        if (ok && same) maxp = fmaxf(maxp, cv);
-                        if (ok && !same) minn = fminf(minn, cv);
+                        maxp = same ? fmaxf(maxp, cv) : maxp;   // fmaxf / fminf drop a NaN operand
+                        minn = same ? minn : fminf(minn, cv);
                     }
                 }
             }
             const bool avalid = rvalid && maxp > -INFINITY && minn < INFINITY;
-            const float thr_p = maxp < 1e-4f + 2.0f * eps ? -INFINITY : maxp - 2.0f * eps;  // clamp region: every positive ties
-            const float thr_n = fmaxf(minn, 1e-4f) + 2.0f * eps;
+            const float qnan = __int_as_float(0x7fc00000);
+            const float thr_p = !avalid ? qnan : (maxp < 1e-4f + 2.0f * eps ? -INFINITY : maxp - 2.0f * eps);  // clamp region: every positive ties
+            const float thr_n = !avalid ? qnan : fmaxf(minn, 1e-4f) + 2.0f * eps;
             uint64_t cpw = 0, cnw = 0;  // up to 8 candidate rows per role, one byte each, ascending row order
             int ncp = 0, ncn = 0;
             if (__any_sync(0xffffffffu, avalid)) {
@@ -325,24 +333,30 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                     uint32_t r[32];
                     tmem_ld32(taddr + ch * 32, r);
                     tmem_wait_ld();
+                    blank_diag(r, ch);
+                    uint32_t mp = 0, mn = 0;  // band members of this chunk; the (rare) set bits are unpacked below
 #pragma unroll
                     for (int i = 0; i < 32; i += 2) {
                         const float4 nl = *reinterpret_cast<const float4 *>(&s_nl[ch * 32 + i]);
 #pragma unroll
                         for (int h = 0; h < 2; ++h) {
-                            const int j = ch * 32 + i + h;
                             const float cv = __fmaf_rn(-2.0f, __uint_as_float(r[i + h]), __fadd_rn(na, h ? nl.z : nl.x));
-                            const bool ok = avalid && j < B && j != row;
                             const bool same = __float_as_int(h ? nl.w : nl.y) == la;
-                            if (ok && same && cv >= thr_p) {
-                                if (ncp < TCAND) cpw |= (uint64_t)j << (8 * ncp);
-                                ++ncp;
-                            }
-                            if (ok && !same && cv <= thr_n) {
-                                if (ncn < TCAND) cnw |= (uint64_t)j << (8 * ncn);
-                                ++ncn;
-                            }
+                            mp |= (same && cv >= thr_p) ? (1u << (i + h)) : 0u;
+                            mn |= (!same && cv <= thr_n) ? (1u << (i + h)) : 0u;
                         }
+                    }
+                    while (mp) {
+                        const int j = ch * 32 + __ffs(mp) - 1;
+                        mp &= mp - 1;
+                        if (ncp < TCAND) cpw |= (uint64_t)j << (8 * ncp);
+                        ++ncp;
+                    }
+                    while (mn) {
+                        const int j = ch * 32 + __ffs(mn) - 1;
+                        mn &= mn - 1;
+                        if (ncn < TCAND) cnw |= (uint64_t)j << (8 * ncn);
+                        ++ncn;
                     }
                 }
             }
