@@ -239,6 +239,16 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     return VQ_OK;
 }
 
+// Bytes of the [tile_q, n] canonical score matrix the evaluators work on at a time.  One block per query ranks a row,
+// so the tile has to hold several queries per SM to keep the memory system busy: a quarter of the free HBM, between
+// 256 MiB and 8 GiB (kept mask and per-video keys add ~ 1/3 of that on the moment path).
+static int64_t score_tile_bytes() {
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return (int64_t)1 << 31;
+    const int64_t quarter = (int64_t)(free_b / 4);
+    return std::max<int64_t>((int64_t)256 << 20, std::min<int64_t>((int64_t)8 << 30, quarter));
+}
+
 static int check_search_args(const vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k) {
     VQ_CHECK(ix && xq, VQ_ERR_INVALID, "NULL argument");
     VQ_CHECK(ix->n > 0, VQ_ERR_STATE, "search on an empty index");
@@ -324,7 +334,7 @@ int vq_index_eval_trimmed(vq_index *ix, const void *xq, int64_t nq, int dtype, c
     VQ_TRY(oR.bind(recall, (size_t)nq * 3 * 8, st));
     VQ_TRY(oT.bind(top_idx, (size_t)nq * 100 * 8, st));
     // full-list AP / R@N: canonical scores for a tile of queries, then the rank-count reduction
-    const int64_t tile_q = std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(1ll << 31) / std::max<int64_t>(1, ix->n * 4)));
+    const int64_t tile_q = std::max<int64_t>(1, std::min<int64_t>(nq, score_tile_bytes() / std::max<int64_t>(1, ix->n * 4)));
     Tmp d2, ovf;
     VQ_TRY(d2.alloc((size_t)tile_q * ix->n * 4, st));
     VQ_TRY(ovf.alloc(4, st));
@@ -399,7 +409,7 @@ int vq_index_eval_moment(vq_index *ix, const void *xq, int64_t nq, int dtype, co
     VQ_TRY(oR.bind(recall, (size_t)nq * 3 * 8, st));
     VQ_TRY(oN.bind(n_kept, (size_t)nq * 8, st));
     VQ_TRY(oK.bind(kept_mask, (size_t)nq * ix->n, st));
-    int64_t tile_q = std::max<int64_t>(1, std::min<int64_t>(nq, (int64_t)(1ll << 31) / std::max<int64_t>(1, ix->n * 4)));
+    int64_t tile_q = std::max<int64_t>(1, std::min<int64_t>(nq, score_tile_bytes() / std::max<int64_t>(1, ix->n * 4)));
     tile_q = std::min<int64_t>(tile_q, 32768);  // grid.y of the NMS kernel
     Tmp d2, kept, vbest, ovf;
     VQ_TRY(d2.alloc((size_t)tile_q * ix->n * 4, st));

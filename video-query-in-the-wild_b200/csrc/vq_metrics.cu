@@ -104,20 +104,45 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     // ---- pass 1: positives, survivor count, last-ranked survivor ----
     int nvalid_t = 0, nkept_t = 0;
     unsigned long long lk = 0ull;
-    for (int64_t j = tid; j < p.n; j += kApThreads) {
+    // Both passes stream the row four columns per thread with every load of a step issued up front (16-byte loads of
+    // the score, video, label and IoU columns, 4 bytes of the kept mask): the block is alone with its row, so what
+    // bounds it is the number of loads in flight, not bandwidth.  Rows that are not 16-byte aligned walk column by column.
+    const bool vec4 = (p.n & 3) == 0 && ((((uintptr_t)p.d2) | ((uintptr_t)p.g_label) | ((uintptr_t)p.g_video) |
+                                          (MOMENT ? ((uintptr_t)p.g_iou) : 0)) & 15) == 0 &&
+                      (!MOMENT || (((uintptr_t)p.kept) & 3) == 0);
+    auto scan_row = [&](auto &&body) {  // body(j, kept, d2, video, label, iou)
+        if (vec4) {
+            for (int64_t j = (int64_t)tid * 4; j < p.n; j += kApThreads * 4) {
+                const uchar4 k4 = MOMENT ? *reinterpret_cast<const uchar4 *>(keptrow + j) : make_uchar4(1, 1, 1, 1);
+                const float4 r4 = *reinterpret_cast<const float4 *>(row + j);
+                const int4 v4 = n_ign ? __ldg(reinterpret_cast<const int4 *>(p.g_video + j)) : make_int4(0, 0, 0, 0);
+                const int4 l4 = __ldg(reinterpret_cast<const int4 *>(p.g_label + j));
+                const float4 i4 = MOMENT ? __ldg(reinterpret_cast<const float4 *>(p.g_iou + j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                body(j, k4.x, r4.x, v4.x, l4.x, i4.x);
+                body(j + 1, k4.y, r4.y, v4.y, l4.y, i4.y);
+                body(j + 2, k4.z, r4.z, v4.z, l4.z, i4.z);
+                body(j + 3, k4.w, r4.w, v4.w, l4.w, i4.w);
+            }
+        } else {
+            for (int64_t j = tid; j < p.n; j += kApThreads)
+                body(j, MOMENT ? keptrow[j] : (uint8_t)1, row[j], n_ign ? p.g_video[j] : 0, p.g_label[j],
+                     MOMENT ? p.g_iou[j] : 0.f);
+        }
+    };
+    scan_row([&](int64_t j, uint8_t kp, float d2v, int vid, int lab, float iou) {
         if (MOMENT) {
-            if (!keptrow[j]) continue;
+            if (!kp) return;
             ++nkept_t;
         }
-        if (n_ign && is_ignored(p.g_video[j], ign, n_ign)) continue;
+        if (n_ign && is_ignored(vid, ign, n_ign)) return;
         ++nvalid_t;
-        const unsigned long long key = make_key_asc(row[j], (uint32_t)j);
+        const unsigned long long key = make_key_asc(d2v, (uint32_t)j);
         lk = key > lk ? key : lk;
-        if (is_tp(j)) {
+        if (lab == ql && (!MOMENT || iou >= 0.5f)) {
             const int slot = atomicAdd(&misc[0], 1);
             if (slot < pcap2) pos[slot] = key;
         }
-    }
+    });
     atomicAdd(&misc[1], nvalid_t);
     if (MOMENT) atomicAdd(&misc[2], nkept_t);
     if (!MOMENT) atomicMax(last_key, lk);
@@ -184,10 +209,10 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     block_bitonic_sort(pos, n2);  // ascending (d2, row): best first
 
     // ---- pass 2: bucket every survivor against the sorted positive d2 values ----
-    for (int64_t j = tid; j < p.n; j += kApThreads) {
-        if (MOMENT && !keptrow[j]) continue;
-        if (n_ign && is_ignored(p.g_video[j], ign, n_ign)) continue;
-        const uint32_t s = f32_to_ordered(row[j]);
+    scan_row([&](int64_t, uint8_t kp, float d2v, int vid, int, float) {
+        if (MOMENT && !kp) return;
+        if (n_ign && is_ignored(vid, ign, n_ign)) return;
+        const uint32_t s = f32_to_ordered(d2v);
         int lo = 0, hi = npos;  // lower bound: first i with pos_d2[i] >= s
         while (lo < hi) {
             const int mid = (lo + hi) >> 1;
@@ -195,7 +220,7 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
         }
         atomicAdd(&cntA[lo], 1);
         if (lo < npos && (uint32_t)(pos[lo] >> 32) == s) atomicAdd(&cntE[lo], 1);
-    }
+    });
     __syncthreads();
     block_exclusive_scan(cntA, npos + 1, part);  // cntA[i] = #{survivors with lower bound < i}
     // inclusive count LE(g) = cntA[g+1] = #{survivors with d2 <= pos_d2[g]} for a group start g

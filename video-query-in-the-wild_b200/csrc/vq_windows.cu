@@ -33,8 +33,16 @@ __global__ void __launch_bounds__(256) window_means_kernel(const float *__restri
         const int c = c0 + ch;
         double *row = P + ch * pitch;
         if (c < C) {
+            // eight independent loads in flight per lane: a 600-frame channel is three memory latencies, not nineteen
             const float *src = feat + (int64_t)c * Ttot + t0;
-            for (int t = lane; t < T; t += 32) row[t + 1] = (double)__ldg(src + t);
+            for (int t = lane; t < T; t += 256) {
+                float v[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) v[u] = t + 32 * u < T ? __ldg(src + t + 32 * u) : 0.f;
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (t + 32 * u < T) row[t + 32 * u + 1] = (double)v[u];
+            }
         } else {
             for (int t = lane; t < T; t += 32) row[t + 1] = 0.0;
         }
@@ -42,6 +50,7 @@ __global__ void __launch_bounds__(256) window_means_kernel(const float *__restri
         __syncwarp();
         const int per = (T + 31) / 32, b = min(T, lane * per), e = min(T, b + per);
         double tot = 0.0;
+#pragma unroll 4
         for (int t = b; t < e; ++t) tot += row[t + 1];
         double inc = tot;
 #pragma unroll
@@ -50,6 +59,7 @@ __global__ void __launch_bounds__(256) window_means_kernel(const float *__restri
             if (lane >= o) inc += u;
         }
         double run = inc - tot;  // sum of the slices before mine
+#pragma unroll 4
         for (int t = b; t < e; ++t) {
             run += row[t + 1];
             row[t + 1] = run;
