@@ -621,6 +621,44 @@ def test_full_size_cfg1_properties(vq):
     assert np.array_equal(I[sub], Io) and np.array_equal(D[sub].view(np.uint32), Do.view(np.uint32))
 
 
+def test_large_gallery_cfg3_properties(vq):
+    """BASELINE configs[3] shape at a size the box checks in seconds (2 M clips x 512-d bf16, top-100): the properties
+    that do not depend on the gallery size -- the tensor-core pre-filter path returns exactly what the canonical
+    CUDA-core scan does (scores and rows, bit for bit), lists are sorted with distinct rows, and a row-sharded search
+    merged with topk_merge equals the single-index answer (what the N-GPU path relies on)."""
+    import torch
+    gen = torch.Generator(device="cuda").manual_seed(11)
+    n, nq, d, k = 2_000_000, 512, 512, 100
+    g = torch.randn(n, d, device="cuda", generator=gen)
+    g = (g / g.norm(dim=1, keepdim=True) * (0.7 + 0.3 * torch.rand(n, 1, device="cuda", generator=gen))).to(torch.bfloat16)
+    q = torch.randn(nq, d, device="cuda", generator=gen)
+    q[:64] = g[torch.randint(0, n, (64,), device="cuda", generator=gen)].float() + 0.02 * q[:64]   # queries with close hits
+    q = (q / q.norm(dim=1, keepdim=True)).to(torch.bfloat16)
+    q[64:72] = g[5:13]                                                                           # exact hits: d2 = 0
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    D, I = ix.search(q, k)
+    st = ix.last_stats()
+    assert st["fallback_queries"] == 0, st
+    Dc, Ic = D.cpu().numpy(), I.cpu().numpy()
+    assert (np.diff(Dc, axis=1) >= 0).all()
+    assert (np.sort(Ic, axis=1)[:, 1:] != np.sort(Ic, axis=1)[:, :-1]).all()
+    assert (Ic[64:72, 0] == np.arange(5, 13)).all() and (Dc[64:72, 0] == 0).all()
+    ix.set_precision(3)                                   # VQ_PREC_EXACT
+    De, Ie = ix.search(q, k)
+    assert torch.equal(I, Ie) and torch.equal(D.view(torch.int32), De.view(torch.int32))
+    # two row shards -> local top-k -> merge == whole gallery
+    parts_d, parts_i = [], []
+    for lo, hi in ((0, 900_000), (900_000, n)):
+        sh = vq.IndexFlatL2(d)
+        sh.add(g[lo:hi])
+        Ds, Is = sh.search(q, k)
+        parts_d.append(Ds)
+        parts_i.append(torch.where(Is >= 0, Is + lo, Is))
+    Dm, Im = vq.topk_merge(torch.stack(parts_d), torch.stack(parts_i))
+    assert torch.equal(Im, I) and torch.equal(Dm.view(torch.int32), D.view(torch.int32))
+
+
 def test_cfg4_elmo_1024d_k_sweep(vq):
     """BASELINE configs[4]: 1024-d unit-norm embeddings (ELMo word space), 4096 x 20480, top-100 exact + the
     k sweep {5, 30, 50, 100} (R@k as the reference's :475-481; AP@k as defined in metrics.ap_at_k)."""
