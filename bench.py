@@ -498,8 +498,7 @@ def run_b200(a):
         index.search(xq, k, out=(D, I))
         if G == 1:
             return D, I
-        Ig = torch.where(I >= 0, I + r0, I)
-        return ops.merge_gathered(D, Ig)
+        return ops.exchange_merge(D, I, r0)
 
     xq_host = torch.empty(xq.shape, dtype=torch.bfloat16, pin_memory=True)
     xq_host.copy_(xq)
@@ -518,8 +517,7 @@ def run_b200(a):
             return Dh, Ih
         xd = xq_host.to(dev, non_blocking=True)
         index.search(xd, k, out=(D, I))
-        Ig = torch.where(I >= 0, I + r0, I)
-        Dm, Im = ops.merge_gathered(D, Ig)
+        Dm, Im = ops.exchange_merge(D, I, r0)
         Dh.copy_(Dm, non_blocking=True)
         Ih.copy_(Im, non_blocking=True)
         torch.cuda.synchronize()
@@ -603,7 +601,7 @@ def run_b200(a):
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload_name(a), "nq": a.nq, "n": a.n, "d": a.d, "k": a.k,
-                   "parallelism": "gallery rows sharded %d-way, queries replicated, 1 all-gather of [Q,k] (d2,idx) + merge" % G
+                   "parallelism": "gallery rows sharded %d-way, queries replicated, 1 all-gather of [Q,k] packed (d2,row) keys + merge" % G
                    if G > 1 else "single GPU",
                    "l2_policy": "inputs larger than L2 (gallery shard %.1f GB per rank)" % ((r1 - r0) * a.d * 2 / 1e9),
                    "tie_break": "d2 ascending, lowest gallery row first", "result": "canonical fp32 d2, verified top-k"},

@@ -229,6 +229,15 @@ VQ_API int vq_window_means(const float *feat, int C, int64_t Ttot, const int64_t
 VQ_API int vq_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k,
                          float *out_d2, int64_t *out_idx, void *stream);
 
+/* 8e, packed form of the same exchange: a rank turns its local list (d2 f32[count], idx int64[count] LOCAL rows,
+ * -1 = empty) into one 8-byte key per entry, (order-preserving d2 bits << 32 | row_offset + idx; all ones = empty;
+ * global rows must fit 32 bits), all-gathers the keys in ONE collective (8 instead of 12 bytes per entry) and
+ * vq_topk_merge_keys sorts keys u64[G,nq,k] into the same [nq,k] answer vq_topk_merge gives. */
+VQ_API int vq_topk_pack(const float *d2, const int64_t *idx, int64_t count, int64_t row_offset,
+                        uint64_t *keys, void *stream);
+VQ_API int vq_topk_merge_keys(const uint64_t *keys, int G, int64_t nq, int64_t k, float *out_d2,
+                              int64_t *out_idx, void *stream);
+
 /* Canonical all-pairs squared L2 (CUDA cores), out f32[nq,n]; test / small-problem utility. */
 VQ_API int vq_l2sq(const float *q, const float *g, int64_t nq, int64_t n, int d, float *out,
                    void *stream);

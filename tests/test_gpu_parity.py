@@ -602,6 +602,22 @@ def test_topk_merge(vq):
     assert np.array_equal(oi, wi) and np.array_equal(od.view(np.uint32), wd.view(np.uint32))
 
 
+def test_topk_pack_merge_keys(vq):
+    """The packed exchange (one 8-byte key per entry) gives what topk_merge gives on (d2, global row) lists."""
+    rng = np.random.default_rng(12)
+    G, nq, k = 8, 41, 100
+    d2 = np.sort(rng.random((G, nq, k)).astype(np.float32), axis=2)
+    local = np.stack([np.stack([np.sort(rng.choice(5000, k, replace=False)) for _ in range(nq)]) for _ in range(G)]).astype(np.int64)
+    local[3, :, 80:] = -1
+    d2[5, 2, :7] = d2[4, 2, :7]                      # cross-shard ties: the lower global row wins
+    offs = np.arange(G) * 5000
+    keys = np.stack([vq.topk_pack(d2[g], local[g], offs[g]) for g in range(G)])
+    od, oi = vq.topk_merge_keys(keys)
+    glob = np.where(local >= 0, local + offs[:, None, None], -1)
+    wd, wi = orc.topk_merge(d2, glob)
+    assert np.array_equal(oi, wi) and np.array_equal(od.view(np.uint32), wd.view(np.uint32))
+
+
 def test_full_size_cfg1_properties(vq):
     """BASELINE configs[0] shape (4096 x 20480 x 512): oracle on a query subsample + properties."""
     rng = np.random.default_rng(10)

@@ -770,6 +770,39 @@ int vq_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_
     return VQ_OK;
 }
 
+int vq_topk_pack(const float *d2, const int64_t *idx, int64_t count, int64_t row_offset, uint64_t *keys, void *stream) {
+    VQ_CHECK(d2 && idx && keys, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(count >= 0 && row_offset >= 0, VQ_ERR_INVALID, "bad shape");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In a, b;
+    Out o;
+    VQ_TRY(a.bind(d2, (size_t)count * 4, st));
+    VQ_TRY(b.bind(idx, (size_t)count * 8, st));
+    VQ_TRY(o.bind(keys, (size_t)count * 8, st));
+    VQ_TRY(launch_topk_pack(a.as<float>(), b.as<int64_t>(), count, row_offset, o.as<uint64_t>(), st));
+    VQ_TRY(o.finish(st));
+    if (o.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
+int vq_topk_merge_keys(const uint64_t *keys, int G, int64_t nq, int64_t k, float *out_d2, int64_t *out_idx, void *stream) {
+    VQ_CHECK(keys && out_d2 && out_idx, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(G >= 1 && nq >= 0 && k >= 1, VQ_ERR_INVALID, "bad shape");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In a;
+    Out oD, oI;
+    VQ_TRY(a.bind(keys, (size_t)G * nq * k * 8, st));
+    VQ_TRY(oD.bind(out_d2, (size_t)nq * k * 4, st));
+    VQ_TRY(oI.bind(out_idx, (size_t)nq * k * 8, st));
+    VQ_TRY(launch_topk_merge_keys(a.as<uint64_t>(), G, nq, k, oD.as<float>(), oI.as<int64_t>(), st));
+    VQ_TRY(oD.finish(st));
+    VQ_TRY(oI.finish(st));
+    if (oD.host || oI.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
 int vq_l2sq(const float *q, const float *g, int64_t nq, int64_t n, int d, float *out, void *stream) {
     VQ_CHECK(q && g && out, VQ_ERR_INVALID, "NULL argument");
     VQ_TRY(check_device());

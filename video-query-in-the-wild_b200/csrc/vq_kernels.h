@@ -168,6 +168,8 @@ int launch_average_precision(const int32_t *y_true, const double *y_score, const
                              cudaStream_t st);
 int launch_nms1d(const double *dets, const int64_t *offsets, int64_t nseg, double thresh,
                  uint8_t *keep, uint8_t *dead_scratch, cudaStream_t st);
+int launch_topk_pack(const float *d2, const int64_t *idx, int64_t count, int64_t row_offset, uint64_t *keys, cudaStream_t st);
+int launch_topk_merge_keys(const uint64_t *keys, int G, int64_t nq, int64_t k, float *od, int64_t *oi, cudaStream_t st);
 int launch_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k, float *od,
                       int64_t *oi, cudaStream_t st);
 

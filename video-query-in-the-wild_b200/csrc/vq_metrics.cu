@@ -534,6 +534,54 @@ __global__ void __launch_bounds__(128) topk_merge_kernel(const float *__restrict
     }
 }
 
+// Packed exchange: a rank's local list as ONE 8-byte key per entry, (ordered d2 << 32 | global row),
+// so the all-gather moves 8 instead of 12 bytes per entry in one collective and the merge sorts what arrives.
+__global__ void __launch_bounds__(256) topk_pack_kernel(const float *__restrict__ d2, const int64_t *__restrict__ idx,
+                                                        int64_t count, int64_t row_offset, uint64_t *__restrict__ keys) {
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= count) return;
+    const int64_t r = idx[i];
+    keys[i] = r < 0 ? ~0ull : make_key_asc(d2[i], (uint32_t)(r + row_offset));
+}
+
+__global__ void __launch_bounds__(128) topk_merge_keys_kernel(const uint64_t *__restrict__ in, int G, int64_t nq, int64_t k,
+                                                              float *__restrict__ od, int64_t *__restrict__ oi, int n2) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint64_t *keys = (uint64_t *)sm;
+    const int64_t q = blockIdx.x;
+    const int total = (int)(G * k);
+    for (int i = threadIdx.x; i < n2; i += blockDim.x) {
+        const int g = i / (int)k, j = i % (int)k;
+        keys[i] = i < total ? in[((int64_t)g * nq + q) * k + j] : ~0ull;
+    }
+    __syncthreads();
+    block_bitonic_sort(keys, n2);
+    for (int i = threadIdx.x; i < k; i += blockDim.x) {
+        const uint64_t kk = keys[i];
+        const bool ok = kk != ~0ull;
+        od[q * k + i] = ok ? ordered_to_f32((uint32_t)(kk >> 32)) : INFINITY;
+        oi[q * k + i] = ok ? (int64_t)(uint32_t)kk : -1;
+    }
+}
+
+int launch_topk_pack(const float *d2, const int64_t *idx, int64_t count, int64_t row_offset, uint64_t *keys, cudaStream_t st) {
+    if (count == 0) return VQ_OK;
+    topk_pack_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(d2, idx, count, row_offset, keys);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+int launch_topk_merge_keys(const uint64_t *keys, int G, int64_t nq, int64_t k, float *od, int64_t *oi, cudaStream_t st) {
+    if (nq == 0) return VQ_OK;
+    const int n2 = next_pow2((int)(G * k));
+    const size_t smem = (size_t)n2 * 8;
+    VQ_CHECK(smem <= 200 * 1024, VQ_ERR_CAPACITY, "topk_merge: G*k=%lld too large", (long long)(G * k));
+    VQ_CUDA(cudaFuncSetAttribute(topk_merge_keys_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    topk_merge_keys_kernel<<<(unsigned)nq, 128, smem, st>>>(keys, G, nq, k, od, oi, n2);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
 int launch_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k, float *od, int64_t *oi,
                       cudaStream_t st) {
     if (nq == 0) return VQ_OK;

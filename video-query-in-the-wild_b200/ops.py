@@ -36,6 +36,38 @@ def topk_merge(d2, idx):
     return od, oi
 
 
+def topk_pack(d2, idx, row_offset=0):
+    """Local list -> packed keys int64[...] (bit pattern of u64: ordered d2 << 32 | row_offset + idx; -1 = empty)."""
+    keys = L.empty_like_kind(d2, tuple(d2.shape), np.int64)
+    L.check(L.lib().vq_topk_pack(L.ptr(d2), L.ptr(idx), C.c_int64(int(np.prod(d2.shape))), C.c_int64(int(row_offset)),
+                                 L.ptr(keys), L.stream_of(d2)))
+    return keys
+
+
+def topk_merge_keys(keys):
+    """[G,nq,k] packed keys -> ([nq,k] d2, [nq,k] global rows), the answer of ``topk_merge``."""
+    G, nq, k = keys.shape
+    od = L.empty_like_kind(keys, (nq, k), np.float32)
+    oi = L.empty_like_kind(keys, (nq, k), np.int64)
+    L.check(L.lib().vq_topk_merge_keys(L.ptr(keys), C.c_int(G), C.c_int64(nq), C.c_int64(k), L.ptr(od), L.ptr(oi),
+                                       L.stream_of(keys)))
+    return od, oi
+
+
+def exchange_merge(D, I, row_offset, group=None):
+    """The exchange step of the row-sharded search on CUDA tensors: pack the local list (LOCAL rows I, this rank's
+    first global row ``row_offset``), ONE all-gather of the 8-byte keys, merge.  Same result as
+    ``merge_gathered(D, I + row_offset)``, a third fewer bytes and one collective instead of two."""
+    import torch
+    import torch.distributed as dist
+    ws = dist.get_world_size(group)
+    nq, k = D.shape
+    keys = topk_pack(D.contiguous(), I.contiguous(), row_offset)
+    gk = torch.empty((ws * nq, k), dtype=torch.int64, device=D.device)
+    dist.all_gather_into_tensor(gk, keys, group=group)
+    return topk_merge_keys(gk.view(ws, nq, k))
+
+
 def sharded_search(index, xq, k, row_offset, group=None):
     """Row-sharded gallery: every rank searches its shard (`index` holds rows
     [row_offset, row_offset + ntotal) of the global gallery), the per-rank top-k lists are
@@ -46,6 +78,8 @@ def sharded_search(index, xq, k, row_offset, group=None):
     D, I = index.search(xq, k)
     D = torch.as_tensor(D)
     I = torch.as_tensor(I)
+    if D.is_cuda:
+        return exchange_merge(D, I, row_offset, group)
     I = torch.where(I >= 0, I + int(row_offset), I)
     return merge_gathered(D, I, group)
 
