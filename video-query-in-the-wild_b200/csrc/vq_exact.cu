@@ -93,6 +93,10 @@ __global__ void __launch_bounds__(kExThreads) exact_topk_kernel(const FallbackPa
     int *scratch = (int *)(qs + p.d);         // [40]; [36] = count, [37] = ignore list base
     int *ign = scratch + 40;                  // [kMaxIgnore]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // rows are scored 32 at a time through this warp's shared-memory tile (coalesced copies, vq_blocksel.cuh) when
+    // they are whole 128-byte chunks
+    const bool tiled = ((size_t)p.d * sizeof(T)) % 128 == 0 && (((uintptr_t)p.g) & 15) == 0;
+    uint8_t *tile = (uint8_t *)((((uintptr_t)(ign + kMaxIgnore)) + 127) & ~(uintptr_t)127) + warp * kRescoreTileBytes;
     const int nlist = p.unproven_count ? *p.unproven_count : (int)p.nq;
     const int ksort = next_pow2(p.k);
 
@@ -111,13 +115,18 @@ __global__ void __launch_bounds__(kExThreads) exact_topk_kernel(const FallbackPa
             uint64_t key = ~0ull;
             if (!SEGMAX) {
                 const int64_t j = base + tid;
-                if (j < p.n) {
-                    bool masked = false;
-                    if (p.n_ign > 0) {
-                        const int v = p.col_video[j];
-                        for (int z = 0; z < p.n_ign; ++z) masked |= (v == ign[z]);
+                bool want = j < p.n;
+                if (want && p.n_ign > 0) {
+                    const int v = p.col_video[j];
+                    for (int z = 0; z < p.n_ign; ++z) want &= (v != ign[z]);
+                }
+                if (tiled) {
+                    if (base + warp * 32 < p.n) {  // warp-uniform: at least one lane has a row; the others copy a valid one
+                        const float d2v = warp_canon_d2_rows<T>(qs, (const T *)p.g + (j < p.n ? j : p.n - 1) * p.d, p.d, tile, lane);
+                        if (want) key = make_key_asc(d2v, (uint32_t)j);
                     }
-                    if (!masked) key = make_key_asc(canon_d2_row<T>(qs, (const T *)p.g + j * p.d, p.d), (uint32_t)j);
+                } else if (want) {
+                    key = make_key_asc(canon_d2_row<T>(qs, (const T *)p.g + j * p.d, p.d), (uint32_t)j);
                 }
             } else {
                 const int64_t v = base + warp;
@@ -129,7 +138,14 @@ __global__ void __launch_bounds__(kExThreads) exact_topk_kernel(const FallbackPa
                         for (int z = 0; z < p.n_ign; ++z) masked |= (vid == ign[z]);
                     }
                     uint64_t best = ~0ull;
-                    if (!masked)
+                    if (!masked && tiled) {
+                        for (int64_t r0 = s0; r0 < s1; r0 += 32) {
+                            const int64_t rr = r0 + lane;
+                            const float d2v = warp_canon_d2_rows<T>(qs, (const T *)p.g + (rr < s1 ? rr : r0) * p.d, p.d, tile, lane);
+                            const uint64_t kk = rr < s1 ? make_key_asc(d2v, (uint32_t)rr) : ~0ull;
+                            best = kk < best ? kk : best;
+                        }
+                    } else if (!masked)
                         for (int64_t rr = s0 + lane; rr < s1; rr += 32) {
                             const uint64_t kk =
                                 make_key_asc(canon_d2_row<T>(qs, (const T *)p.g + rr * p.d, p.d), (uint32_t)rr);
@@ -198,7 +214,8 @@ __global__ void __launch_bounds__(kExThreads) exact_topk_kernel(const FallbackPa
 
 template <typename T, bool SEGMAX>
 static int launch_ex(const FallbackParams &p, int grid, cudaStream_t st) {
-    const size_t smem = (size_t)kExCap * 8 + (size_t)p.d * 4 + 40 * 4 + kMaxIgnore * 4 + 16;
+    const size_t smem = (size_t)kExCap * 8 + (size_t)p.d * 4 + 40 * 4 + kMaxIgnore * 4 + 16 + 128 +
+                        (size_t)(kExThreads / 32) * kRescoreTileBytes;
     auto kern = exact_topk_kernel<T, SEGMAX>;
     VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<grid, kExThreads, smem, st>>>(p);
