@@ -28,24 +28,34 @@ __global__ void __launch_bounds__(256) l2sq_all_kernel(const T *__restrict__ q, 
 #pragma unroll
         for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
     const int lr = tid >> 2, lk = (tid & 3) * 8;  // loader: row lr, 8 consecutive k
+    // The next k-block's values are fetched into registers while this one is being multiplied (the global latency
+    // used to sit between the two barriers of every step); the tile columns are XOR-swizzled by the k-group so that
+    // the four loader lanes of a row do not land in one bank.
+    const int sw_st = (lk >> 3) << 3;  // (tid & 3) << 3
+    float rq[8], rg[8];
+    auto fetch = [&](int k0) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            const int k = k0 + lk + e;
+            rq[e] = (k < d && q0 + lr < nq) ? to_f32<T>(q[(q0 + lr) * d + k]) : 0.f;
+            rg[e] = (k < d && g0 + lr < n) ? to_f32<T>(g[(g0 + lr) * d + k]) : 0.f;
+        }
+    };
+    fetch(0);
     for (int k0 = 0; k0 < d; k0 += AK) {
         __syncthreads();
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-            const int k = k0 + lk + e;
-            float vq_ = 0.f, vg_ = 0.f;
-            if (k < d) {
-                if (q0 + lr < nq) vq_ = to_f32<T>(q[(q0 + lr) * d + k]);
-                if (g0 + lr < n) vg_ = to_f32<T>(g[(g0 + lr) * d + k]);
-            }
-            sQ[lk + e][lr] = vq_;
-            sG[lk + e][lr] = vg_;
+            sQ[lk + e][lr ^ sw_st] = rq[e];
+            sG[lk + e][lr ^ sw_st] = rg[e];
         }
         __syncthreads();
+        if (k0 + AK < d) fetch(k0 + AK);
 #pragma unroll
         for (int kk = 0; kk < AK; ++kk) {
-            const float4 a4 = *reinterpret_cast<const float4 *>(&sQ[kk][ty * 4]);
-            const float4 b4 = *reinterpret_cast<const float4 *>(&sG[kk][tx * 4]);
+            const int sw = (kk >> 3) << 3;
+            const float4 a4 = *reinterpret_cast<const float4 *>(&sQ[kk][(ty * 4) ^ sw]);
+            const float4 b4 = *reinterpret_cast<const float4 *>(&sG[kk][(tx * 4) ^ sw]);
             const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
             for (int a = 0; a < 4; ++a)
