@@ -78,7 +78,7 @@ def sharded_search(index, xq, k, row_offset, group=None):
     D, I = index.search(xq, k)
     D = torch.as_tensor(D)
     I = torch.as_tensor(I)
-    if D.is_cuda:
+    if D.is_cuda and int(row_offset) + int(index.ntotal) <= 1 << 32:   # packed keys carry the global row in 32 bits
         return exchange_merge(D, I, row_offset, group)
     I = torch.where(I >= 0, I + int(row_offset), I)
     return merge_gathered(D, I, group)
