@@ -301,13 +301,14 @@ def aux_windows(torch, peaks_hbm, V=2048, T=600, C=512):
     feat = torch.rand(C, V * T, device="cuda")
     lo_d = torch.from_numpy(np.tile(lo, V).astype(np.int32)).cuda()
     hi_d = torch.from_numpy(np.tile(hi, V).astype(np.int32)).cuda()
-    for _ in range(2):
-        ops.window_means(feat, t0, ws, lo_d, hi_d)
+    o = torch.empty((V * nw, C), dtype=torch.float32, device="cuda")   # allocated once: a 2.9 GB cudaMalloc inside the
+    for _ in range(2):                                                  # timed loop is what the number would show
+        ops.window_means(feat, t0, ws, lo_d, hi_d, out=o)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     e0.record()
     for _ in range(5):
-        o = ops.window_means(feat, t0, ws, lo_d, hi_d)
+        ops.window_means(feat, t0, ws, lo_d, hi_d, out=o)
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / 5

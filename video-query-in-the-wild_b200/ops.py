@@ -99,11 +99,12 @@ def merge_gathered(D, I, group=None, merge=None):
     return (merge or topk_merge)(gD.view(ws, nq, k), gI.view(ws, nq, k))
 
 
-def window_means(feat, vid_t0, win_start, lo, hi):
+def window_means(feat, vid_t0, win_start, lo, hi, out=None):
     """every window mean ``np.mean(video_feat[:, lo:hi], axis=1)`` of garner_feat
     (dataloader_baseline.py:1125-1147, :809-834) in one launch.  feat [C, Ttot] (per-frame features of the
     videos concatenated along time; numpy or CUDA tensor), vid_t0 / win_start int64[V+1], lo / hi int32 per
-    window relative to the video's first frame.  Returns [n_windows, C] float32 where ``feat`` lives."""
+    window relative to the video's first frame.  Returns [n_windows, C] float32 where ``feat`` lives (``out``: a
+    buffer of that shape to fill instead of allocating one)."""
     t0 = np.ascontiguousarray(vid_t0, dtype=np.int64)
     ws = np.ascontiguousarray(win_start, dtype=np.int64)
     feat = L.as_f32(feat)
@@ -112,7 +113,8 @@ def window_means(feat, vid_t0, win_start, lo, hi):
     if L._is_torch(feat) and feat.is_cuda and not L._is_torch(lo_):
         import torch
         lo_, hi_ = torch.from_numpy(lo_).to(feat.device), torch.from_numpy(hi_).to(feat.device)
-    out = L.empty_like_kind(feat, (int(ws[-1]), nch), np.float32)
+    if out is None:
+        out = L.empty_like_kind(feat, (int(ws[-1]), nch), np.float32)
     L.check(L.lib().vq_window_means(L.ptr(feat), C.c_int(nch), C.c_int64(Ttot), L.ptr(t0), L.ptr(ws),
                                     C.c_int64(len(t0) - 1), L.ptr(lo_), L.ptr(hi_), L.ptr(out), L.stream_of(feat)))
     return out
