@@ -151,6 +151,10 @@ def cpu_sample(a, steps, warmup):
     import numpy as np
     import torch
     from oracle import oracle as orc
+    # all the host threads this process may use: torchrun exports OMP_NUM_THREADS=1 to its ranks, which would time
+    # the CPU arm on one core at N>1 (VQ_CPU_THREADS overrides)
+    want = int(os.environ.get("VQ_CPU_THREADS", "0")) or len(os.sched_getaffinity(0))
+    orc.set_num_threads(want)
     cores = orc.num_threads()
     n_s = min(a.n, 1 << 18)
     nq_s = min(a.nq, 4 * cores)
