@@ -157,7 +157,7 @@ def cpu_sample(a, steps, warmup):
     orc.set_num_threads(want)
     cores = orc.num_threads()
     n_s = min(a.n, 1 << 18)
-    nq_s = min(a.nq, 4 * cores)
+    nq_s = min(a.nq, 32 * cores)  # ~7 s of work per step on 16 threads
     g = gen_block(torch, "g", 0, n_s, a.d, "cpu").float().numpy()
     q = gen_block(torch, "q", 0, nq_s, a.d, "cpu").float().numpy()
     times = []
