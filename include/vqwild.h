@@ -57,6 +57,10 @@ typedef enum {
 
 VQ_API int vq_version(void);
 VQ_API const char *vq_last_error(void);
+/* Test / A-B hooks ("FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS",
+ * "NO_TC_EVAL").  Their initial values come from the VQ_DEBUG_<NAME> environment variables, read once when the
+ * library is loaded; no entry point reads the environment afterwards. */
+VQ_API int vq_debug_set(const char *hook, int value);
 /* 0 if device `dev` exists and is sm_100; else VQ_ERR_NO_DEVICE / VQ_ERR_ARCH. */
 VQ_API int vq_device_check(int dev);
 
@@ -88,8 +92,9 @@ VQ_API int vq_index_set_segments(vq_index *ix, const int64_t *seg_start, int64_t
 
 /* faiss-shaped search.  xq [nq,d] (host or device, dtype as given); outputs D float32[nq,k]
  * (canonical squared L2, ascending) and I int64[nq,k] (host or device; -1 / +inf padding when
- * fewer than k rows qualify).  k <= ntotal.  k <= 1024 takes the tensor-core streaming top-k
- * path; larger k (the reference's k = ntotal, :1594) takes the full-sort path.
+ * fewer than k rows qualify).  k <= ntotal.  k <= 512 takes the tensor-core streaming top-k path
+ * (gemm_topk + select); larger k -- the reference's own call is k = ntotal, :1594 -- takes the full-sort path:
+ * canonical scores of every pair + a stable per-row radix sort (vq_sort.cu), tiled over the queries.
  * ignore_video: optional int32[nq, n_ignore] (host or device) -- rows whose video id matches
  * any entry are skipped (the reference's ignore rule, :1548); requires vq_index_set_meta. */
 VQ_API int vq_index_search(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k,
@@ -130,8 +135,10 @@ VQ_API int vq_index_eval_trimmed(vq_index *ix, const void *xq, int64_t nq, int d
  * (:1268-1281) + do_nms (:1283-1312: cluster by video in first-seen order, nms_cpu per cluster)
  * + tp = IoU >= 0.5 (:1315-1319) + multiprocess_calculate (:386-402) on the grouped list.
  *   vq_index_set_moments  per gallery row (host or device, [ntotal]): start_sec, end_sec (f32),
- *                         closest_hit IoU (f32; 0 when there is no hit) and closest_hit label id
- *                         (int32; -1 when there is none).  Requires vq_index_set_segments (one
+ *                         closest_hit IoU (f32; 0 when there is no hit; tp tests iou >= 0.5f -- the reference
+ *                         compares the FLOAT64 IoU, :1315-1319, so callers holding float64 values pass the flag
+ *                         (iou64 >= 0.5 ? 1 : 0) to keep boundary cases exact; the Python mirror does) and
+ *                         closest_hit label id (int32; -1 when there is none).  Requires vq_index_set_segments (one
  *                         segment per video, <= 4096 moments each) and vq_index_set_meta (video).
  *   vq_index_eval_moment  q_label int32[nq], ignore_video int32[nq,n_ignore];
  *                         ap float64[nq], recall float64[nq,3]; optional n_kept int64[nq] (moments

@@ -21,23 +21,22 @@ D = torch.empty((nq, 100), dtype=torch.float32, device=dev)
 I = torch.empty((nq, 100), dtype=torch.int64, device=dev)
 variants = {
     "dense8(default)": {},
-    "nodense": {"VQ_DEBUG_DENSE_ROWS": "33"},
-    "dense2": {"VQ_DEBUG_DENSE_ROWS": "2"},
-    "dense3": {"VQ_DEBUG_DENSE_ROWS": "3"},
-    "dense4": {"VQ_DEBUG_DENSE_ROWS": "4"},
-    "dense16": {"VQ_DEBUG_DENSE_ROWS": "16"},
-    "nochain+nodense": {"VQ_DEBUG_NO_CHAIN": "1", "VQ_DEBUG_DENSE_ROWS": "33"},
+    "nodense": {"DENSE_ROWS": 33},
+    "dense2": {"DENSE_ROWS": 2},
+    "dense3": {"DENSE_ROWS": 3},
+    "dense4": {"DENSE_ROWS": 4},
+    "dense16": {"DENSE_ROWS": 16},
+    "nochain+nodense": {"NO_CHAIN": 1, "DENSE_ROWS": 33},
 }
-keys = ("VQ_DEBUG_NO_CHAIN", "VQ_DEBUG_DENSE_ROWS")
+keys = {"NO_CHAIN": 0, "DENSE_ROWS": -1}
 for _ in range(3):
     ix.search(xq, 100, out=(D, I))
 res = {k: [] for k in variants}
 ref = None
 for r in range(rounds):
     for name, env in variants.items():
-        for k in keys:
-            os.environ.pop(k, None)
-        os.environ.update(env)
+        for k, dflt in keys.items():
+            vq._lib.debug_set(k, env.get(k, dflt))
         ix.search(xq, 100, out=(D, I))
         t = ix.last_timing()
         res[name].append(t["gemm_topk_ms"])

@@ -24,9 +24,9 @@ for G in (1, 148, 4096):
         if mode == "simt":
             if G > 148:
                 continue
-            os.environ["VQ_DEBUG_NO_TC_TRIPLET"] = "1"
+            L.debug_set("NO_TC_TRIPLET", 1)
         else:
-            os.environ.pop("VQ_DEBUG_NO_TC_TRIPLET", None)
+            L.debug_set("NO_TC_TRIPLET", 0)
 
         def run():
             L.check(lib.vq_triplet_batchhard(L.ptr(emb), L.ptr(lab), C.c_int64(G), C.c_int64(256), C.c_int(512),

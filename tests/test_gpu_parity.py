@@ -139,14 +139,15 @@ def test_search_with_ignore_and_device_tensors(vq):
 def test_search_forced_fallback_path(vq):
     rng = np.random.default_rng(4)
     q, g = _emb(rng, 40, 128), _emb(rng, 3000, 128)
-    os.environ["VQ_DEBUG_FORCE_FALLBACK"] = "1"
+    from vqwild_b200 import _lib as L
+    L.debug_set("FORCE_FALLBACK", 1)
     try:
         ix = vq.IndexFlatL2(128)
         ix.add(g)
         D, I = ix.search(q, 100)
         st = ix.last_stats()
     finally:
-        del os.environ["VQ_DEBUG_FORCE_FALLBACK"]
+        L.debug_set("FORCE_FALLBACK", 0)
     assert st["fallback_queries"] == 40
     Do, Io = orc.search(q, g, 100)
     assert np.array_equal(I, Io) and np.array_equal(D.view(np.uint32), Do.view(np.uint32))
@@ -166,7 +167,7 @@ def test_search_bf16_input_mode(vq):
     assert np.array_equal(D.cpu().numpy().view(np.uint32), Do.view(np.uint32))
     # bf16-input scores vs the fp32 originals: 2e-3 relative (north_star, stated separately)
     ref = ((q[:, None, :].astype(np.float64) - g[Io].astype(np.float64)) ** 2).sum(-1)
-    assert np.max(np.abs(Do - ref) / ref) < 2e-2  # distances near 2.0; bf16 rounding of inputs
+    assert np.max(np.abs(Do - ref) / ref) < 2e-3  # the stated bar; measured ~2e-4 (bf16 rounding of 512 unit-scale components)
 
 
 @pytest.mark.parametrize("ragged", [False, True])

@@ -43,6 +43,11 @@ def lib():
     return _lib
 
 
+def debug_set(hook, value):
+    """Test / A-B hooks (FORCE_FALLBACK, NO_PAIR, NO_CHAIN, DENSE_ROWS, NO_TC_TRIPLET, TRIPLET_CLOCKS, NO_TC_EVAL)."""
+    check(lib().vq_debug_set(hook.encode(), C.c_int(int(value))))
+
+
 def check(rc):
     if rc != 0:
         raise VqError(rc, lib().vq_last_error().decode())

@@ -2,6 +2,7 @@
 // index object and the orchestration of the kernels.  Host logic only; every number a caller
 // sees is produced by the kernels in this directory.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -11,6 +12,25 @@
 #include "vq_kernels.h"
 
 namespace vq {
+
+DebugHooks g_hooks;
+static int *hook_slot(const char *name) {
+    struct { const char *n; int *p; } tab[] = {
+        {"FORCE_FALLBACK", &g_hooks.force_fallback}, {"NO_PAIR", &g_hooks.no_pair}, {"NO_CHAIN", &g_hooks.no_chain},
+        {"DENSE_ROWS", &g_hooks.dense_rows}, {"NO_TC_TRIPLET", &g_hooks.no_tc_triplet},
+        {"TRIPLET_CLOCKS", &g_hooks.triplet_clocks}, {"NO_TC_EVAL", &g_hooks.no_tc_eval}};
+    for (auto &t : tab)
+        if (!strcmp(name, t.n)) return t.p;
+    return nullptr;
+}
+static const bool g_hooks_from_env = [] {
+    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL"}) {
+        char env[64];
+        snprintf(env, sizeof(env), "VQ_DEBUG_%s", n);
+        if (const char *e = getenv(env)) *hook_slot(n) = atoi(e);
+    }
+    return true;
+}();
 
 static thread_local char g_err[512] = "";
 void set_error(const char *fmt, ...) {
@@ -238,7 +258,15 @@ static size_t esize(int dtype) { return dtype == VQ_F32 ? 4 : 2; }
 
 extern "C" {
 
-int vq_version(void) { return 100; }
+int vq_version(void) { return 200; }
+
+int vq_debug_set(const char *hook, int value) {
+    VQ_CHECK(hook, VQ_ERR_INVALID, "NULL hook name");
+    int *p = hook_slot(hook);
+    VQ_CHECK(p, VQ_ERR_INVALID, "unknown debug hook %s", hook);
+    *p = value;
+    return VQ_OK;
+}
 const char *vq_last_error(void) { return g_err; }
 
 int vq_device_check(int dev) {

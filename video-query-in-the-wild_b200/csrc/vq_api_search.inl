@@ -3,6 +3,8 @@
 
 namespace vq {
 
+
+
 static int resolve_prec(const vq_index *ix) {
     if (ix->prec != VQ_PREC_AUTO) return ix->prec;
     return ix->dtype == VQ_F32 ? VQ_PREC_SPLIT3 : VQ_PREC_BF16;
@@ -23,7 +25,7 @@ static void error_model(int prec, int dtype, int dp, float *eps_rel, float *eps_
     if (dtype == VQ_F32) rel += prec == VQ_PREC_SPLIT3 ? 2.4e-5f : 8.0e-3f;  // operand rounding to bf16 (split / single)
     *eps_rel = rel;
     *eps_abs = 6.0f * dp * u;                               // |g|^2 reduction and its 3-term bf16 split + the canonical chain's own rounding
-    if (getenv("VQ_DEBUG_FORCE_FALLBACK")) *eps_abs = 1e30f;  // test hook: no query can be proven
+    if (g_hooks.force_fallback) *eps_abs = 1e30f;  // test hook: no query can be proven
 }
 
 // Work plan (vq_kernels.h, GemmTopkParams).  The gallery is cut into `n_chunks` row ranges so that
@@ -83,7 +85,7 @@ static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int k
         sb[(size_t)s_] = cs[(size_t)chunk];
         se[(size_t)s_] = cs[(size_t)chunk + 1];
         sg[(size_t)s_] = (int32_t)g;
-        pred[(size_t)s_] = (chunk > 0 && !getenv("VQ_DEBUG_NO_CHAIN")) ? s_of_u[(size_t)(u - n_groups)] : -1;  // A/B hook
+        pred[(size_t)s_] = (chunk > 0 && !g_hooks.no_chain) ? s_of_u[(size_t)(u - n_groups)] : -1;  // A/B hook
         gsegs[(size_t)(g * n_chunks + chunk)] = s_;
     }
     pl->nseg = (int)units;
@@ -136,7 +138,7 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     const int kprime = choose_kprime(k, prec, dtype);
     VQ_CHECK(k <= kprime, VQ_ERR_CAPACITY, "k=%d exceeds the streaming top-k limit %d", k, kMaxKPrime);
     // bf16 single pass with dim <= 512 runs on CTA pairs (resident queries, split gallery tiles)
-    const bool pair = prec != VQ_PREC_SPLIT3 && ix->dp <= 512 && !getenv("VQ_DEBUG_NO_PAIR");
+    const bool pair = prec != VQ_PREC_SPLIT3 && ix->dp <= 512 && !g_hooks.no_pair;
     // query operand planes
     Tmp qhi, qlo;
     ix->ev_valid = false;
@@ -190,7 +192,7 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     gp.col_seg = segmax ? ix->seg_of_row : nullptr;
     gp.q_ignore = n_ign > 0 ? ign : nullptr; gp.n_ign = n_ign; gp.kprime = kprime;
     gp.dense_rows = 4;  // measured: scripts/ab_gemm.py, profiles/r01_ab_gemm_chain_dense.txt
-    if (const char *e = getenv("VQ_DEBUG_DENSE_ROWS")) gp.dense_rows = atoi(e);  // A/B hook (33 = never)
+    if (g_hooks.dense_rows >= 0) gp.dense_rows = g_hooks.dense_rows;  // A/B hook (33 = never)
     gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau;
     VQ_CUDA(cudaEventRecord(ix->ev[1], st));
     if (pair) {
@@ -249,6 +251,39 @@ static int64_t score_tile_bytes() {
     return std::max<int64_t>((int64_t)256 << 20, std::min<int64_t>((int64_t)8 << 30, quarter));
 }
 
+// k > kMaxKPrime: the reference's own call, search(xq, k = ntotal) (dataloader_baseline.py:1592-1597, :935-940,
+// :1268-1273) -- canonical scores of a tile of queries against every row, then a stable per-row radix sort
+// (vq_sort.cu).  The first k entries of each sorted row are written.  All pointers are device pointers.
+static int full_sort_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k, const int32_t *ign, int n_ign,
+                          float *D, int64_t *I, cudaStream_t st) {
+    // per query: 4 B score + 2 x 8 B sort buffers per row (+ histograms)
+    int64_t tile_q = score_tile_bytes() / std::max<int64_t>(1, ix->n * 20);
+    tile_q = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(nq, tile_q), 32768));
+    Tmp d2, a, b, h;
+    VQ_TRY(d2.alloc((size_t)tile_q * ix->n * 4, st));
+    VQ_TRY(a.alloc((size_t)tile_q * ix->n * 8, st));
+    VQ_TRY(b.alloc((size_t)tile_q * ix->n * 8, st));
+    VQ_TRY(h.alloc(rowsort_hist_ints(tile_q, ix->n) * 4, st));
+    int launches = 0;
+    for (int64_t q0 = 0; q0 < nq; q0 += tile_q) {
+        const int64_t tq = std::min(tile_q, nq - q0);
+        const char *qt = (const char *)xq + (size_t)q0 * ix->d * esize(dtype);
+        VQ_TRY(launch_l2sq_all(qt, ix->raw, dtype, tq, ix->n, ix->d, (float *)d2.p, st));
+        RowSortParams r{};
+        r.nq_tile = tq; r.n = ix->n; r.k = k; r.d2 = (const float *)d2.p;
+        r.col_video = n_ign > 0 ? ix->video : nullptr;
+        r.q_ignore = n_ign > 0 ? ign + q0 * n_ign : nullptr;
+        r.n_ign = n_ign; r.hist = (int32_t *)h.p;
+        r.out_d2 = D + q0 * k; r.out_idx = I + q0 * k;
+        VQ_TRY(launch_row_sort(r, (uint64_t *)a.p, (uint64_t *)b.p, st));
+        launches += 13;
+    }
+    ix->ev_valid = false;
+    ix->stats[0] = 0; ix->stats[1] = 0; ix->stats[2] = 0; ix->stats[3] = 0; ix->stats[4] = 0; ix->stats[5] = launches;
+    VQ_CUDA(cudaMemsetAsync(ix->unproven_count, 0, 4, st));
+    return VQ_OK;
+}
+
 static int check_search_args(const vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k) {
     VQ_CHECK(ix && xq, VQ_ERR_INVALID, "NULL argument");
     VQ_CHECK(ix->n > 0, VQ_ERR_STATE, "search on an empty index");
@@ -269,9 +304,6 @@ int vq_index_search(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t
     VQ_CHECK(k <= ix->n, VQ_ERR_INVALID, "k=%lld exceeds ntotal=%lld", (long long)k, (long long)ix->n);
     VQ_CHECK(n_ignore >= 0 && n_ignore <= kMaxIgnore, VQ_ERR_INVALID, "n_ignore=%d (max %d)", n_ignore, kMaxIgnore);
     VQ_CHECK(!(ignore_video && n_ignore > 0) || ix->video, VQ_ERR_STATE, "ignore list given but no video ids set");
-    VQ_CHECK(k <= kMaxKPrime, VQ_ERR_CAPACITY,
-             "k=%lld: the streaming top-k path serves k <= %d; use vq_index_eval_trimmed for full-list metrics",
-             (long long)k, kMaxKPrime);
     if (nq == 0) return VQ_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const int n_ign = ignore_video ? n_ignore : 0;
@@ -281,8 +313,11 @@ int vq_index_search(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t
     VQ_TRY(ig.bind(ignore_video, (size_t)nq * n_ign * 4, st));
     VQ_TRY(oD.bind(D, (size_t)nq * k * 4, st));
     VQ_TRY(oI.bind(I, (size_t)nq * k * 8, st));
-    VQ_TRY(search_core(ix, q.dev, nq, dtype, (int)k, false, ig.as<int32_t>(), n_ign, oD.as<float>(), oI.as<int64_t>(),
-                       nullptr, st));
+    if (k > kMaxKPrime)
+        VQ_TRY(full_sort_core(ix, q.dev, nq, dtype, k, ig.as<int32_t>(), n_ign, oD.as<float>(), oI.as<int64_t>(), st));
+    else
+        VQ_TRY(search_core(ix, q.dev, nq, dtype, (int)k, false, ig.as<int32_t>(), n_ign, oD.as<float>(), oI.as<int64_t>(),
+                           nullptr, st));
     VQ_TRY(oD.finish(st));
     VQ_TRY(oI.finish(st));
     if (oD.host || oI.host) VQ_CUDA(cudaStreamSynchronize(st));

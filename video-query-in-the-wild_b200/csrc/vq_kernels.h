@@ -6,6 +6,14 @@
 
 namespace vq {
 
+// Debug / A-B hooks (tests, scripts/ab_*.py): initialised ONCE from the VQ_DEBUG_* environment when the library is
+// loaded and changed afterwards only through vq_debug_set() -- never getenv() on a search path.
+struct DebugHooks {
+    int force_fallback = 0, no_pair = 0, no_chain = 0, dense_rows = -1, no_tc_triplet = 0, triplet_clocks = 0,
+        no_tc_eval = 0;
+};
+extern DebugHooks g_hooks;
+
 static constexpr int kTileM = 128;      // queries per work unit (UMMA M)
 static constexpr int kTileN = 256;      // gallery rows per tile (UMMA N)
 static constexpr int kCandCap = 1024;   // candidate slots per (work unit, query)
@@ -111,6 +119,26 @@ struct FallbackParams {
     const int32_t *unproven_count;  // null => nq
 };
 int launch_exact_topk(const FallbackParams &p, int grid, cudaStream_t st);
+
+// ---- vq_sort.cu ----
+// Full ascending list per query (faiss search with k = ntotal, dataloader_baseline.py:1592-1597): stable LSD radix
+// sort of the canonical score tile d2[nq_tile, n]; the first k entries of every sorted row go to out_d2 / out_idx
+// ([nq_tile, k]); rows hit by the ignore rule sort last and are reported as +inf / -1.
+struct RowSortParams {
+    int64_t nq_tile, n, k;
+    const float *d2;            // [nq_tile, n] canonical
+    const int32_t *col_video;   // [n] or null
+    const int32_t *q_ignore;    // [nq_tile, n_ign] or null
+    int n_ign;
+    int32_t *hist;              // [rowsort_hist_ints(nq_tile, n)]
+    float *out_d2;
+    int64_t *out_idx;
+    const uint64_t *in;         // set per pass by launch_row_sort
+    uint64_t *out;
+};
+size_t rowsort_hist_ints(int64_t nq_tile, int64_t n);
+// bufA / bufB: u64[nq_tile * n] each
+int launch_row_sort(RowSortParams p, uint64_t *bufA, uint64_t *bufB, cudaStream_t st);
 
 // ---- vq_metrics.cu ----
 struct ApRowsParams {

@@ -663,7 +663,7 @@ int launch_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G,
                              float *loss, float *grad, int32_t *trip, float *scratch, int32_t *work, cudaStream_t st) {
     if (G == 0 || B == 0) return VQ_OK;
     const bool fused = B <= TB && d % 4 == 0 && d >= 4 && ((uintptr_t)emb & 15u) == 0 &&
-                       (!grad || ((uintptr_t)grad & 15u) == 0) && G * B < (1ll << 31) && !getenv("VQ_DEBUG_NO_TC_TRIPLET");
+                       (!grad || ((uintptr_t)grad & 15u) == 0) && G * B < (1ll << 31) && !g_hooks.no_tc_triplet;
     if (!fused) return launch_triplet_batchhard_simt(emb, labels, G, B, d, margin, loss, grad, trip, scratch, nullptr, nullptr, st);
     CUtensorMap tm;
     VQ_TRY(make_tensor_map_2d(&tm, emb, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (uint64_t)d, (uint64_t)(G * B), (uint64_t)d * 4,
@@ -679,7 +679,7 @@ int launch_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G,
     p.labels = labels; p.G = (int)G; p.B = (int)B; p.d = d; p.margin = margin;
     p.loss = loss; p.grad = grad; p.trip = trip; p.bad_count = work; p.bad_list = work + 1;
     static long long *dbg_buf = nullptr;
-    if (getenv("VQ_DEBUG_TRIPLET_CLOCKS")) {
+    if (g_hooks.triplet_clocks) {
         if (!dbg_buf) VQ_CUDA(cudaMalloc(&dbg_buf, 148 * 8 * 8));
         p.dbg = dbg_buf;
     }

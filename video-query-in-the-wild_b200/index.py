@@ -98,6 +98,9 @@ class IndexFlatL2:
     def set_moments(self, start_sec, end_sec, iou, hit_label):
         """Per-row moment metadata (candidate["start_sec"], ["end_sec"], closest_hit iou / label id,
         dataloader_baseline.py:1239-1255); needs ``set_segments`` (one segment per video) and ``set_meta``."""
+        if isinstance(iou, np.ndarray) and iou.dtype == np.float64:
+            # the reference tests the float64 IoU >= 0.5 (:1315-1319): take the threshold before narrowing to float32
+            iou = (iou >= 0.5).astype(np.float32)
         a = [L.as_f32(start_sec), L.as_f32(end_sec), L.as_f32(iou), L.as_i32(hit_label)]
         L.check(L.lib().vq_index_set_moments(self._h, L.ptr(a[0]), L.ptr(a[1]), L.ptr(a[2]), L.ptr(a[3]),
                                              L.stream_of(a[0])))

@@ -9,6 +9,14 @@ from .index import IndexFlatL2
 from .metrics import evaluation_metric, generate_multi_query
 
 
+def _has(args, name):
+    """``name in args`` for the reference's argparse namespace / dict-like args (:928)."""
+    try:
+        return name in args
+    except TypeError:
+        return hasattr(args, name)
+
+
 def _ids(values, table=None):
     table = {} if table is None else table
     out = np.empty(len(values), np.int32)
@@ -69,6 +77,64 @@ class ARV_Retrieval:
         return self.ranking()
 
 
+class ARV_Retrieval_Clip:
+    """``ARV_Retrieval_Clip.ranking`` (dataloader_baseline.py:883-955) over the reference's hand-off lists:
+    ``gallery_list`` = the non-overlapping clips of the untrimmed videos (``feat``, ``video_id``, ``clip_label`` from
+    ``cal_label`` :795-807 -- "unknown" when no annotation of a possible class contains the clip); ``query_list`` items
+    carry ``feat``, ``label``, ``video_id``, ``retrieval_type``.  tp = (clip_label == query label) :915-920, ignore =
+    shared video id :922-925, every query ranks ALL clips (:935-938); no ``is_query`` filter (:894 is commented out in
+    the reference)."""
+
+    def __init__(self, args, feat_extract_func=None, query_list=None, gallery_list=None):
+        self.args = args
+        self.feat_extract_func = feat_extract_func
+        self.query_list = query_list
+        self.gallery_list = gallery_list
+        self.faiss_index = None
+
+    def build_index(self):
+        """:872-881 plus the per-clip metadata the labelling loop reads."""
+        gl = self.gallery_list
+        xb = np.ascontiguousarray(np.stack([g["feat"].reshape(-1) for g in gl]), dtype=np.float32)
+        self.faiss_index = IndexFlatL2(xb.shape[1])
+        self.faiss_index.add(xb)
+        self.faiss_xb = xb
+        self._label_ids, self._label_table = _ids([g["clip_label"] for g in gl])
+        self._video_ids, self._video_table = _ids([g["video_id"] for g in gl])
+        self.faiss_index.set_meta(self._label_ids, self._video_ids)
+
+    def ranking(self):
+        if self.faiss_index is None:
+            self.build_index()
+        if getattr(self.args, "debug", False):                                   # :890-893
+            self.query_list = [[i] for i in self.query_list]
+        else:
+            self.query_list = generate_multi_query(self.query_list)
+        self.class_map_evaluation = evaluation_metric(self.args, self.query_list)
+        nq = len(self.query_list)
+        has_qn = _has(self.args, "query_num")
+        qn = int(self.args.query_num) if has_qn else 1                            # :928-934
+        xq = np.empty((nq, self.faiss_xb.shape[1]), np.float32)
+        for i, queries in enumerate(self.query_list):
+            acc = 0
+            for j in range(qn):
+                acc = acc + queries[j]["feat"]
+            xq[i] = acc / qn if has_qn else acc
+        q_label, _ = _ids([q[0]["label"] for q in self.query_list], dict(self._label_table))
+        ign = np.stack([_ids([x["video_id"] for x in q], dict(self._video_table))[0] for q in self.query_list])
+        ap, rec, _ = self.faiss_index.eval_trimmed(xq, q_label, ign)
+        cls = [q[0]["label"] for q in self.query_list]
+        typ = [q[0]["retrieval_type"] for q in self.query_list]
+        self.class_map_evaluation.update_arrays(cls, typ, ap, rec)
+        for i in range(nq):  # :436-440 -- the clip hit dicts carry gt_label but no "label"
+            survivors = int((~np.isin(self._video_ids, ign[i])).sum())
+            self.class_map_evaluation.cm_gt_labels.extend([cls[i]] * min(100, survivors))
+        return self.class_map_evaluation.get_result()
+
+    def evaluation(self):
+        return self.ranking()
+
+
 class ARV_Retrieval_Moment:
     """``ARV_Retrieval_Moment.ranking`` (dataloader_baseline.py:1206-1371) over the reference's hand-off
     lists: ``gallery_list`` = moments (``feat``, ``video_id``, ``start_sec``, ``end_sec``,
@@ -95,12 +161,16 @@ class ARV_Retrieval_Moment:
             raise ValueError("gallery_list: the moments of a video must be contiguous")
         self._label_table = {}
         hit = np.full(len(gl), -1, np.int32)
-        iou = np.zeros(len(gl), np.float32)
+        iou64 = np.zeros(len(gl), np.float64)
         for i, g in enumerate(gl):
             ch = g["closest_hit"]
             if ch is not None:
                 hit[i] = self._label_table.setdefault(ch["label"], len(self._label_table))
-                iou[i] = ch["iou"]
+                iou64[i] = ch["iou"]
+        # The reference tests the FLOAT64 closest_hit["iou"] >= 0.5 (:1315-1319); narrowing 0.49999999999999994 to
+        # float32 would flip it.  The tp threshold is therefore taken here, in float64, and the kernel's
+        # `iou >= 0.5f` sees an exact 1.0 / 0.0 flag.
+        iou = (iou64 >= 0.5).astype(np.float32)
         self.faiss_index = IndexFlatL2(xb.shape[1])
         self.faiss_index.add(xb)
         self.faiss_xb = xb
@@ -164,6 +234,39 @@ def clip_grid(duration, feat_length, fps=3, temporal_stride=1, clip_sec=6):
     a, z = st * fps // temporal_stride, (st + clip_sec) * fps // temporal_stride
     keep = z <= feat_length
     return st[keep], st[keep] + clip_sec, a[keep], z[keep]
+
+
+def cal_label(loc_sec, annotations, possible_classes):
+    """cal_label of ARV_Retrieval_Clip's garner_feat (:795-807): label of the FIRST annotation of a possible class
+    that fully contains the clip, else "unknown"."""
+    for ann in annotations:
+        seg = ann["segment"]
+        if seg[0] <= loc_sec[0] and seg[1] >= loc_sec[1] and ann["label"] in possible_classes:
+            return ann["label"]
+    return "unknown"
+
+
+def garner_clips(gallery_videos, possible_classes, fps=3, temporal_stride=1, clip_sec=6):
+    """All clips of all untrimmed videos in one device pass (the reference loops garner_feat over the videos on the
+    host, :836-844).  Returns dict(feat [n, C], video_id list, loc_sec [n, 2], clip_label list, seg_start)."""
+    from . import ops
+    t0, ws, los, his, ss, ee, vids, labs = [0], [0], [], [], [], [], [], []
+    for g in gallery_videos:
+        T = int(g["feat"].shape[1])
+        s, e, lo, hi = clip_grid(g["activitynet_duration"], T, fps, temporal_stride, clip_sec)
+        t0.append(t0[-1] + T), ws.append(ws[-1] + len(s))
+        los.append(lo), his.append(hi), ss.append(s), ee.append(e)
+        labs.extend(cal_label((int(a), int(b)), g["annotations"], possible_classes) for a, b in zip(s, e))
+        vids.extend([g["video_id"]] * len(s))
+    feats = [g["feat"] for g in gallery_videos]
+    if feats and type(feats[0]).__module__.startswith("torch"):
+        import torch
+        cat = torch.cat(feats, dim=1).contiguous()
+    else:
+        cat = np.ascontiguousarray(np.concatenate(feats, axis=1), dtype=np.float32)
+    out = ops.window_means(cat, t0, ws, np.concatenate(los).astype(np.int32), np.concatenate(his).astype(np.int32))
+    return dict(feat=out, video_id=vids, loc_sec=np.stack([np.concatenate(ss), np.concatenate(ee)], 1), clip_label=labs,
+                seg_start=np.asarray(ws, np.int64))
 
 
 def closest_hits(start_sec, end_sec, annotations, possible_classes):
