@@ -51,6 +51,7 @@ def parse():
     ap.add_argument("--d", type=int, default=512)
     ap.add_argument("--k", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the 64-query oracle check of the full-size result")
     ap.add_argument("--no-aux", action="store_true", help="skip the cfg-1 mAP-eval and cfg-2 loss side measurements")
     return ap.parse_args()
 
@@ -174,6 +175,39 @@ def cpu_sample(a, steps, warmup):
     return nq_s * n_s / dt, cores, sample, dt * 1e3
 
 
+def parity_subsample(torch, a, Dm, Im, nsub=64):
+    """Outside the timed region: a subsample of the queries of the FULL-size result (after the merge when N > 1)
+    against the CPU oracle.  The gallery is regenerated block by block (1 Mi rows, the same seeded generator every
+    sharding uses), each block searched by the oracle (canonical d2 to every row of the block, exact top-k), the
+    per-block lists merged by the oracle's merge.  Indices exact, distances bit-equal."""
+    import numpy as np
+    from oracle import oracle as orc
+    t0 = time.perf_counter()
+    orc.set_num_threads(int(os.environ.get("VQ_CPU_THREADS", "0")) or len(os.sched_getaffinity(0)))
+    rs = np.random.RandomState(12345)
+    sub = np.sort(rs.choice(a.nq, min(nsub, a.nq), replace=False))
+    dev = Dm.device
+    xq = gen_rows(torch, "q", 0, a.nq, a.d, dev)[torch.from_numpy(sub).to(dev)].float().cpu().numpy()
+    k = a.k
+    parts_d, parts_i = [], []
+    for b0 in range(0, a.n, BLOCK_ROWS):
+        b1 = min(a.n, b0 + BLOCK_ROWS)
+        blk = gen_rows(torch, "g", b0, b1, a.d, dev).float().cpu().numpy()
+        kk = min(k, b1 - b0)
+        d_, i_ = orc.search(xq, blk, kk)
+        d_ = np.pad(d_, ((0, 0), (0, k - kk)), constant_values=np.inf)
+        i_ = np.pad(i_, ((0, 0), (0, k - kk)), constant_values=-1)
+        parts_d.append(d_)
+        parts_i.append(np.where(i_ >= 0, i_ + b0, i_))
+        del blk
+    Do, Io = orc.topk_merge(np.stack(parts_d), np.stack(parts_i))
+    sel = torch.from_numpy(sub).to(dev)
+    Dg, Ig = Dm[sel].cpu().numpy(), Im[sel].cpu().numpy()
+    ok = bool(np.array_equal(Ig, Io) and np.array_equal(Dg.view(np.uint32), np.asarray(Do, np.float32).view(np.uint32)))
+    return {"queries": int(len(sub)), "ok": ok, "checked": "top-%d rows exact + d2 bit-equal vs the CPU oracle over all %d gallery rows"
+            % (k, a.n), "mismatching_queries": int((Ig != Io).any(axis=1).sum()), "seconds": time.perf_counter() - t0}
+
+
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -201,9 +235,16 @@ def aux_measurements(torch, vq):
     out = {}
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            peaks_hbm = json.load(f).get("hbm_gbs")
+            pk = json.load(f)
+        peaks_hbm, peaks_tc = pk.get("hbm_gbs"), pk.get("bf16_tflops")
     except (OSError, ValueError):
-        peaks_hbm = None
+        peaks_hbm, peaks_tc = None, None
+    peaks_tc = peaks_tc or 1590.0
+
+    def tc_roof(flops, ms, note):
+        ach = flops / (ms * 1e-3) / 1e12
+        return {"bound": "tensor", "achieved": ach, "peak": peaks_tc, "unit": "TFLOP/s", "frac": ach / peaks_tc,
+                "algorithmic_flops": flops, "note": note}
     # configs[0]: trimmed retrieval eval, 4096 x 20480 x 512 f32, full-list AP + R@N
     rng = np.random.default_rng(0)
     n, nq, d = 20480, 4096, 512
@@ -231,7 +272,11 @@ def aux_measurements(torch, vq):
         ts.append(time.perf_counter() - t0)
     out["map_eval_cfg0"] = {"workload": "configs[0]: 4096 queries x 20480 gallery x 512-d f32, full-list AP + R@30/50/100",
                             "wall_ms": min(ts[1:]) * 1e3, "mAP": float(ap.double().mean().item()),
-                            "pairs_per_s": nq * n / min(ts[1:])}
+                            "pairs_per_s": nq * n / min(ts[1:]),
+                            "roofline": tc_roof(2.0 * nq * n * d, min(ts[1:]) * 1e3,
+                                                "2*Q*N*D against the burst bf16 peak as SURVEY.md 8d scores it; the evaluator "
+                                                "scores every pair with the canonical fp32 chain on the packed FFMA2/FADD2 "
+                                                "CUDA-core pipes (DESIGN.md 4.4 says why not tensor cores)")}
     # the same evaluation by the CPU port (oracle, all host threads) on a bounded sample of the queries
     try:
         from oracle import oracle as orc
@@ -284,7 +329,7 @@ def aux_measurements(torch, vq):
     # configs[2]: untrimmed moment retrieval, 4096 queries x 20480 videos x 64 moments, 512-d f32: segment
     # max-pool + top-100 videos (tensor cores) and the full moment evaluation (rank all, per-video NMS, AP, R@N)
     try:
-        out.update(aux_moment(torch, vq))
+        out.update(aux_moment(torch, vq, tc_roof=tc_roof))
     except Exception as e:  # noqa: BLE001 -- a side measurement must not lose the headline line
         out["moment_cfg2_error"] = repr(e)
     # f1: sliding-moment pooling (garner_feat) at untrimmed-gallery scale, HBM-bound
@@ -382,7 +427,7 @@ def sharded_map_eval(torch, dist, vq, ops, dev, G):
             "timing": "CUDA events, max over ranks, best of 3 after 1 warm-up"}
 
 
-def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
+def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512, tc_roof=None):
     import numpy as np
     dev, n, out = "cuda", V * S, {}
     gen = torch.Generator(device=dev).manual_seed(0)
@@ -422,7 +467,11 @@ def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
     tm = ix.last_timing()
     out["segmax_cfg2"] = {"workload": "configs[2]: %d queries x %d videos x %d moments x %d-d f32, per-video max + top-100 videos"
                           % (nq, V, S, d), "wall_ms": t * 1e3, "pairs_per_s": nq * n / t,
-                          "gemm_topk_ms": tm["gemm_topk_ms"], "tflops_algorithmic": 2.0 * nq * n * d / tm["gemm_topk_ms"] / 1e9}
+                          "gemm_topk_ms": tm["gemm_topk_ms"], "select_ms": tm["select_ms"],
+                          "tflops_algorithmic": 2.0 * nq * n * d / tm["gemm_topk_ms"] / 1e9}
+    if tc_roof:
+        out["segmax_cfg2"]["roofline"] = tc_roof(2.0 * nq * n * d, tm["gemm_topk_ms"], "SEGMAX GEMM launch alone; 3-pass split-bf16 "
+                                                 "issues 3x these flops")
     # the same gallery held in bf16 (north_star's bf16-input mode): CTA-pair kernel, one MMA pass
     ixb = vq.IndexFlatL2(d)
     ixb.add(torch.cat([ix_rows.to(torch.bfloat16) for ix_rows in gsrc]))
@@ -431,7 +480,10 @@ def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
     t, _ = wall(lambda: ixb.search_segmax(qb, 100), 3)
     tm = ixb.last_timing()
     out["segmax_cfg2_bf16"] = {"workload": "configs[2] with bf16 gallery and queries", "wall_ms": t * 1e3, "pairs_per_s": nq * n / t,
-                               "gemm_topk_ms": tm["gemm_topk_ms"], "tflops_algorithmic": 2.0 * nq * n * d / tm["gemm_topk_ms"] / 1e9}
+                               "gemm_topk_ms": tm["gemm_topk_ms"], "select_ms": tm["select_ms"],
+                               "tflops_algorithmic": 2.0 * nq * n * d / tm["gemm_topk_ms"] / 1e9}
+    if tc_roof:
+        out["segmax_cfg2_bf16"]["roofline"] = tc_roof(2.0 * nq * n * d, tm["gemm_topk_ms"], "SEGMAX GEMM launch alone (CTA-pair kernel)")
     del ixb, gsrc
     t, r = wall(lambda: ix.eval_moment(q, ql, ign), 2)
     cpu = None
@@ -450,6 +502,9 @@ def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512):
     out["moment_eval_cfg2"] = {"cpu_port": cpu,"workload": "configs[2]: full moment evaluation (rank all %d moments per query, per-video NMS, "
                                "AP@tIoU0.5, grouped R@30/50/100), %d queries" % (n, nq), "wall_ms": t * 1e3,
                                "ms_per_query": t * 1e3 / nq, "pairs_per_s": nq * n / t, "mAP": float(r[0].mean().item())}
+    if tc_roof:
+        out["moment_eval_cfg2"]["roofline"] = tc_roof(2.0 * nq * n * d, t * 1e3, "whole evaluation (canonical scores on FFMA2/FADD2 + "
+                                                      "per-video NMS + AP) against the tensor peak, as SURVEY.md 8d scores it")
     return out
 
 
@@ -499,11 +554,13 @@ def run_b200(a):
     D = torch.empty((a.nq, k), dtype=torch.float32, device=dev)
     I = torch.empty((a.nq, k), dtype=torch.int64, device=dev)
 
+    xevents = []
+
     def step_device():
         index.search(xq, k, out=(D, I))
         if G == 1:
             return D, I
-        return ops.exchange_merge(D, I, r0)
+        return ops.exchange_merge(D, I, r0, events=xevents)
 
     xq_host = torch.empty(xq.shape, dtype=torch.bfloat16, pin_memory=True)
     xq_host.copy_(xq)
@@ -560,11 +617,27 @@ def run_b200(a):
         phase_ms.append(t)
 
     sampler = ClockSampler(local) if rank == 0 else None
+    del xevents[:]
     total_ms, t0, t1 = timed(step_device, a.steps, collect)
     clocks = sampler.stop(t0, t1) if sampler else None
+    xphase = None
+    if G > 1 and xevents:   # this rank's exchange phases (CUDA events around pack / all-gather / merge), mean over the steps
+        ev = [xevents[i:i + 4] for i in range(0, len(xevents) - 3, 4)]
+        xphase = {nm: sum(e[j].elapsed_time(e[j + 1]) for e in ev) / len(ev)
+                  for j, nm in enumerate(("pack_ms", "allgather_ms", "merge_ms"))}
+        # allgather_ms on one rank includes waiting for the slowest rank's GEMM (rank skew); max - min over ranks shows it
+        tt = torch.tensor([xphase["allgather_ms"], -xphase["allgather_ms"]], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        xphase["allgather_ms_max_over_ranks"], xphase["allgather_ms_min_over_ranks"] = float(tt[0].item()), -float(tt[1].item())
     stats = index.last_stats()
     out = step_device()
     checksum = int((out[1].sum() % (1 << 61)).item())
+    parity = None
+    if rank == 0 and not a.no_parity:
+        try:
+            parity = parity_subsample(torch, a, out[0], out[1])
+        except Exception as e:  # noqa: BLE001 -- reported, never hidden
+            parity = {"queries": 0, "ok": False, "error": repr(e)}
 
     for _ in range(max(1, min(a.warmup, 2))):
         step_e2e()
@@ -594,12 +667,13 @@ def run_b200(a):
         peak, which = peaks["bf16_tflops"], "MEASURED_PEAKS.json bf16_tflops (burst)"
     else:
         peak, which = 1590.0, "fallback 1.59 PFLOP/s (B200_PROFILING.md)"
-    traffic = None
-    try:
-        with open(os.path.join(ROOT, "profiles", "gemm_topk_traffic.json")) as f:
-            traffic = json.load(f).get("dram_bytes_per_launch")
-    except (OSError, ValueError):
-        pass
+    traffic = None   # ncu dram bytes of ONE launch of this exact workload; measured at N = 1 only (a shard's launch differs)
+    if G == 1 and (a.nq, a.n, a.d, a.k) == (100_000, 10_000_000, 512, 100):
+        try:
+            with open(os.path.join(ROOT, "profiles", "gemm_topk_traffic.json")) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        except (OSError, ValueError):
+            pass
 
     line = {
         "metric": "query-gallery pairs/sec (512-d)", "value": value, "unit": "pairs/s", "n_gpus": G,
@@ -613,13 +687,15 @@ def run_b200(a):
         "e2e": {"value": e2e_value, "unit": "pairs/s", "h2d_bytes_per_step": a.nq * a.d * 2,
                 "d2h_bytes_per_step": a.nq * k * 12, "ms_per_step": e2e_ms / a.steps,
                 "gemm_topk_ms": sum(e2e_gemm_ms) / len(e2e_gemm_ms)},
-        "gpu_launches": (stats["launches"] + (1 if G > 1 else 0)) * a.steps,
+        "gpu_launches": (stats["launches"] + (2 if G > 1 else 0)) * a.steps,   # + topk_pack and topk_merge_keys at N > 1
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
                      "traffic": traffic, "kernel": "gemm_topk_pair_kernel<false> (cta_group::2)", "kernel_ms": g_ms,
                      "algorithmic_flops_per_launch": flops, "peak_source": which},
         "phases_ms": {kk: sum(p[kk] for p in phase_ms) / len(phase_ms) for kk in phase_ms[0]},
-        "search_stats": stats, "result_checksum": checksum, "clocks": clocks,
+        "search_stats": stats, "result_checksum": checksum, "clocks": clocks, "parity_subsample": parity,
     }
+    if xphase:
+        line["phases_ms"].update(xphase)
     if add_info:
         line["index_add"] = add_info
 

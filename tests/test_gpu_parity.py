@@ -603,6 +603,24 @@ def test_topk_merge(vq):
     assert np.array_equal(oi, wi) and np.array_equal(od.view(np.uint32), wd.view(np.uint32))
 
 
+def test_topk_merge_unsorted_lists_take_the_sort_path(vq):
+    """The merge ranks sorted lists; a caller's unsorted lists are detected and sorted instead."""
+    rng = np.random.default_rng(13)
+    G, nq, k = 3, 17, 60
+    d2 = rng.random((G, nq, k)).astype(np.float32)            # NOT sorted
+    idx = rng.permutation(G * nq * k).reshape(G, nq, k).astype(np.int64)
+    idx[1, :, ::7] = -1                                        # holes anywhere
+    od, oi = vq.topk_merge(d2, idx)
+    wd, wi = orc.topk_merge(d2, idx)
+    assert np.array_equal(oi, wi) and np.array_equal(od.view(np.uint32), wd.view(np.uint32))
+    # few valid entries: the tail is padded
+    idx[:] = -1
+    idx[0, :, :5] = np.arange(5)
+    d2[0, :, :5] = np.sort(d2[0, :, :5], axis=1)
+    od, oi = vq.topk_merge(d2, idx)
+    assert (oi[:, :5] == np.arange(5)).all() and (oi[:, 5:] == -1).all() and np.isinf(od[:, 5:]).all()
+
+
 def test_topk_pack_merge_keys(vq):
     """The packed exchange (one 8-byte key per entry) gives what topk_merge gives on (d2, global row) lists."""
     rng = np.random.default_rng(12)

@@ -126,6 +126,23 @@ def _worker(rank, world, port, tmp):
                                 merge=lambda a, b: orc.topk_merge(a.numpy(), b.numpy()))
     Do, Io = orc.search(q, g, k)
     ok = np.array_equal(Im, Io) and np.array_equal(np.asarray(Dm).view(np.uint32), Do.view(np.uint32))
+
+    class LocalIndex:                               # stand-in for the per-rank IndexFlatL2 (local rows)
+        ntotal = r1 - r0
+
+        def search(self, xq, kq):
+            return D, np.where(I >= 0, I - r0, I)
+
+    omerge = lambda a, b: orc.topk_merge(a.numpy(), b.numpy())  # noqa: E731
+    Ds, Is = ops.sharded_search(LocalIndex(), torch.from_numpy(q), k, r0, merge=omerge)
+    ok = ok and np.array_equal(Is, Io) and np.array_equal(np.asarray(Ds).view(np.uint32), Do.view(np.uint32))
+    # more than 2^32 rows in total: EVERY rank refuses (the branch is taken on the all-reduced global count; a per-rank
+    # test would send rank 0 and rank 1 into different collectives)
+    try:
+        ops.sharded_search(LocalIndex(), torch.from_numpy(q), k, (1 << 32) - 10 if rank == world - 1 else r0, merge=omerge)
+        ok = False
+    except ValueError:
+        pass
     # query-sharded evaluation: per-rank slice -> one all-gather of [ap, R@30, R@50, R@100] rows
     gl_, gv_ = rng.integers(0, 9, n).astype(np.int32), (np.arange(n) // 3).astype(np.int32)
     ql_, qi_ = rng.integers(0, 9, nq).astype(np.int32), rng.integers(0, n // 3, (nq, 5)).astype(np.int32)

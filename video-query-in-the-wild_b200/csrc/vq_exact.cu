@@ -15,18 +15,25 @@ namespace vq {
 // ---------------------------------------------------------------------------------------
 static constexpr int AT = 64, AK = 32, APAD = 4;
 
+// Packed fp32x2 canonical step (sm_100a FADD2 / FFMA2): two independent chains per instruction, each lane rounded
+// exactly as the scalar __fsub_rn / __fmaf_rn pair (no FTZ) -- same bits as canon_step, half the issue slots.
+__device__ __forceinline__ unsigned long long canon_step2(unsigned long long acc, unsigned long long q2, unsigned long long g2) {
+    unsigned long long df, r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(df) : "l"(q2), "l"(g2));
+    asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(r) : "l"(df), "l"(acc));
+    return r;
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) l2sq_all_kernel(const T *__restrict__ q, const T *__restrict__ g,
                                                        int64_t nq, int64_t n, int d, float *__restrict__ out) {
-    __shared__ __align__(16) float sQ[AK][AT + APAD];
+    __shared__ __align__(16) float2 sQ[AK][AT + APAD];  // every query value twice: the {q, q} operand of a packed step
     __shared__ __align__(16) float sG[AK][AT + APAD];
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
     const int64_t q0 = (int64_t)blockIdx.y * AT, g0 = (int64_t)blockIdx.x * AT;
-    float acc[4][4];
+    unsigned long long acc[4][2];  // [query a][gallery pair]: {acc(a, 2p), acc(a, 2p+1)}
 #pragma unroll
-    for (int a = 0; a < 4; ++a)
-#pragma unroll
-        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+    for (int a = 0; a < 4; ++a) acc[a][0] = acc[a][1] = 0ull;
     const int lr = tid >> 2, lk = (tid & 3) * 8;  // loader: row lr, 8 consecutive k
     // The next k-block's values are fetched into registers while this one is being multiplied (the global latency
     // used to sit between the two barriers of every step); the tile columns are XOR-swizzled by the k-group so that
@@ -46,7 +53,7 @@ __global__ void __launch_bounds__(256) l2sq_all_kernel(const T *__restrict__ q, 
         __syncthreads();
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-            sQ[lk + e][lr ^ sw_st] = rq[e];
+            sQ[lk + e][lr ^ sw_st] = make_float2(rq[e], rq[e]);
             sG[lk + e][lr ^ sw_st] = rg[e];
         }
         __syncthreads();
@@ -54,23 +61,30 @@ __global__ void __launch_bounds__(256) l2sq_all_kernel(const T *__restrict__ q, 
 #pragma unroll
         for (int kk = 0; kk < AK; ++kk) {
             const int sw = (kk >> 3) << 3;
-            const float4 a4 = *reinterpret_cast<const float4 *>(&sQ[kk][(ty * 4) ^ sw]);
-            const float4 b4 = *reinterpret_cast<const float4 *>(&sG[kk][(tx * 4) ^ sw]);
-            const float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+            const ulonglong2 qa = *reinterpret_cast<const ulonglong2 *>(&sQ[kk][(ty * 4) ^ sw]);
+            const ulonglong2 qb = *reinterpret_cast<const ulonglong2 *>(&sQ[kk][((ty * 4) ^ sw) + 2]);
+            const ulonglong2 b2 = *reinterpret_cast<const ulonglong2 *>(&sG[kk][(tx * 4) ^ sw]);
+            const unsigned long long qv[4] = {qa.x, qa.y, qb.x, qb.y};
 #pragma unroll
-            for (int a = 0; a < 4; ++a)
-#pragma unroll
-                for (int b = 0; b < 4; ++b) acc[a][b] = canon_step(acc[a][b], av[a], bv[b]);
+            for (int a = 0; a < 4; ++a) {
+                acc[a][0] = canon_step2(acc[a][0], qv[a], b2.x);
+                acc[a][1] = canon_step2(acc[a][1], qv[a], b2.y);
+            }
         }
     }
 #pragma unroll
     for (int a = 0; a < 4; ++a) {
         const int64_t qi = q0 + ty * 4 + a;
         if (qi >= nq) continue;
+        const float r[4] = {__uint_as_float((uint32_t)acc[a][0]), __uint_as_float((uint32_t)(acc[a][0] >> 32)),
+                            __uint_as_float((uint32_t)acc[a][1]), __uint_as_float((uint32_t)(acc[a][1] >> 32))};
+        const int64_t gi0 = g0 + tx * 4;
+        if (gi0 + 3 < n && ((qi * n + gi0) & 3) == 0) {
+            *reinterpret_cast<float4 *>(out + qi * n + gi0) = make_float4(r[0], r[1], r[2], r[3]);
+        } else {
 #pragma unroll
-        for (int b = 0; b < 4; ++b) {
-            const int64_t gi = g0 + tx * 4 + b;
-            if (gi < n) out[qi * n + gi] = acc[a][b];
+            for (int b = 0; b < 4; ++b)
+                if (gi0 + b < n) out[qi * n + gi0 + b] = r[b];
         }
     }
 }

@@ -54,34 +54,65 @@ def topk_merge_keys(keys):
     return od, oi
 
 
-def exchange_merge(D, I, row_offset, group=None):
+def exchange_merge(D, I, row_offset, group=None, events=None):
     """The exchange step of the row-sharded search on CUDA tensors: pack the local list (LOCAL rows I, this rank's
     first global row ``row_offset``), ONE all-gather of the 8-byte keys, merge.  Same result as
-    ``merge_gathered(D, I + row_offset)``, a third fewer bytes and one collective instead of two."""
+    ``merge_gathered(D, I + row_offset)``, a third fewer bytes and one collective instead of two.
+    ``events``: a list that receives four CUDA events (start, packed, gathered, merged) for phase timing."""
     import torch
     import torch.distributed as dist
     ws = dist.get_world_size(group)
     nq, k = D.shape
+
+    def mark():
+        if events is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            events.append(e)
+
+    mark()
     keys = topk_pack(D.contiguous(), I.contiguous(), row_offset)
+    mark()
     gk = torch.empty((ws * nq, k), dtype=torch.int64, device=D.device)
     dist.all_gather_into_tensor(gk, keys, group=group)
-    return topk_merge_keys(gk.view(ws, nq, k))
+    mark()
+    out = topk_merge_keys(gk.view(ws, nq, k))
+    mark()
+    return out
 
 
-def sharded_search(index, xq, k, row_offset, group=None):
+MAX_GLOBAL_ROWS = 1 << 32   # merge keys carry the global row in 32 bits
+
+
+def check_global_rows(n_global):
+    """The exchange (packed or not) merges on 8-byte (d2, global row) keys: galleries of more than 2^32 rows are
+    refused instead of silently truncated.  The decision uses the GLOBAL row count, so every rank takes the same
+    branch (a per-rank test could issue different collectives on either side of the limit and hang)."""
+    if int(n_global) > MAX_GLOBAL_ROWS:
+        raise ValueError("row-sharded search supports at most 2^32 gallery rows in total, got %d" % int(n_global))
+
+
+def sharded_search(index, xq, k, row_offset, group=None, n_global=None, merge=None):
     """Row-sharded gallery: every rank searches its shard (`index` holds rows
     [row_offset, row_offset + ntotal) of the global gallery), the per-rank top-k lists are
     exchanged with ONE all-gather and merged on every rank.  xq: CUDA tensor (NCCL) or CPU
-    tensor / numpy (gloo tests call `merge_gathered` with an oracle-made local list)."""
+    tensor / numpy (gloo tests call `merge_gathered` with an oracle-made local list).
+    ``n_global``: total rows over all ranks; when omitted it is all-reduced (max of row_offset + ntotal)."""
     import torch
     import torch.distributed as dist
+    if n_global is None:
+        t = torch.tensor([int(row_offset) + int(index.ntotal)], dtype=torch.int64,
+                         device=xq.device if getattr(xq, "is_cuda", False) else "cpu")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+        n_global = int(t.item())
+    check_global_rows(n_global)
     D, I = index.search(xq, k)
     D = torch.as_tensor(D)
     I = torch.as_tensor(I)
-    if D.is_cuda and int(row_offset) + int(index.ntotal) <= 1 << 32:   # packed keys carry the global row in 32 bits
+    if D.is_cuda:
         return exchange_merge(D, I, row_offset, group)
     I = torch.where(I >= 0, I + int(row_offset), I)
-    return merge_gathered(D, I, group)
+    return merge_gathered(D, I, group, merge)
 
 
 def merge_gathered(D, I, group=None, merge=None):
