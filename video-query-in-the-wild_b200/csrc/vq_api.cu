@@ -18,13 +18,14 @@ static int *hook_slot(const char *name) {
     struct { const char *n; int *p; } tab[] = {
         {"FORCE_FALLBACK", &g_hooks.force_fallback}, {"NO_PAIR", &g_hooks.no_pair}, {"NO_CHAIN", &g_hooks.no_chain},
         {"DENSE_ROWS", &g_hooks.dense_rows}, {"NO_TC_TRIPLET", &g_hooks.no_tc_triplet},
-        {"TRIPLET_CLOCKS", &g_hooks.triplet_clocks}, {"NO_TC_EVAL", &g_hooks.no_tc_eval}};
+        {"TRIPLET_CLOCKS", &g_hooks.triplet_clocks}, {"NO_TC_EVAL", &g_hooks.no_tc_eval},
+        {"NO_INSERT", &g_hooks.no_insert}, {"KPRIME", &g_hooks.kprime}, {"TRIGGER", &g_hooks.trigger}};
     for (auto &t : tab)
         if (!strcmp(name, t.n)) return t.p;
     return nullptr;
 }
 static const bool g_hooks_from_env = [] {
-    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL"}) {
+    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER"}) {
         char env[64];
         snprintf(env, sizeof(env), "VQ_DEBUG_%s", n);
         if (const char *e = getenv(env)) *hook_slot(n) = atoi(e);
@@ -240,6 +241,7 @@ struct vq_index {
     size_t cand_bytes = 0;
     int32_t *cand_cnt = nullptr;
     float *cand_tau = nullptr;
+    int32_t *cand_cum = nullptr;
     size_t cand_units = 0;
     int64_t *plan_rows_dev = nullptr;  // segment plan of the last search (GemmTopkParams)
     size_t plan_rows_cap = 0;
@@ -309,7 +311,7 @@ int vq_index_destroy(vq_index *ix) {
     cudaDeviceSynchronize();
     void *ptrs[] = {ix->raw,   ix->hi,         ix->lo,           ix->norm2,    ix->gmax_bits,
                     ix->label, ix->video,      ix->seg_of_row,   ix->seg_start_dev, ix->cand,     ix->cand_cnt,
-                    ix->cand_tau, ix->plan_rows_dev, ix->plan_ints_dev, ix->unproven, ix->unproven_count,
+                    ix->cand_tau, ix->cand_cum, ix->plan_rows_dev, ix->plan_ints_dev, ix->unproven, ix->unproven_count,
                     ix->m_start, ix->m_end, ix->m_iou, ix->m_hit, ix->seg_small, ix->seg_large};
     for (void *p : ptrs)
         if (p) cudaFree(p);

@@ -135,7 +135,8 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
         ix->stats[1] = 0; ix->stats[2] = 0; ix->stats[3] = 0; ix->stats[4] = 0; ix->stats[5] = 1;
         return VQ_OK;
     }
-    const int kprime = choose_kprime(k, prec, dtype);
+    int kprime = choose_kprime(k, prec, dtype);
+    if (g_hooks.kprime >= k && g_hooks.kprime <= kMaxKPrime) kprime = (g_hooks.kprime + 7) / 8 * 8;  // A/B hook
     VQ_CHECK(k <= kprime, VQ_ERR_CAPACITY, "k=%d exceeds the streaming top-k limit %d", k, kMaxKPrime);
     // bf16 single pass with dim <= 512 runs on CTA pairs (resident queries, split gallery tiles)
     const bool pair = prec != VQ_PREC_SPLIT3 && ix->dp <= 512 && !g_hooks.no_pair;
@@ -174,9 +175,10 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     VQ_CUDA(cudaMemcpyAsync(ix->plan_ints_dev, pl.ints.data(), pl.ints.size() * 4, cudaMemcpyHostToDevice, st));
     VQ_TRY(ensure(&ix->cand, &ix->cand_bytes, units * kTileM * kCandCap));
     if (ix->cand_units < units) {
-        if (ix->cand_cnt) { VQ_CUDA(cudaDeviceSynchronize()); cudaFree(ix->cand_cnt); cudaFree(ix->cand_tau); }
+        if (ix->cand_cnt) { VQ_CUDA(cudaDeviceSynchronize()); cudaFree(ix->cand_cnt); cudaFree(ix->cand_tau); cudaFree(ix->cand_cum); }
         VQ_CUDA(cudaMalloc(&ix->cand_cnt, units * kTileM * 4));
         VQ_CUDA(cudaMalloc(&ix->cand_tau, units * kTileM * 4));
+        VQ_CUDA(cudaMalloc(&ix->cand_cum, units * kTileM * 4));
         ix->cand_units = units;
     }
     VQ_TRY(ensure(&ix->unproven, &ix->unproven_cap, (size_t)nq));
@@ -191,9 +193,11 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     gp.col_video = n_ign > 0 ? ix->video : nullptr;
     gp.col_seg = segmax ? ix->seg_of_row : nullptr;
     gp.q_ignore = n_ign > 0 ? ign : nullptr; gp.n_ign = n_ign; gp.kprime = kprime;
+    gp.dbg_no_insert = g_hooks.no_insert;
+    gp.trigger = g_hooks.trigger;
     gp.dense_rows = 4;  // measured: scripts/ab_gemm.py, profiles/r01_ab_gemm_chain_dense.txt
     if (g_hooks.dense_rows >= 0) gp.dense_rows = g_hooks.dense_rows;  // A/B hook (33 = never)
-    gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau;
+    gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau; gp.cand_cum = ix->cand_cum;
     VQ_CUDA(cudaEventRecord(ix->ev[1], st));
     if (pair) {
         VQ_TRY(launch_gemm_topk_pair(maps, gp, segmax, pl.n_cta, st));
@@ -207,7 +211,7 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     sp.nq = nq; sp.n = ix->n; sp.d = ix->d; sp.dtype = dtype; sp.q = xq; sp.g = ix->raw;
     sp.group_size = group_size; sp.group_segs = ix->plan_ints_dev + 2 * pl.nseg + pl.n_cta + 1;
     sp.segs_per_group = pl.n_chunks; sp.cand = ix->cand; sp.cand_cnt = ix->cand_cnt;
-    sp.cand_tau = ix->cand_tau; sp.kprime = kprime; sp.k = k;
+    sp.cand_tau = ix->cand_tau; sp.cand_cum = ix->cand_cum; sp.kprime = kprime; sp.k = k;
     error_model(prec, ix->dtype, ix->dp, &sp.eps_rel, &sp.eps_abs);
     sp.gmax_norm2_bits = ix->gmax_bits;
     sp.seg_of_row = segmax ? ix->seg_of_row : nullptr;

@@ -31,6 +31,9 @@ namespace vq {
 static constexpr int BM = kTileM, BN = kTileN, BK = 64;
 static constexpr int kEpiThreads = 128;
 static constexpr int kThreads = 64 + kEpiThreads;
+static constexpr int kOwnerSlots = 8;    // scratch rows per epilogue warp (owners handled per pass)
+static constexpr int kOwnerStride = 36;  // floats per scratch row: 128 B + 16 B pad, so the eight rows cover all banks
+static constexpr int kScrBytes = 4 * kOwnerSlots * kOwnerStride * 4;  // four epilogue warps
 static constexpr int A_BYTES = BM * BK * 2;  // 16 KB
 static constexpr int B_BYTES = BN * BK * 2;  // 32 KB
 
@@ -39,8 +42,8 @@ struct SmemLayout {
     static constexpr int NPLANE = NPASS == 1 ? 1 : 2;
     static constexpr int STAGE_BYTES = NPLANE * (A_BYTES + B_BYTES);
     static constexpr int STAGES = NPASS == 1 ? 4 : 2;
-    static constexpr int OFF_SCR = STAGES * STAGE_BYTES;           // float[4][32] per-warp transpose scratch
-    static constexpr int OFF_IGN = OFF_SCR + 4 * 32 * 4;           // int[BM][kMaxIgnore]
+    static constexpr int OFF_SCR = STAGES * STAGE_BYTES;           // float[4 warps][kOwnerSlots][kOwnerStride] owner scratch rows
+    static constexpr int OFF_IGN = OFF_SCR + kScrBytes;            // int[BM][kMaxIgnore]
     static constexpr int OFF_BAR = OFF_IGN + BM * kMaxIgnore * 4;  // mbarriers
     static constexpr int NBAR = 2 * STAGES + 4;
     static constexpr int OFF_TMEM = OFF_BAR + NBAR * 8;
@@ -54,7 +57,7 @@ struct PairLayout {
     static constexpr int STAGES = 4;
     static constexpr int OFF_B = (KB_MAX + 1) * A_BYTES;     // 144 KB
     static constexpr int OFF_SCR = OFF_B + STAGES * BH_BYTES;
-    static constexpr int OFF_IGN = OFF_SCR + 4 * 32 * 4;
+    static constexpr int OFF_IGN = OFF_SCR + kScrBytes;
     static constexpr int OFF_BAR = OFF_IGN + BM * kMaxIgnore * 4;
     // full[S] empty[S] tfull[2] tempty[2] afull aempty
     static constexpr int NBAR = 2 * STAGES + 6;
@@ -83,19 +86,34 @@ __device__ __forceinline__ int compact_row(uint64_t *buf, int cnt, int kprime, i
         lo[i] = (uint32_t)e;
     }
     __syncwarp();
-    uint32_t T = 0;
-    int cT = cnt;  // #{hi >= T}
+    // Bisection of the VALUE interval [smallest, largest] of the listed scores (ordered-uint images) instead of the 32 key
+    // bits: the scores of one row sit in a narrow band, so bit-by-bit descent spent ~10 rounds on the bits they all
+    // share; the interval version lands in the [k', keep_max] window after 3-6 rounds and still ends at the exact k'-th
+    // largest when it has to (hi_ - lo == 1).
+    uint32_t mx = 0u, mn = 0xffffffffu;
+#pragma unroll
+    for (int i = 0; i < E; ++i) {
+        const bool valid = (i * 32 + lane) < cnt;
+        mx = valid && hi[i] > mx ? hi[i] : mx;
+        mn = valid && hi[i] < mn ? hi[i] : mn;
+    }
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    uint32_t T = mn;      // #{hi >= T} >= kprime holds throughout
+    uint32_t hi_ = mx == 0xffffffffu ? mx : mx + 1u;  // #{hi >= hi_} < kprime (NaN-pattern keys excepted: they are kept)
+    int cT = cnt;         // #{hi >= T}; the padding slots hold 0 and are never >= a midpoint
 #pragma unroll 1
-    for (int bit = 31; bit >= 0; --bit) {
-        const uint32_t cand = T | (1u << bit);
+    while (hi_ - T > 1u && cT > keep_max) {
+        const uint32_t mid = T + ((hi_ - T) >> 1);
         int c = 0;
 #pragma unroll
-        for (int i = 0; i < E; ++i) c += (hi[i] >= cand) ? 1 : 0;
+        for (int i = 0; i < E; ++i) c += (hi[i] >= mid) ? 1 : 0;
         c = __reduce_add_sync(0xffffffffu, c);
         if (c >= kprime) {
-            T = cand;
+            T = mid;
             cT = c;
-            if (c <= keep_max) break;
+        } else {
+            hi_ = mid;
         }
     }
     const uint32_t lt_mask = (1u << lane) - 1u;
@@ -158,7 +176,7 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
     const int row = quarter * 32 + lane;     // accumulator row == query row in the block
     const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
     const uint32_t lt_mask = (1u << lane) - 1u;
-    float *wscr = scr + quarter * 32;
+    float *wscr = scr + quarter * (kOwnerSlots * kOwnerStride);  // this warp's owner scratch rows
     int as = 0;
     uint32_t aphase = 0;
     for (int sg_i = s0; sg_i < s1; ++sg_i) {
@@ -175,16 +193,38 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
         // tau: everything discarded so far has coarse score <= tau; tauh = tau / 2 is what the
         // accumulator (= score / 2) is compared with
         float tau = qvalid ? -INFINITY : INFINITY;
-        {   // start from the predecessor segment's final threshold if it has been published (NaN = not yet):
-            // everything it discarded or still lists below its k'-th entry is <= that value
+        int cnt = 0;
+        int cum = 1;  // this unit's list covers every earlier gallery chunk of the row as well
+        {   // CONTINUE the predecessor segment (same query rows, previous gallery chunk) if it has been published
+            // (tau NaN = not yet): take over its final threshold AND its final list, so the row's stream goes on as
+            // if the chunk boundary were not there -- the next compaction tightens tau after k' new candidates instead
+            // of the list having to refill from empty -- and the select kernel reads ONE list per query.
             const int pr = p.seg_pred[sg_i];
             if (pr >= 0 && qvalid) {
-                const float t0 = *(const volatile float *)(p.cand_tau + ((int64_t)(PAIR ? 2 * pr + rank : pr) * BM + row));
-                if (t0 == t0) tau = t0;
+                cum = 0;
+                const int64_t pu = (int64_t)(PAIR ? 2 * pr + rank : pr) * BM + row;
+                const float t0 = *(const volatile float *)(p.cand_tau + pu);
+                if (t0 == t0) tau = t0;  // everything the predecessor discarded is <= its final threshold
+                // its list is taken over only if it covers all earlier chunks itself: a list that continued a
+                // non-cumulative one would be read by the select kernel TOGETHER with the lists it contains
+                if (t0 == t0 && *(const volatile int32_t *)(p.cand_cum + pu) != 0) {
+                    __threadfence();  // the list, its count and its flag were written before tau was published
+                    cum = 1;
+                    const int pc = min(*(const volatile int32_t *)(p.cand_cnt + pu), p.kprime);
+                    const uint64_t *src = p.cand + pu * kCandCap;
+                    for (int i0 = 0; i0 < pc; i0 += 8) {
+                        uint64_t e[8];
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) e[i] = i0 + i < pc ? __ldcg(src + i0 + i) : 0ull;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i)
+                            if (i0 + i < pc) buf[i0 + i] = e[i];
+                    }
+                    cnt = pc;
+                }
             }
         }
         float tauh = 0.5f * tau;
-        int cnt = 0;
         // group-max state (SEGMAX), in accumulator (half-score) units
         int cur_seg = -2;
         float cur_maxh = -INFINITY;
@@ -223,8 +263,7 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
         // Intermediate compactions are cheap (few registers, early-exit bisection) and fire
         // often so that tau stays close to the k'-th best seen so far.  A 32-column step can add
         // at most 33 entries, hence the cap.
-        const int dense_rows = p.n_ign > 0 ? 33 : p.dense_rows;  // the per-thread scan does not apply the ignore rule
-        const int trigger = min(2 * p.kprime, kCandCap - 64);
+        const int trigger = p.trigger > 0 ? min(p.trigger, kCandCap - 64) : min(2 * p.kprime, kCandCap - 64);
         const int keep_max = min(p.kprime + p.kprime / 2, trigger - 32);
         for (int t = 0; t < ntiles; ++t) {
             mbar_wait(&tfull_bar[as], aphase);
@@ -305,41 +344,38 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                     if (need) compact_rows(need, keep_max);
                 } else {
                     uint32_t bal = __ballot_sync(0xffffffffu, m32 > tauh);
-                    if (__popc(bal) >= dense_rows) {
-                        // many rows hold candidates in this step (threshold warm-up at the start of a
-                        // segment, or a gallery row that is close to every query): every thread scans
-                        // its own 32 values -- predicated, no per-row serialisation through the warp
-                        const uint32_t jlow = ~(jbase + (uint32_t)(ch * 32));  // key low word = ~row
-#pragma unroll
-                        for (int i = 0; i < 32; ++i) {
-                            if (v[i] > tauh) {
-                                buf[cnt] = ((uint64_t)f32_to_ordered(2.0f * v[i]) << 32) | (uint64_t)(jlow - (uint32_t)i);
-                                ++cnt;
-                            }
-                        }
-                        const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
-                        if (need) compact_rows(need, keep_max);
-                    } else if (bal) {  // warp-uniform; rare once tau has warmed up
-                        while (bal) {
-                            const int L = __ffs(bal) - 1;
-                            bal &= bal - 1;
-                            if (lane == L) {
+                    if (p.dbg_no_insert) bal = 0u;  // timing probe only (results are wrong): the kernel without candidate handling
+                    if (bal) {  // warp-uniform
+                        // Rows that hold a candidate in these 32 columns ("owners") handle themselves, all at once: an
+                        // owner parks its 32 values in a scratch row of its own, forms the hit mask from its registers
+                        // (straight-line compares) and appends the hits to its own list, reading them back by index.
+                        // No cross-lane traffic, no barrier, no per-row serialisation: a step with events costs the
+                        // same ~120 instructions whether one row or eight rows hit (the first version passed one row at
+                        // a time through the warp -- transpose, shuffles, ballot: ~500 cycles per row on a warp that is
+                        // alone on its scheduler; ncu source view, profiles/r02_ncu_gemm_topk_n8shape_source.txt).
+                        const bool owner = (bal >> lane) & 1u;
+                        const int pos = __popc(bal & lt_mask);  // this owner's ordinal
+                        const int nown = __popc(bal);
+                        for (int base = 0; base < nown; base += kOwnerSlots) {  // warp-uniform trip count
+                            if (owner && pos >= base && pos < base + kOwnerSlots) {
+                                float *my = wscr + (pos - base) * kOwnerStride;
 #pragma unroll
                                 for (int i = 0; i < 8; ++i)
-                                    *reinterpret_cast<float4 *>(wscr + 4 * i) =
-                                        make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                                    *reinterpret_cast<float4 *>(my + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                                uint32_t hm = 0u;
+#pragma unroll
+                                for (int i = 0; i < 32; ++i) hm |= v[i] > tauh ? (1u << i) : 0u;
+                                const uint32_t jb = jbase + (uint32_t)(ch * 32);
+                                while (hm) {
+                                    const int i = __ffs(hm) - 1;
+                                    hm &= hm - 1;
+                                    const uint32_t j = jb + (uint32_t)i;
+                                    if (p.n_ign > 0 && is_ignored(row, __ldg(p.col_video + j))) continue;
+                                    buf[cnt] = make_key_desc(2.0f * my[i], j);
+                                    ++cnt;
+                                }
                             }
-                            __syncwarp();
-                            const float x = wscr[lane];  // row L, column ch*32 + lane
-                            const float tL = __shfl_sync(0xffffffffu, tauh, L);
-                            const int cL = __shfl_sync(0xffffffffu, cnt, L);
-                            const uint32_t j = jbase + (uint32_t)(ch * 32 + lane);
-                            bool hit = x > tL;
-                            if (hit && p.n_ign > 0) hit = !is_ignored(quarter * 32 + L, __ldg(p.col_video + j));
-                            const uint32_t hm = __ballot_sync(0xffffffffu, hit);
-                            if (hit) wbuf[(int64_t)L * kCandCap + cL + __popc(hm & lt_mask)] = make_key_desc(2.0f * x, j);
-                            if (lane == L) cnt += __popc(hm);
-                            __syncwarp();  // scratch is reused by the next row
+                            if (nown > kOwnerSlots) __syncwarp();  // the scratch rows change hands between passes
                         }
                         const uint32_t need = __ballot_sync(0xffffffffu, cnt > trigger);
                         if (need) compact_rows(need, keep_max);
@@ -358,7 +394,10 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
         // final compaction of this unit to exactly <= k' entries per row
         compact_rows(__ballot_sync(0xffffffffu, cnt > p.kprime), p.kprime);
         p.cand_cnt[(int64_t)u * BM + row] = qvalid ? cnt : 0;
-        p.cand_tau[(int64_t)u * BM + row] = tau;
+        p.cand_cum[(int64_t)u * BM + row] = cum;
+        __syncwarp();     // the row's entries were written by the whole warp (appends, compactions) ...
+        __threadfence();  // ... and are visible device-wide before the threshold that publishes them
+        *(volatile float *)(p.cand_tau + (int64_t)u * BM + row) = tau;
     }
 }
 

@@ -10,7 +10,7 @@ namespace vq {
 // loaded and changed afterwards only through vq_debug_set() -- never getenv() on a search path.
 struct DebugHooks {
     int force_fallback = 0, no_pair = 0, no_chain = 0, dense_rows = -1, no_tc_triplet = 0, triplet_clocks = 0,
-        no_tc_eval = 0;
+        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0;
 };
 extern DebugHooks g_hooks;
 
@@ -47,11 +47,14 @@ struct GemmTopkParams {
     const int32_t *q_ignore;     // device [nq, n_ign] or null
     int n_ign;
     int kprime;
+    int dbg_no_insert;  // debug hook NO_INSERT
+    int trigger;        // list fill level that triggers an intermediate compaction (0: 2 k')
     int dense_rows;  // rows of a warp with candidates in one 32-column step from which every thread scans its own row
     // unit = (segment, query block inside the group): u = seg * group_size + member
     uint64_t *cand;   // [units][kTileM][kCandCap] keys (ordered coarse score << 32 | ~row)
     int32_t *cand_cnt;  // [units][kTileM]
     float *cand_tau;    // [units][kTileM] everything not listed has coarse score <= tau (NaN until the unit is done)
+    int32_t *cand_cum;  // [units][kTileM] 1: the list continues the predecessor's (it covers all earlier chunks of the row)
 };
 
 int launch_gemm_topk(const CUtensorMap *maps4, const GemmTopkParams &p, int npass, bool segmax,
@@ -87,6 +90,7 @@ struct SelectParams {
     const uint64_t *cand;
     const int32_t *cand_cnt;
     const float *cand_tau;
+    const int32_t *cand_cum;     // 1: the unit's list already covers every earlier segment of the row (vq_gemm_topk.cu)
     int kprime, k;
     float eps_rel, eps_abs;      // |coarse - (|q|^2 - d2)| <= eps_rel*|q|*gmax + eps_abs
     const uint32_t *gmax_norm2_bits;

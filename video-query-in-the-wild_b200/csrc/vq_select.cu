@@ -48,12 +48,23 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
     // ---- 1. gather: per-segment counts first, then one flattened copy with independent loads (the lists of the
     // later segments are nearly empty once tau has tightened, so the compacted total is a small multiple of k') ----
     for (int i = tid; i < p.d; i += kSelThreads) qs[i] = to_f32<T>(qrow[i]);
-    float tau = -INFINITY;
+    // A segment whose list CONTINUED its predecessor's (cand_cum, vq_gemm_topk.cu) already holds the best k' of every
+    // earlier gallery chunk: only the segments from the last such one on are read -- normally just the final one.
+    __shared__ int s_first;
+    if (tid == 0) s_first = 0;
+    __syncthreads();
     for (int c = tid; c < nsg; c += kSelThreads) {
         const int64_t ur = ((int64_t)segs[c] * p.group_size + member) * kTileM + r;
-        cnts[c] = min(p.cand_cnt[ur], p.kprime);
         urs[c] = ur;
-        tau = fmaxf(tau, p.cand_tau[ur]);
+        if (c > 0 && p.cand_cum[ur]) atomicMax(&s_first, c);
+    }
+    __syncthreads();
+    const int first = s_first;
+    float tau = -INFINITY;
+    for (int c = tid; c < nsg; c += kSelThreads) {
+        const int64_t ur = urs[c];
+        cnts[c] = c >= first ? min(p.cand_cnt[ur], p.kprime) : 0;
+        if (c >= first) tau = fmaxf(tau, p.cand_tau[ur]);
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) tau = fmaxf(tau, __shfl_xor_sync(0xffffffffu, tau, o));
