@@ -432,6 +432,33 @@ def test_eval_trimmed_random_with_ties(vq):
     assert np.array_equal(top, topo)
 
 
+def test_eval_trimmed_many_exact_ties_near_the_top(vq):
+    """Galleries with blocks of EXACT duplicate rows: tie groups of 40 and of 300 positives right at the top of the
+    list (R@N must count positions inside the tie by gallery row; the 300-group overflows the kernel's tie queue)."""
+    rng = np.random.default_rng(21)
+    n, d, nq = 3000, 64, 12
+    g = _emb(rng, n, d)
+    label = rng.integers(0, 6, n).astype(np.int32)
+    g[100:140] = g[100]
+    label[100:140] = 2
+    g[1000:1300] = g[1000]
+    label[1000:1300] = 3
+    label[1100:1150] = 4                       # non-positives inside the duplicate block
+    video = np.arange(n, dtype=np.int32)
+    q = _emb(rng, nq, d)
+    q[0], q[1], q[2] = g[100], g[1000], g[1000] + 1e-3
+    ql = np.array([2, 3, 3] + [int(x) for x in rng.integers(0, 6, nq - 3)], np.int32)
+    ign = np.stack([rng.integers(0, n, nq), np.full(nq, 1005)], 1).astype(np.int32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    ix.set_meta(label, video)
+    ap, rec, top = ix.eval_trimmed(q, ql, ign, want_top=True)
+    apo, reco, topo, _ = orc.eval_trimmed(q, g, label, video, ql, ign)
+    np.testing.assert_allclose(ap, apo, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-12)
+    assert np.array_equal(top, topo)
+
+
 def test_average_precision_lists_golden(vq, golden):
     yts, yss, want = [], [], []
     off = 0

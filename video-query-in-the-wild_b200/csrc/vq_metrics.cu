@@ -87,6 +87,7 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
         misc[0] = 0;
         misc[1] = 0;
         misc[2] = 0;
+        misc[4] = 0;
         last_key[0] = 0ull;
         last_key[1] = 0ull;
         topn[0] = topn[1] = topn[2] = 0;
@@ -302,27 +303,59 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
         }
     }
     // ---- R@N: exact rank of every TRUE positive under the (d2, row) order ----
+    // A positive whose d2 is shared by other survivors (float32 collisions are common: ~n^2 / 2^23 pairs per row)
+    // needs #{survivors with equal d2 and row <= mine}.  Those positives are queued and each one is resolved by the
+    // WHOLE block in one sweep of the row (the first version let the owning thread walk the row alone: up to n
+    // dependent loads in one thread, ~1 ms for a 20 480-row gallery, hit by every second query).
+    int *tie_n = misc + 4;
     for (int i = tid; !MOMENT && i < npos; i += kApThreads) {
         const uint64_t key = pos[i];
         if (!last_is_true && key == lastk) continue;  // the forced one is not a true positive
         const int g = gstart[i];
-        const int lt = cntA[g + 1] - cntE[g];  // survivors strictly ahead by d2
-        int rank;
         if (cntE[g] == 1) {
-            rank = lt + 1;
-        } else {  // exact ties: count survivors with equal d2 and row <= mine (rare)
+            const int rank = cntA[g + 1];  // survivors strictly ahead by d2, plus itself
+            if (rank <= 30) atomicAdd(&topn[0], 1);
+            if (rank <= 50) atomicAdd(&topn[1], 1);
+            if (rank <= 100) atomicAdd(&topn[2], 1);
+        } else if (cntA[g + 1] - cntE[g] < 100) {  // it can still rank inside the first 100
+            const int slot = atomicAdd(tie_n, 1);
+            if (slot < 128) {
+                tcnt[slot] = i;  // (tcnt / tv are free in the trimmed mode)
+            } else {  // > 128 tied positives near the top (a gallery of exact duplicates): walk the row alone
+                const uint32_t s = (uint32_t)(key >> 32), myrow = (uint32_t)key;
+                int c = 0;
+                for (int64_t j = 0; j <= myrow; ++j)
+                    if (f32_to_ordered(row[j]) == s && !(n_ign && is_ignored(p.g_video[j], ign, n_ign))) ++c;
+                const int rank = cntA[g + 1] - cntE[g] + c;
+                if (rank <= 30) atomicAdd(&topn[0], 1);
+                if (rank <= 50) atomicAdd(&topn[1], 1);
+                if (rank <= 100) atomicAdd(&topn[2], 1);
+            }
+        }
+    }
+    __syncthreads();
+    if (!MOMENT) {
+        const int nt = min(*tie_n, 128);
+        // more than 128 tied positives inside the first 100 ranks cannot happen: each takes a distinct rank
+        for (int t = 0; t < nt; ++t) {
+            const int i = tcnt[t];
+            const uint64_t key = pos[i];
+            const int g = gstart[i];
             const uint32_t s = (uint32_t)(key >> 32), myrow = (uint32_t)key;
             int c = 0;
-            for (int64_t j = 0; j <= myrow; ++j) {
+            for (int64_t j = tid; j <= myrow; j += kApThreads) {
                 if (f32_to_ordered(row[j]) != s) continue;
                 if (n_ign && is_ignored(p.g_video[j], ign, n_ign)) continue;
                 ++c;
             }
-            rank = lt + c;
+            c = block_sum(c, part);
+            if (tid == 0) {
+                const int rank = cntA[g + 1] - cntE[g] + c;
+                if (rank <= 30) atomicAdd(&topn[0], 1);
+                if (rank <= 50) atomicAdd(&topn[1], 1);
+                if (rank <= 100) atomicAdd(&topn[2], 1);
+            }
         }
-        if (rank <= 30) atomicAdd(&topn[0], 1);
-        if (rank <= 50) atomicAdd(&topn[1], 1);
-        if (rank <= 100) atomicAdd(&topn[2], 1);
     }
     __syncthreads();
     if (tid == 0) {
