@@ -101,6 +101,16 @@ VQ_API int vq_index_search(vq_index *ix, const void *xq, int64_t nq, int dtype, 
                            const int32_t *ignore_video, int n_ignore, float *D, int64_t *I,
                            void *stream);
 
+/* Workspace of the k <= 512 search path (candidate lists, work plan).  It belongs to the index and is grown on demand,
+ * stream-ordered on the caller's stream from the library's own memory pool (no device synchronisation);
+ * vq_index_search_workspace_bytes reports what a search of nq queries would need -- persistent_bytes stay with the
+ * index, transient_bytes are stream-ordered temporaries of one call -- and vq_index_reserve grows the persistent part
+ * ahead of time, after which searches of up to that shape allocate nothing but the temporaries.  Calls on one index
+ * must be ordered with respect to each other (same stream, or synchronised): they share this workspace. */
+VQ_API int vq_index_search_workspace_bytes(vq_index *ix, int64_t nq, int64_t k, int segmax, int64_t *persistent_bytes,
+                                           int64_t *transient_bytes);
+VQ_API int vq_index_reserve(vq_index *ix, int64_t nq, int64_t k, int segmax, void *stream);
+
 /* configs[2]: per (query, video) best moment (segment max-pool) and the top-k videos.
  * Outputs [nq,k]: video id (int64), arg-best gallery row (int64), its canonical d2. */
 VQ_API int vq_index_search_segmax(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k,

@@ -157,6 +157,11 @@ def test_memory_logits_golden_and_oracle(gl, torch):
     mem = torch.from_numpy(gl["ml_mem"]).cuda()
     logits = memory_logits(x, mem, float(gl["ml_temp"]))
     (logits * torch.from_numpy(gl["ml_w"]).cuda()).sum().backward()
+    # Tolerances, stated: north_star's 1e-6 absolute is for loss VALUES of order 1.  These logits are
+    # -dist / temperature with temperature 0.1: |logit| ~ 14, where ONE fp32 ulp is 9.5e-7, and the reference itself
+    # (torch, fp32) sums the 512 squared differences in an unspecified order (relative noise ~ sqrt(512) * 2^-24 = 1.4e-6).
+    # 2e-5 absolute = 1.4e-6 relative = that noise; the float64 oracle comparison below carries the same fp32 budget
+    # once more for the kernel's own rounding (1e-4 absolute = 7e-6 relative).
     np.testing.assert_allclose(logits.detach().cpu().numpy(), gl["ml_logits"], rtol=0, atol=2e-5)
     np.testing.assert_allclose(x.grad.cpu().numpy(), gl["ml_gx"], rtol=0, atol=2e-5)
     # VA head shapes: batch 64 x 512-d vs 200 visual memory slots; VASA word space 1024-d; memory with grad

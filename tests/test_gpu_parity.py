@@ -136,6 +136,27 @@ def test_search_with_ignore_and_device_tensors(vq):
         assert np.array_equal(D[a].view(np.uint32), Do[a][keep][:k].view(np.uint32))
 
 
+def test_workspace_query_and_reserve(vq):
+    """SURVEY.md 8b convention: the workspace a search needs can be asked for and reserved up front."""
+    import torch
+    rng = np.random.default_rng(40)
+    q, g = _emb(rng, 300, 128), _emb(rng, 5000, 128)
+    ix = vq.IndexFlatL2(128)
+    ix.add(g)
+    pers, trans = ix.workspace_bytes(300, 100)
+    assert pers > 0 and trans > 0
+    ix.reserve(300, 100)
+    torch.cuda.synchronize()
+    before = torch.cuda.mem_get_info()[0]
+    D, I = ix.search(q, 100)
+    torch.cuda.synchronize()
+    after = torch.cuda.mem_get_info()[0]
+    assert before - after <= trans + (32 << 20)   # nothing persistent was added by the search (pool granularity aside)
+    Do, Io = orc.search(q, g, 100)
+    assert np.array_equal(I, Io) and np.array_equal(D.view(np.uint32), Do.view(np.uint32))
+    assert ix.workspace_bytes(4, 5000)[0] == 0      # k > 512: the full-sort path only uses stream-ordered temporaries
+
+
 def test_search_forced_fallback_path(vq):
     rng = np.random.default_rng(4)
     q, g = _emb(rng, 40, 128), _emb(rng, 3000, 128)

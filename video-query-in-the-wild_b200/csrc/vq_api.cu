@@ -242,7 +242,7 @@ struct vq_index {
     int32_t *cand_cnt = nullptr;
     float *cand_tau = nullptr;
     int32_t *cand_cum = nullptr;
-    size_t cand_units = 0;
+    size_t cand_cnt_cap = 0, cand_tau_cap = 0, cand_cum_cap = 0;
     int64_t *plan_rows_dev = nullptr;  // segment plan of the last search (GemmTopkParams)
     size_t plan_rows_cap = 0;
     int32_t *plan_ints_dev = nullptr;

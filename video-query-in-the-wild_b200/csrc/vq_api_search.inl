@@ -99,21 +99,64 @@ static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int k
     pl->ints.insert(pl->ints.end(), gsegs.begin(), gsegs.end());
 }
 
+// Search workspace of an index (candidate lists, plan, ...): owned by the index, grown on demand on the CALLER's
+// stream from the library's pool -- stream-ordered (cudaFreeAsync of the old block, cudaMallocFromPoolAsync of the new
+// one), so growing never synchronises the device.  vq_index_reserve() sizes it ahead of time.
 template <typename T>
-static int ensure(T **p, size_t *cap, size_t need) {
+static int ensure(T **p, size_t *cap, size_t need, cudaStream_t st) {
     if (*cap >= need) return VQ_OK;
     if (*p) {
-        VQ_CUDA(cudaDeviceSynchronize());
-        cudaFree(*p);
+        VQ_CUDA(cudaFreeAsync(*p, st));
         *p = nullptr;
         *cap = 0;
     }
-    if (cudaMalloc(p, need * sizeof(T)) != cudaSuccess) {
+    cudaMemPool_t pool = nullptr;
+    VQ_TRY(scratch_pool(&pool));
+    if (cudaMallocFromPoolAsync((void **)p, need * sizeof(T), pool, st) != cudaSuccess) {
         cudaGetLastError();
         set_error("out of device memory for a %zu-byte workspace", need * sizeof(T));
         return VQ_ERR_NOMEM;
     }
     *cap = need;
+    return VQ_OK;
+}
+
+// Host-side planning of one tensor-core search: everything search_core needs to size its buffers.
+struct SearchPlan {
+    int prec = 0, kprime = 0, n_qblocks = 0, group_size = 1, n_groups = 0, slots = 0;
+    bool pair = false, split = false;
+    SegPlan pl;
+    size_t units = 0;
+    // bytes: persistent workspace of the index | stream-ordered temporaries of the call
+    size_t persistent_bytes() const {
+        return pl.rows.size() * 8 + pl.ints.size() * 4 + units * kTileM * kCandCap * 8 + units * kTileM * 4 * 3;
+    }
+};
+
+static void make_search_plan(const vq_index *ix, int64_t nq, int dtype, int k, bool segmax, SearchPlan *sp) {
+    sp->prec = resolve_prec(ix);
+    sp->kprime = choose_kprime(k, sp->prec, dtype);
+    if (g_hooks.kprime >= k && g_hooks.kprime <= kMaxKPrime) sp->kprime = (g_hooks.kprime + 7) / 8 * 8;  // A/B hook
+    sp->split = sp->prec == VQ_PREC_SPLIT3;
+    // bf16 single pass with dim <= 512 runs on CTA pairs (resident queries, split gallery tiles)
+    sp->pair = !sp->split && ix->dp <= 512 && !g_hooks.no_pair;
+    sp->n_qblocks = (int)((nq + kTileM - 1) / kTileM);
+    if (sp->pair) sp->n_qblocks = (sp->n_qblocks + 1) / 2 * 2;  // the pad block is all out of range
+    sp->group_size = sp->pair ? 2 : 1;
+    sp->n_groups = sp->n_qblocks / sp->group_size;
+    sp->slots = sp->pair ? gemm_topk_pair_slots() : sm_count();
+    plan_segments(ix, sp->n_groups, sp->slots, sp->kprime, segmax, &sp->pl);
+    sp->units = (size_t)sp->pl.nseg * sp->group_size;
+}
+
+static int ensure_workspace(vq_index *ix, const SearchPlan &sp, int64_t nq, cudaStream_t st) {
+    VQ_TRY(ensure(&ix->plan_rows_dev, &ix->plan_rows_cap, sp.pl.rows.size(), st));
+    VQ_TRY(ensure(&ix->plan_ints_dev, &ix->plan_ints_cap, sp.pl.ints.size(), st));
+    VQ_TRY(ensure(&ix->cand, &ix->cand_bytes, sp.units * kTileM * kCandCap, st));
+    VQ_TRY(ensure(&ix->cand_cnt, &ix->cand_cnt_cap, sp.units * kTileM, st));
+    VQ_TRY(ensure(&ix->cand_tau, &ix->cand_tau_cap, sp.units * kTileM, st));
+    VQ_TRY(ensure(&ix->cand_cum, &ix->cand_cum_cap, sp.units * kTileM, st));
+    VQ_TRY(ensure(&ix->unproven, &ix->unproven_cap, (size_t)nq, st));
     return VQ_OK;
 }
 
@@ -135,17 +178,19 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
         ix->stats[1] = 0; ix->stats[2] = 0; ix->stats[3] = 0; ix->stats[4] = 0; ix->stats[5] = 1;
         return VQ_OK;
     }
-    int kprime = choose_kprime(k, prec, dtype);
-    if (g_hooks.kprime >= k && g_hooks.kprime <= kMaxKPrime) kprime = (g_hooks.kprime + 7) / 8 * 8;  // A/B hook
+    SearchPlan spn;
+    make_search_plan(ix, nq, dtype, k, segmax, &spn);
+    const int kprime = spn.kprime;
     VQ_CHECK(k <= kprime, VQ_ERR_CAPACITY, "k=%d exceeds the streaming top-k limit %d", k, kMaxKPrime);
-    // bf16 single pass with dim <= 512 runs on CTA pairs (resident queries, split gallery tiles)
-    const bool pair = prec != VQ_PREC_SPLIT3 && ix->dp <= 512 && !g_hooks.no_pair;
+    const bool pair = spn.pair, split = spn.split;
+    const SegPlan &pl = spn.pl;
+    const int n_qblocks = spn.n_qblocks, group_size = spn.group_size;
+    const size_t units = spn.units;
     // query operand planes
     Tmp qhi, qlo;
     ix->ev_valid = false;
     VQ_CUDA(cudaEventRecord(ix->ev[0], st));
     VQ_TRY(qhi.alloc((size_t)nq * ix->dpa * 2, st));
-    const bool split = prec == VQ_PREC_SPLIT3;
     if (split) VQ_TRY(qlo.alloc((size_t)nq * ix->dpa * 2, st));
     VQ_TRY(launch_prepare_rows(xq, dtype, nq, ix->d, ix->dp, true, (__nv_bfloat16 *)qhi.p,
                                split ? (__nv_bfloat16 *)qlo.p : nullptr, nullptr, nullptr, st));
@@ -160,28 +205,9 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
         VQ_TRY(make_map(&maps[2], ix->hi, ix->n, ix->dpa, kTileN));
         VQ_TRY(make_map(&maps[3], split ? (void *)ix->lo : (void *)ix->hi, ix->n, ix->dpa, kTileN));
     }
-    // work decomposition (pair path: query blocks padded to an even count, the pad block is all out of range)
-    int n_qblocks = (int)((nq + kTileM - 1) / kTileM);
-    if (pair) n_qblocks = (n_qblocks + 1) / 2 * 2;
-    const int group_size = pair ? 2 : 1;
-    const int n_groups = n_qblocks / group_size;
-    const int slots = pair ? gemm_topk_pair_slots() : sm_count();
-    SegPlan pl;
-    plan_segments(ix, n_groups, slots, kprime, segmax, &pl);
-    const size_t units = (size_t)pl.nseg * group_size;
-    VQ_TRY(ensure(&ix->plan_rows_dev, &ix->plan_rows_cap, pl.rows.size()));
-    VQ_TRY(ensure(&ix->plan_ints_dev, &ix->plan_ints_cap, pl.ints.size()));
+    VQ_TRY(ensure_workspace(ix, spn, nq, st));
     VQ_CUDA(cudaMemcpyAsync(ix->plan_rows_dev, pl.rows.data(), pl.rows.size() * 8, cudaMemcpyHostToDevice, st));
     VQ_CUDA(cudaMemcpyAsync(ix->plan_ints_dev, pl.ints.data(), pl.ints.size() * 4, cudaMemcpyHostToDevice, st));
-    VQ_TRY(ensure(&ix->cand, &ix->cand_bytes, units * kTileM * kCandCap));
-    if (ix->cand_units < units) {
-        if (ix->cand_cnt) { VQ_CUDA(cudaDeviceSynchronize()); cudaFree(ix->cand_cnt); cudaFree(ix->cand_tau); cudaFree(ix->cand_cum); }
-        VQ_CUDA(cudaMalloc(&ix->cand_cnt, units * kTileM * 4));
-        VQ_CUDA(cudaMalloc(&ix->cand_tau, units * kTileM * 4));
-        VQ_CUDA(cudaMalloc(&ix->cand_cum, units * kTileM * 4));
-        ix->cand_units = units;
-    }
-    VQ_TRY(ensure(&ix->unproven, &ix->unproven_cap, (size_t)nq));
 
     GemmTopkParams gp{};
     gp.nq = nq; gp.n = ix->n; gp.kb_count = ix->dp / 64; gp.n_qblocks = n_qblocks; gp.n_seg = pl.nseg;
@@ -326,6 +352,35 @@ int vq_index_search(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t
     VQ_TRY(oI.finish(st));
     if (oD.host || oI.host) VQ_CUDA(cudaStreamSynchronize(st));
     return VQ_OK;
+}
+
+int vq_index_search_workspace_bytes(vq_index *ix, int64_t nq, int64_t k, int segmax, int64_t *persistent_bytes,
+                                    int64_t *transient_bytes) {
+    VQ_CHECK(ix && persistent_bytes && transient_bytes, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(ix->n > 0, VQ_ERR_STATE, "empty index");
+    VQ_CHECK(nq >= 0 && k >= 1, VQ_ERR_INVALID, "bad sizes");
+    if (k > kMaxKPrime || resolve_prec(ix) == VQ_PREC_EXACT) {  // full-sort tiles / exact scan: stream-ordered temporaries only
+        int64_t tile_q = score_tile_bytes() / std::max<int64_t>(1, ix->n * 20);
+        tile_q = std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(std::max<int64_t>(nq, 1), tile_q), 32768));
+        *persistent_bytes = 0;
+        *transient_bytes = k > kMaxKPrime ? tile_q * ix->n * 20 + (int64_t)rowsort_hist_ints(tile_q, ix->n) * 4 : 0;
+        return VQ_OK;
+    }
+    SearchPlan sp;
+    make_search_plan(ix, nq, ix->dtype, (int)k, segmax != 0, &sp);
+    *persistent_bytes = (int64_t)sp.persistent_bytes() + nq * 4;
+    *transient_bytes = nq * ix->dpa * 2 * (sp.split ? 2 : 1);
+    return VQ_OK;
+}
+
+int vq_index_reserve(vq_index *ix, int64_t nq, int64_t k, int segmax, void *stream) {
+    VQ_CHECK(ix, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(ix->n > 0, VQ_ERR_STATE, "empty index");
+    VQ_CHECK(nq >= 1 && k >= 1, VQ_ERR_INVALID, "bad sizes");
+    if (k > kMaxKPrime || resolve_prec(ix) == VQ_PREC_EXACT) return VQ_OK;
+    SearchPlan sp;
+    make_search_plan(ix, nq, ix->dtype, (int)k, segmax != 0, &sp);
+    return ensure_workspace(ix, sp, nq, (cudaStream_t)stream);
 }
 
 int vq_index_search_segmax(vq_index *ix, const void *xq, int64_t nq, int dtype, int64_t k, int64_t *video,

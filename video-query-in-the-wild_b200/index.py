@@ -122,6 +122,18 @@ class IndexFlatL2:
                                              L.ptr(nk), L.ptr(km), L.stream_of(xq)))
         return ap, rec, nk, km
 
+    def workspace_bytes(self, nq, k, segmax=False):
+        """(persistent, transient) bytes a search of this shape needs (vq_index_search_workspace_bytes)."""
+        a, b = C.c_int64(), C.c_int64()
+        L.check(L.lib().vq_index_search_workspace_bytes(self._h, C.c_int64(int(nq)), C.c_int64(int(k)), C.c_int(int(segmax)),
+                                                        C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
+
+    def reserve(self, nq, k, segmax=False, stream=None):
+        """Grow the index's search workspace now, so that later searches of up to this shape allocate nothing."""
+        L.check(L.lib().vq_index_reserve(self._h, C.c_int64(int(nq)), C.c_int64(int(k)), C.c_int(int(segmax)),
+                                         C.c_void_p(0 if stream is None else int(stream))))
+
     def last_stats(self):
         out = (C.c_int64 * 6)()
         L.check(L.lib().vq_index_last_stats(self._h, out))
