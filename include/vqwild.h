@@ -255,6 +255,14 @@ VQ_API int vq_topk_pack(const float *d2, const int64_t *idx, int64_t count, int6
 VQ_API int vq_topk_merge_keys(const uint64_t *keys, int G, int64_t nq, int64_t k, float *out_d2,
                               int64_t *out_idx, void *stream);
 
+/* 8e, two-round form of the exchange: with G shards a query's global top-k takes ~k/G entries from each, so the ranks
+ * first all-gather only the first m < k keys of their (sorted) lists.  keys u64[G,nq,m] -> out [nq,k]; `incomplete`
+ * (int32[1], host or device) receives the number of queries whose merge is NOT final -- some shard's head ends before
+ * the merged k-th key, so it may hold better entries it has not sent -- in which case the caller repeats the exchange
+ * with the full lists (vq_topk_merge_keys).  0 incomplete queries = the result equals the full merge. */
+VQ_API int vq_topk_merge_heads(const uint64_t *keys, int G, int64_t nq, int64_t m, int64_t k, float *out_d2,
+                               int64_t *out_idx, int32_t *incomplete, void *stream);
+
 /* Canonical all-pairs squared L2 (CUDA cores), out f32[nq,n]; test / small-problem utility. */
 VQ_API int vq_l2sq(const float *q, const float *g, int64_t nq, int64_t n, int d, float *out,
                    void *stream);

@@ -27,6 +27,15 @@ full = vq.IndexFlatL2(d)
 full.add(g)
 Df, If = full.search(xq, k)
 ok = torch.equal(I, If) and torch.equal(D.view(torch.int32), Df.view(torch.int32))
+# the two-round (head) exchange, forced at this world size: final when complete, full round otherwise -- same answer
+from vqwild_b200 import ops
+Dl, Il = shard.search(xq, k)
+for head in (64, 8):   # 8: far too short -> incomplete -> the full round runs
+    ops._head_failed.clear()
+    Dh, Ih = ops.exchange_merge(Dl, Il, r0, head=head)
+    ok = ok and torch.equal(Ih, If) and torch.equal(Dh.view(torch.int32), Df.view(torch.int32))
+    if rank == 0:
+        print("head=%d: fell back to the full round: %s" % (head, bool(ops._head_failed)))
 flag = torch.tensor([1 if ok else 0], device=dev)
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:

@@ -685,6 +685,37 @@ def test_topk_pack_merge_keys(vq):
     assert np.array_equal(oi, wi) and np.array_equal(od.view(np.uint32), wd.view(np.uint32))
 
 
+def test_topk_merge_heads_two_round_exchange(vq):
+    """Round 1 of the exchange merges only the first m entries of every shard's list: final (and equal to the full merge)
+    when every head reaches the merged k-th key, reported incomplete otherwise."""
+    from vqwild_b200 import ops
+    rng = np.random.default_rng(14)
+    G, nq, k, m = 8, 50, 100, 40
+    assert ops.head_len(100, 8) == 40 and ops.head_len(100, 4) == 56 and ops.head_len(100, 2) == 100
+    d2 = np.sort(rng.random((G, nq, k)).astype(np.float32), axis=2)
+    local = np.stack([np.stack([np.sort(rng.choice(5000, k, replace=False)) for _ in range(nq)]) for _ in range(G)]).astype(np.int64)
+    local[3, :, 30:] = -1                            # a short list: its head ends inside the list
+    offs = np.arange(G) * 5000
+    keys = np.stack([vq.topk_pack(d2[g], local[g], offs[g]) for g in range(G)])
+    wd, wi = orc.topk_merge(d2, np.where(local >= 0, local + offs[:, None, None], -1))
+    od, oi, inc = ops.topk_merge_heads(np.ascontiguousarray(keys[:, :, :m]), k)
+    assert int(inc[0]) == 0
+    assert np.array_equal(oi, wi) and np.array_equal(od.view(np.uint32), wd.view(np.uint32))
+    # one shard holds most of a query's neighbours: its head is too short -> that query is reported
+    d2b = d2.copy()
+    d2b[5, 7] = np.sort(rng.random(k).astype(np.float32) * 1e-3)
+    d2b[2, 9] = np.sort(rng.random(k).astype(np.float32) * 1e-3)
+    keysb = np.stack([vq.topk_pack(d2b[g], local[g], offs[g]) for g in range(G)])
+    _, _, inc = ops.topk_merge_heads(np.ascontiguousarray(keysb[:, :, :m]), k)
+    assert int(inc[0]) == 2
+    # fewer than k entries in all
+    few = np.full((2, 3, 8), -1, np.int64)
+    few[0, :, :5] = np.arange(5)
+    kf = np.stack([vq.topk_pack(np.sort(rng.random((3, 8)).astype(np.float32), axis=1), few[g], 100 * g) for g in range(2)])
+    od, oi, inc = ops.topk_merge_heads(kf, 10)
+    assert int(inc[0]) == 0 and (oi[:, 5:] == -1).all() and (np.sort(oi[:, :5], axis=1) == np.arange(5)).all()
+
+
 def test_full_size_cfg1_properties(vq):
     """BASELINE configs[0] shape (4096 x 20480 x 512): oracle on a query subsample + properties."""
     rng = np.random.default_rng(10)

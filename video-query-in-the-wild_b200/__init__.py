@@ -15,7 +15,7 @@ def __getattr__(name):  # torch-dependent pieces are imported lazily
                 "memory_logits"):
         from . import loss
         return getattr(loss, name)
-    if name in ("pool_normalize", "topk_merge", "topk_pack", "topk_merge_keys", "exchange_merge", "l2sq", "sharded_search",
+    if name in ("pool_normalize", "topk_merge", "topk_pack", "topk_merge_keys", "topk_merge_heads", "exchange_merge", "l2sq", "sharded_search",
                 "window_means"):
         from . import ops
         return getattr(ops, name)

@@ -897,6 +897,27 @@ int vq_topk_merge_keys(const uint64_t *keys, int G, int64_t nq, int64_t k, float
     return VQ_OK;
 }
 
+int vq_topk_merge_heads(const uint64_t *keys, int G, int64_t nq, int64_t m, int64_t k, float *out_d2, int64_t *out_idx,
+                        int32_t *incomplete, void *stream) {
+    VQ_CHECK(keys && out_d2 && out_idx && incomplete, VQ_ERR_INVALID, "NULL argument");
+    VQ_CHECK(G >= 1 && nq >= 0 && m >= 1 && k >= 1 && (int64_t)G * m >= k, VQ_ERR_INVALID, "bad shape (G*m must reach k)");
+    VQ_TRY(check_device());
+    cudaStream_t st = (cudaStream_t)stream;
+    In a;
+    Out oD, oI, oC;
+    VQ_TRY(a.bind(keys, (size_t)G * nq * m * 8, st));
+    VQ_TRY(oD.bind(out_d2, (size_t)nq * k * 4, st));
+    VQ_TRY(oI.bind(out_idx, (size_t)nq * k * 8, st));
+    VQ_TRY(oC.bind(incomplete, 4, st));
+    VQ_CUDA(cudaMemsetAsync(oC.dev, 0, 4, st));
+    VQ_TRY(launch_topk_merge_heads(a.as<uint64_t>(), G, nq, (int)m, (int)k, oD.as<float>(), oI.as<int64_t>(), oC.as<int32_t>(), st));
+    VQ_TRY(oD.finish(st));
+    VQ_TRY(oI.finish(st));
+    VQ_TRY(oC.finish(st));
+    if (oD.host || oI.host || oC.host) VQ_CUDA(cudaStreamSynchronize(st));
+    return VQ_OK;
+}
+
 int vq_l2sq(const float *q, const float *g, int64_t nq, int64_t n, int d, float *out, void *stream) {
     VQ_CHECK(q && g && out, VQ_ERR_INVALID, "NULL argument");
     VQ_TRY(check_device());

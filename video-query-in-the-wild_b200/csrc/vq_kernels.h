@@ -202,6 +202,8 @@ int launch_nms1d(const double *dets, const int64_t *offsets, int64_t nseg, doubl
                  uint8_t *keep, uint8_t *dead_scratch, cudaStream_t st);
 int launch_topk_pack(const float *d2, const int64_t *idx, int64_t count, int64_t row_offset, uint64_t *keys, cudaStream_t st);
 int launch_topk_merge_keys(const uint64_t *keys, int G, int64_t nq, int64_t k, float *od, int64_t *oi, cudaStream_t st);
+int launch_topk_merge_heads(const uint64_t *keys, int G, int64_t nq, int m, int k, float *od, int64_t *oi, int32_t *incomplete,
+                            cudaStream_t st);
 int launch_topk_merge(const float *d2, const int64_t *idx, int G, int64_t nq, int64_t k, float *od,
                       int64_t *oi, cudaStream_t st);
 

@@ -640,6 +640,77 @@ __global__ void __launch_bounds__(128) topk_merge_keys_kernel(const uint64_t *__
     merge_sorted_lists(keys, G, (int)k, n2, q, od, oi);
 }
 
+// Head exchange (two rounds): with G shards a query's global top-k takes ~k/G entries from each shard, so
+// the ranks first exchange only the first m < k entries of their lists.  The merge of the G heads is FINAL for a query
+// when every head either ended inside its list (all-ones padding) or ends at / behind the merged k-th key: everything a
+// rank did not send is worse than its own last sent key.  Queries for which that fails are counted in `incomplete`; the
+// caller then falls back to the full exchange (ops.exchange_merge).  Heads that are not sorted count as incomplete.
+__global__ void __launch_bounds__(128) topk_merge_heads_kernel(const uint64_t *__restrict__ in, int G, int64_t nq, int m, int k,
+                                                               float *__restrict__ od, int64_t *__restrict__ oi,
+                                                               int32_t *__restrict__ incomplete) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint64_t *keys = (uint64_t *)sm;
+    __shared__ unsigned long long s_kth;
+    __shared__ int s_valid, s_bad;
+    const int64_t q = blockIdx.x;
+    const int total = G * m;
+    if (threadIdx.x == 0) {
+        s_kth = ~0ull;
+        s_valid = 0;
+        s_bad = 0;
+    }
+    for (int i = threadIdx.x; i < total; i += blockDim.x) keys[i] = in[((int64_t)(i / m) * nq + q) * m + (i % m)];
+    __syncthreads();
+    int bad = 0, valid_t = 0;
+    for (int e = threadIdx.x; e < total; e += blockDim.x) {
+        const uint64_t mine = keys[e];
+        const int g = e / m, i = e - g * m;
+        if (i + 1 < m && mine > keys[e + 1]) bad = 1;
+        if (mine == ~0ull) continue;
+        ++valid_t;
+        int rank = i;
+        for (int h = 0; h < G && rank < k; ++h) {
+            if (h == g) continue;
+            const uint64_t *lst = keys + h * m;
+            int lo = 0, hi = m;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (lst[mid] < mine) lo = mid + 1; else hi = mid;
+            }
+            rank += lo;
+        }
+        if (rank < k) {
+            od[q * k + rank] = ordered_to_f32((uint32_t)(mine >> 32));
+            oi[q * k + rank] = (int64_t)(uint32_t)mine;
+            if (rank == k - 1) s_kth = mine;
+        }
+    }
+    if (valid_t) atomicAdd(&s_valid, valid_t);
+    if (bad) s_bad = 1;
+    __syncthreads();
+    for (int i = s_valid + threadIdx.x; i < k; i += blockDim.x) {
+        od[q * k + i] = INFINITY;
+        oi[q * k + i] = -1;
+    }
+    if (threadIdx.x < G) {
+        const uint64_t last = keys[threadIdx.x * m + m - 1];
+        if (last != ~0ull && last < s_kth) s_bad = 1;  // this shard may hold better entries it has not sent
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && s_bad) atomicAdd(incomplete, 1);
+}
+
+int launch_topk_merge_heads(const uint64_t *keys, int G, int64_t nq, int m, int k, float *od, int64_t *oi, int32_t *incomplete,
+                            cudaStream_t st) {
+    if (nq == 0) return VQ_OK;
+    const size_t smem = (size_t)(G * m + 1) * 8;
+    VQ_CHECK(smem <= 200 * 1024 && G <= 128, VQ_ERR_CAPACITY, "topk_merge_heads: G*m=%lld too large", (long long)G * m);
+    VQ_CUDA(cudaFuncSetAttribute(topk_merge_heads_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    topk_merge_heads_kernel<<<(unsigned)nq, 128, smem, st>>>(keys, G, nq, m, k, od, oi, incomplete);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
 int launch_topk_pack(const float *d2, const int64_t *idx, int64_t count, int64_t row_offset, uint64_t *keys, cudaStream_t st) {
     if (count == 0) return VQ_OK;
     topk_pack_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(d2, idx, count, row_offset, keys);

@@ -54,11 +54,38 @@ def topk_merge_keys(keys):
     return od, oi
 
 
-def exchange_merge(D, I, row_offset, group=None, events=None):
-    """The exchange step of the row-sharded search on CUDA tensors: pack the local list (LOCAL rows I, this rank's
-    first global row ``row_offset``), ONE all-gather of the 8-byte keys, merge.  Same result as
-    ``merge_gathered(D, I + row_offset)``, a third fewer bytes and one collective instead of two.
-    ``events``: a list that receives four CUDA events (start, packed, gathered, merged) for phase timing."""
+def topk_merge_heads(keys, k):
+    """[G,nq,m] heads of the per-shard packed lists -> ([nq,k] d2, [nq,k] global rows, incomplete int32[1]); the result
+    is final iff ``incomplete`` is 0 (vq_topk_merge_heads)."""
+    G, nq, m = keys.shape
+    od = L.empty_like_kind(keys, (nq, k), np.float32)
+    oi = L.empty_like_kind(keys, (nq, k), np.int64)
+    inc = L.empty_like_kind(keys, (1,), np.int32)
+    L.check(L.lib().vq_topk_merge_heads(L.ptr(keys), C.c_int(G), C.c_int64(nq), C.c_int64(m), C.c_int64(k), L.ptr(od),
+                                        L.ptr(oi), L.ptr(inc), L.stream_of(keys)))
+    return od, oi, inc
+
+
+def head_len(k, ws):
+    """Entries of each shard's list sent in the first round: a query's global top-k takes Binomial(k, 1/ws) entries from a
+    shard of a randomly ordered gallery -- mean + 6 sigma + 4, rounded up to 8 (k = 100: 40 of 100 at 8 shards, 64 at 4);
+    k itself (single round) when that saves less than a third."""
+    mu = k / ws
+    m = int(-(-(mu + 6.0 * (k * (1.0 / ws) * (1.0 - 1.0 / ws)) ** 0.5 + 4.0) // 8) * 8)
+    return k if 3 * m > 2 * k else m
+
+
+_head_failed = {}   # (k, world size) -> the head round came back incomplete last time: skip it (gallery ordered by class, ...)
+
+
+def exchange_merge(D, I, row_offset, group=None, events=None, head=None):
+    """The exchange step of the row-sharded search on CUDA tensors.  Round 1: pack the first ``m`` entries of the local
+    list (LOCAL rows I, this rank's first global row ``row_offset``) into 8-byte keys, ONE all-gather, merge the heads
+    (``head_len``: 40 % of the bytes at 8 shards).  Every rank sees the same gathered heads, hence takes the same
+    decision: if some query's merge is not provably final (a shard's head ended before the merged k-th key), round 2
+    repeats the exchange with the full lists -- and later calls skip round 1.  Same result as
+    ``merge_gathered(D, I + row_offset)``.  ``events``: a list that receives four CUDA events (start, packed,
+    gathered, merged) for phase timing."""
     import torch
     import torch.distributed as dist
     ws = dist.get_world_size(group)
@@ -70,7 +97,22 @@ def exchange_merge(D, I, row_offset, group=None, events=None):
             e.record()
             events.append(e)
 
+    m = head_len(k, ws) if head is None else int(head)
     mark()
+    if m < k and not _head_failed.get((k, ws), False):
+        hk = topk_pack(D[:, :m].contiguous(), I[:, :m].contiguous(), row_offset)
+        mark()
+        gk = torch.empty((ws * nq, m), dtype=torch.int64, device=D.device)
+        dist.all_gather_into_tensor(gk, hk, group=group)
+        mark()
+        od, oi, inc = topk_merge_heads(gk.view(ws, nq, m), k)
+        mark()
+        if int(inc.item()) == 0:      # (one 4-byte read-back; identical on every rank)
+            return od, oi
+        _head_failed[(k, ws)] = True
+        if events is not None:
+            del events[-4:]
+            mark()
     keys = topk_pack(D.contiguous(), I.contiguous(), row_offset)
     mark()
     gk = torch.empty((ws * nq, k), dtype=torch.int64, device=D.device)
