@@ -30,7 +30,7 @@ ok = torch.equal(I, If) and torch.equal(D.view(torch.int32), Df.view(torch.int32
 # the two-round (head) exchange, forced at this world size: final when complete, full round otherwise -- same answer
 from vqwild_b200 import ops
 Dl, Il = shard.search(xq, k)
-for head in (64, 8):   # 8: far too short -> incomplete -> the full round runs
+for head in (80, 50):   # 50 = the mean share of a shard at 2 ranks: many heads too short -> the full round runs
     ops._head_failed.clear()
     Dh, Ih = ops.exchange_merge(Dl, Il, r0, head=head)
     ok = ok and torch.equal(Ih, If) and torch.equal(Dh.view(torch.int32), Df.view(torch.int32))

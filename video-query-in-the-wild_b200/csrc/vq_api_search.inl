@@ -46,9 +46,17 @@ static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int k
     int64_t max_chunks = std::min<int64_t>(ntiles, (int64_t)(128 * 64) / kprime);  // select's gather capacity
     max_chunks = std::min<int64_t>(max_chunks, std::max<int64_t>(1, ntiles / 8));   // >= 8 tiles per chunk
     max_chunks = std::max<int64_t>(1, std::min<int64_t>(max_chunks, 64));
+    // Few query groups (fewer than half the CTA slots): "walkers".  The lock-step plan below would put a segment's
+    // predecessor (same group, previous chunk) into the SAME round on another CTA -- running concurrently, its
+    // threshold is not published yet, and nearly every segment would warm up from an empty list (configs[2]: 16 pair
+    // groups on 74 CTA pairs, 460 of 592 segments cold).  Instead the gallery is cut into W = slots / n_groups parts
+    // and CTA (w, g) walks part w for group g as ONE long segment: W cold starts per group, each amortised over
+    // 1/W of the gallery, and the CTAs of one part still sweep the same rows together (L2 sharing).
+    const bool walkers = n_groups * 2 <= slots && !g_hooks.no_chain && ntiles >= 8 * (slots / n_groups);
     int64_t best = 1;
     double best_eff = -1.0;
-    for (int64_t c = 1; c <= max_chunks; ++c) {
+    if (walkers) best = std::min<int64_t>(slots / n_groups, max_chunks);
+    for (int64_t c = 1; c <= max_chunks && !walkers; ++c) {
         const int64_t units = n_groups * c;
         const double eff = (double)units / (double)(((units + slots - 1) / slots) * slots);
         if (eff > best_eff + 0.01) {
@@ -85,7 +93,8 @@ static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int k
         sb[(size_t)s_] = cs[(size_t)chunk];
         se[(size_t)s_] = cs[(size_t)chunk + 1];
         sg[(size_t)s_] = (int32_t)g;
-        pred[(size_t)s_] = (chunk > 0 && !g_hooks.no_chain) ? s_of_u[(size_t)(u - n_groups)] : -1;  // A/B hook
+        // -1: first chunk of the gallery; -2: no predecessor to continue, but earlier chunks exist (walker parts)
+        pred[(size_t)s_] = chunk == 0 ? -1 : (walkers || g_hooks.no_chain) ? -2 : s_of_u[(size_t)(u - n_groups)];
         gsegs[(size_t)(g * n_chunks + chunk)] = s_;
     }
     pl->nseg = (int)units;

@@ -194,14 +194,13 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
         // accumulator (= score / 2) is compared with
         float tau = qvalid ? -INFINITY : INFINITY;
         int cnt = 0;
-        int cum = 1;  // this unit's list covers every earlier gallery chunk of the row as well
+        int cum = p.seg_pred[sg_i] == -1 ? 1 : 0;  // this unit's list covers every earlier gallery chunk of the row as well
         {   // CONTINUE the predecessor segment (same query rows, previous gallery chunk) if it has been published
             // (tau NaN = not yet): take over its final threshold AND its final list, so the row's stream goes on as
             // if the chunk boundary were not there -- the next compaction tightens tau after k' new candidates instead
             // of the list having to refill from empty -- and the select kernel reads ONE list per query.
             const int pr = p.seg_pred[sg_i];
             if (pr >= 0 && qvalid) {
-                cum = 0;
                 const int64_t pu = (int64_t)(PAIR ? 2 * pr + rank : pr) * BM + row;
                 const float t0 = *(const volatile float *)(p.cand_tau + pu);
                 if (t0 == t0) tau = t0;  // everything the predecessor discarded is <= its final threshold
