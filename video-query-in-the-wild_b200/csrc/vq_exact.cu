@@ -13,7 +13,7 @@ namespace vq {
 // ---------------------------------------------------------------------------------------
 // all-pairs: 64 x 64 output tile per 256-thread block, 4 x 4 per thread, k staged 32 at a time
 // ---------------------------------------------------------------------------------------
-static constexpr int AT = 64, AK = 32, APAD = 4;
+static constexpr int AT = 64, AQ = 128, AK = 32, APAD = 4;  // gallery rows / query rows / k per block tile
 
 // Packed fp32x2 canonical step (sm_100a FADD2 / FFMA2): two independent chains per instruction, each lane rounded
 // exactly as the scalar __fsub_rn / __fmaf_rn pair (no FTZ) -- same bits as canon_step, half the issue slots.
@@ -25,56 +25,65 @@ __device__ __forceinline__ unsigned long long canon_step2(unsigned long long acc
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) l2sq_all_kernel(const T *__restrict__ q, const T *__restrict__ g,
-                                                       int64_t nq, int64_t n, int d, float *__restrict__ out) {
-    __shared__ __align__(16) float2 sQ[AK][AT + APAD];  // every query value twice: the {q, q} operand of a packed step
+__global__ void __launch_bounds__(256, 3) l2sq_all_kernel(const T *__restrict__ q, const T *__restrict__ g,
+                                                          int64_t nq, int64_t n, int d, float *__restrict__ out) {
+    // 128 queries x 64 gallery rows per block, 8 x 4 per thread: per k one thread reads 8 query and 4 gallery values
+    // (three LDS.128) for 32 packed steps.  The {q, q} operand of a packed step is the scalar-broadcast form of FADD2
+    // (R.F32): nothing is duplicated in shared memory -- with a 4 x 4 tile and duplicated queries the shared-memory
+    // pipe was the limiter (ncu: l1tex 95 %, fma pipe 58 %).
+    __shared__ __align__(16) float sQ[AK][AQ + APAD];
     __shared__ __align__(16) float sG[AK][AT + APAD];
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
-    const int64_t q0 = (int64_t)blockIdx.y * AT, g0 = (int64_t)blockIdx.x * AT;
-    unsigned long long acc[4][2];  // [query a][gallery pair]: {acc(a, 2p), acc(a, 2p+1)}
+    const int64_t q0 = (int64_t)blockIdx.y * AQ, g0 = (int64_t)blockIdx.x * AT;
+    unsigned long long acc[8][2];  // [query a][gallery pair]: {acc(a, 2p), acc(a, 2p+1)}
 #pragma unroll
-    for (int a = 0; a < 4; ++a) acc[a][0] = acc[a][1] = 0ull;
-    const int lr = tid >> 2, lk = (tid & 3) * 8;  // loader: row lr, 8 consecutive k
-    // The next k-block's values are fetched into registers while this one is being multiplied (the global latency
-    // used to sit between the two barriers of every step); the tile columns are XOR-swizzled by the k-group so that
-    // the four loader lanes of a row do not land in one bank.
-    const int sw_st = (lk >> 3) << 3;  // (tid & 3) << 3
-    float rq[8], rg[8];
+    for (int a = 0; a < 8; ++a) acc[a][0] = acc[a][1] = 0ull;
+    // loaders: query row qr = tid / 2, 16 consecutive k; gallery row gr = tid / 4, 8 consecutive k.  The next k-block's
+    // values are fetched into registers while this one is being multiplied; tile columns are XOR-swizzled by the k-group
+    // so that the loader lanes of one row do not land in one bank.
+    const int qr = tid >> 1, qk = (tid & 1) * 16, q_sw = (tid & 1) << 4;
+    const int gr = tid >> 2, gk = (tid & 3) * 8, g_sw = (tid & 3) << 3;
+    float rq[16], rg[8];
     auto fetch = [&](int k0) {
 #pragma unroll
+        for (int e = 0; e < 16; ++e) {
+            const int k = k0 + qk + e;
+            rq[e] = (k < d && q0 + qr < nq) ? to_f32<T>(q[(q0 + qr) * d + k]) : 0.f;
+        }
+#pragma unroll
         for (int e = 0; e < 8; ++e) {
-            const int k = k0 + lk + e;
-            rq[e] = (k < d && q0 + lr < nq) ? to_f32<T>(q[(q0 + lr) * d + k]) : 0.f;
-            rg[e] = (k < d && g0 + lr < n) ? to_f32<T>(g[(g0 + lr) * d + k]) : 0.f;
+            const int k = k0 + gk + e;
+            rg[e] = (k < d && g0 + gr < n) ? to_f32<T>(g[(g0 + gr) * d + k]) : 0.f;
         }
     };
     fetch(0);
     for (int k0 = 0; k0 < d; k0 += AK) {
         __syncthreads();
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-            sQ[lk + e][lr ^ sw_st] = make_float2(rq[e], rq[e]);
-            sG[lk + e][lr ^ sw_st] = rg[e];
-        }
+        for (int e = 0; e < 16; ++e) sQ[qk + e][qr ^ q_sw] = rq[e];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) sG[gk + e][gr ^ g_sw] = rg[e];
         __syncthreads();
         if (k0 + AK < d) fetch(k0 + AK);
 #pragma unroll
         for (int kk = 0; kk < AK; ++kk) {
-            const int sw = (kk >> 3) << 3;
-            const ulonglong2 qa = *reinterpret_cast<const ulonglong2 *>(&sQ[kk][(ty * 4) ^ sw]);
-            const ulonglong2 qb = *reinterpret_cast<const ulonglong2 *>(&sQ[kk][((ty * 4) ^ sw) + 2]);
-            const ulonglong2 b2 = *reinterpret_cast<const ulonglong2 *>(&sG[kk][(tx * 4) ^ sw]);
-            const unsigned long long qv[4] = {qa.x, qa.y, qb.x, qb.y};
+            const int swq = (kk >> 4) << 4, swg = (kk >> 3) << 3;
+            const float4 a0 = *reinterpret_cast<const float4 *>(&sQ[kk][(ty * 8) ^ swq]);
+            const float4 a1 = *reinterpret_cast<const float4 *>(&sQ[kk][((ty * 8) ^ swq) + 4]);
+            const ulonglong2 b2 = *reinterpret_cast<const ulonglong2 *>(&sG[kk][(tx * 4) ^ swg]);
+            const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
 #pragma unroll
-            for (int a = 0; a < 4; ++a) {
-                acc[a][0] = canon_step2(acc[a][0], qv[a], b2.x);
-                acc[a][1] = canon_step2(acc[a][1], qv[a], b2.y);
+            for (int a = 0; a < 8; ++a) {
+                unsigned long long qv;
+                asm("mov.b64 %0, {%1, %1};" : "=l"(qv) : "f"(av[a]));
+                acc[a][0] = canon_step2(acc[a][0], qv, b2.x);
+                acc[a][1] = canon_step2(acc[a][1], qv, b2.y);
             }
         }
     }
 #pragma unroll
-    for (int a = 0; a < 4; ++a) {
-        const int64_t qi = q0 + ty * 4 + a;
+    for (int a = 0; a < 8; ++a) {
+        const int64_t qi = q0 + ty * 8 + a;
         if (qi >= nq) continue;
         const float r[4] = {__uint_as_float((uint32_t)acc[a][0]), __uint_as_float((uint32_t)(acc[a][0] >> 32)),
                             __uint_as_float((uint32_t)acc[a][1]), __uint_as_float((uint32_t)(acc[a][1] >> 32))};
@@ -92,7 +101,7 @@ __global__ void __launch_bounds__(256) l2sq_all_kernel(const T *__restrict__ q, 
 int launch_l2sq_all(const void *q, const void *g, int dtype, int64_t nq, int64_t n, int d, float *out,
                     cudaStream_t st) {
     if (nq == 0 || n == 0) return VQ_OK;
-    dim3 grid((unsigned)((n + AT - 1) / AT), (unsigned)((nq + AT - 1) / AT));
+    dim3 grid((unsigned)((n + AT - 1) / AT), (unsigned)((nq + AQ - 1) / AQ));
     VQ_CHECK(grid.y <= 65535, VQ_ERR_INVALID, "l2sq_all: too many query tiles in one launch");
     if (dtype == VQ_F32)
         l2sq_all_kernel<float><<<grid, 256, 0, st>>>((const float *)q, (const float *)g, nq, n, d, out);
