@@ -19,13 +19,14 @@ static int *hook_slot(const char *name) {
         {"FORCE_FALLBACK", &g_hooks.force_fallback}, {"NO_PAIR", &g_hooks.no_pair}, {"NO_CHAIN", &g_hooks.no_chain},
         {"DENSE_ROWS", &g_hooks.dense_rows}, {"NO_TC_TRIPLET", &g_hooks.no_tc_triplet},
         {"TRIPLET_CLOCKS", &g_hooks.triplet_clocks}, {"NO_TC_EVAL", &g_hooks.no_tc_eval},
-        {"NO_INSERT", &g_hooks.no_insert}, {"KPRIME", &g_hooks.kprime}, {"TRIGGER", &g_hooks.trigger}};
+        {"NO_INSERT", &g_hooks.no_insert}, {"KPRIME", &g_hooks.kprime}, {"TRIGGER", &g_hooks.trigger},
+        {"NO_VMAJOR", &g_hooks.no_vmajor}};
     for (auto &t : tab)
         if (!strcmp(name, t.n)) return t.p;
     return nullptr;
 }
 static const bool g_hooks_from_env = [] {
-    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER"}) {
+    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER", "NO_VMAJOR"}) {
         char env[64];
         snprintf(env, sizeof(env), "VQ_DEBUG_%s", n);
         if (const char *e = getenv(env)) *hook_slot(n) = atoi(e);

@@ -253,7 +253,15 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     sp.seg_start = segmax ? ix->seg_start_dev : nullptr;
     sp.out_d2 = D; sp.out_idx = I; sp.out_seg = seg_out;
     sp.unproven = ix->unproven; sp.unproven_count = ix->unproven_count;
-    VQ_TRY(launch_select(sp, st));
+    Tmp vm;
+    if (segmax && !g_hooks.no_vmajor) {
+        const int64_t nseg = (int64_t)ix->seg_start.size() - 1;
+        VQ_TRY(vm.alloc(select_vmajor_scratch_bytes(nq, kprime, nseg), st));
+        VQ_TRY(launch_select_segmax_vmajor(sp, nseg, vm.p, st));
+        launches += 4;
+    } else {
+        VQ_TRY(launch_select(sp, st));
+    }
     VQ_CUDA(cudaEventRecord(ix->ev[3], st));
     ++launches;
 

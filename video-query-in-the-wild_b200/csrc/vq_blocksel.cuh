@@ -66,6 +66,15 @@ __device__ __forceinline__ void block_bitonic_sort(uint64_t *keys, int n2) {
     __syncthreads();
 }
 
+// Packed fp32x2 canonical step (sm_100a FADD2 / FFMA2): two independent chains per instruction, each lane rounded
+// exactly as the scalar __fsub_rn / __fmaf_rn pair (no FTZ) -- same bits as canon_step, half the issue slots.
+__device__ __forceinline__ unsigned long long canon_step2(unsigned long long acc, unsigned long long q2, unsigned long long g2) {
+    unsigned long long df, r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(df) : "l"(q2), "l"(g2));
+    asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(r) : "l"(df), "l"(acc));
+    return r;
+}
+
 __host__ __device__ __forceinline__ int next_pow2(int v) {
     int p = 1;
     while (p < v) p <<= 1;

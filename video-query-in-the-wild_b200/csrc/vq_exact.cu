@@ -15,15 +15,6 @@ namespace vq {
 // ---------------------------------------------------------------------------------------
 static constexpr int AT = 64, AQ = 128, AK = 32, APAD = 4;  // gallery rows / query rows / k per block tile
 
-// Packed fp32x2 canonical step (sm_100a FADD2 / FFMA2): two independent chains per instruction, each lane rounded
-// exactly as the scalar __fsub_rn / __fmaf_rn pair (no FTZ) -- same bits as canon_step, half the issue slots.
-__device__ __forceinline__ unsigned long long canon_step2(unsigned long long acc, unsigned long long q2, unsigned long long g2) {
-    unsigned long long df, r;
-    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(df) : "l"(q2), "l"(g2));
-    asm("fma.rn.f32x2 %0, %1, %1, %2;" : "=l"(r) : "l"(df), "l"(acc));
-    return r;
-}
-
 template <typename T>
 __global__ void __launch_bounds__(256, 3) l2sq_all_kernel(const T *__restrict__ q, const T *__restrict__ g,
                                                           int64_t nq, int64_t n, int d, float *__restrict__ out) {

@@ -10,7 +10,7 @@ namespace vq {
 // loaded and changed afterwards only through vq_debug_set() -- never getenv() on a search path.
 struct DebugHooks {
     int force_fallback = 0, no_pair = 0, no_chain = 0, dense_rows = -1, no_tc_triplet = 0, triplet_clocks = 0,
-        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0;
+        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0, no_vmajor = 0;
 };
 extern DebugHooks g_hooks;
 
@@ -103,8 +103,15 @@ struct SelectParams {
     int64_t *out_seg;  // [nq,k] or null (segmax: video id)
     int32_t *unproven;       // [nq] list of query ids that need the exact fallback
     int32_t *unproven_count; // [1]
+    // segmax, video-major re-scoring (launch_select_segmax_vmajor sets these): the select kernel only emits the pairs
+    int32_t *pair_vid;       // [nq, kprime] surviving video of each slot (-1 = none) or null
+    int32_t *pair_m;         // [nq]
+    float *pair_tau;         // [nq]
+    int32_t *vcount;         // [nseg] pairs per video
 };
 int launch_select(const SelectParams &p, cudaStream_t st);
+size_t select_vmajor_scratch_bytes(int64_t nq, int kprime, int64_t nseg);
+int launch_select_segmax_vmajor(SelectParams p, int64_t nseg, void *scratch, cudaStream_t st);
 
 struct FallbackParams {
     int64_t nq, n;

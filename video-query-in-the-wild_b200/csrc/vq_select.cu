@@ -131,6 +131,23 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
         tau = fmaxf(tau, ordered_to_f32(Th));
     }
 
+    if (SEGMAX && p.pair_vid) {
+        // video-major re-scoring (below): hand the surviving (query, video) pairs over instead of re-scoring them here
+        for (int i = tid; i < p.kprime; i += kSelThreads) {
+            int v = -1;
+            if (i < m) {
+                v = p.seg_of_row[key_desc_idx(keys[i])];
+                atomicAdd(p.vcount + v, 1);
+            }
+            p.pair_vid[q * p.kprime + i] = v;
+        }
+        if (tid == 0) {
+            p.pair_m[q] = m;
+            p.pair_tau[q] = tau;
+        }
+        return;
+    }
+
     // ---- 2. canonical re-scoring ----
     for (int i = tid; i < ksort; i += kSelThreads) {
         ex[i] = ~0ull;
@@ -235,6 +252,193 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// SEGMAX, video-major re-scoring.  Block-per-query re-scoring reads 128 candidate videos x all their moments per query
+// -- 69 GB of rows for 4 096 queries x (20 480 videos x 64 moments x 2 KB), far outside L2: HBM-bound.  Here the
+// surviving (query, video) pairs are bucketed by VIDEO (count in the select kernel, scan, fill), each video's rows are
+// read once and scored against all the queries that kept it with the all-pairs register tile (packed canonical
+// chains, same bits), and a last per-query kernel sorts the exact keys and proves completeness.
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024) scan_i32_kernel(const int32_t *__restrict__ in, int32_t *__restrict__ out, int64_t n) {
+    __shared__ int part[1024];
+    const int tid = threadIdx.x;
+    const int64_t per = (n + 1023) / 1024, b = tid * per, e = b + per < n ? b + per : n;
+    int s = 0;
+    for (int64_t i = b; i < e; ++i) s += in[i];
+    part[tid] = s;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const int v = tid >= o ? part[tid - o] : 0;
+        __syncthreads();
+        part[tid] += v;
+        __syncthreads();
+    }
+    int run = part[tid] - s;
+    for (int64_t i = b; i < e; ++i) {
+        const int c = in[i];
+        out[i] = run;
+        run += c;
+    }
+    if (tid == 1023) out[n] = part[1023];
+}
+
+__global__ void __launch_bounds__(256) segmax_fill_kernel(const int32_t *__restrict__ pair_vid, int64_t npairs,
+                                                          const int32_t *__restrict__ voff, int32_t *__restrict__ vfill,
+                                                          int32_t *__restrict__ plist) {
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= npairs) return;
+    const int v = pair_vid[i];
+    if (v >= 0) plist[voff[v] + atomicAdd(vfill + v, 1)] = (int32_t)i;
+}
+
+// one 128-thread block per video: 32 queries x 64 moments per tile, 4 x 4 per thread, k staged 32 at a time
+static constexpr int VQT = 32, VMT = 64, VK = 32, VPAD = 4, VTHREADS = 128;
+
+template <typename T>
+__global__ void __launch_bounds__(VTHREADS) segmax_rescore_kernel(const SelectParams p, const int32_t *__restrict__ voff,
+                                                                  const int32_t *__restrict__ plist, uint64_t *__restrict__ exact) {
+    __shared__ __align__(16) float sQ[VK][VQT + VPAD];
+    __shared__ __align__(16) float sG[VK][VMT + VPAD];
+    __shared__ int s_pair[VQT];
+    const int v = blockIdx.x, tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+    const int p0 = voff[v], p1 = voff[v + 1];
+    if (p0 == p1) return;
+    const int64_t s0 = p.seg_start[v], s1 = p.seg_start[v + 1];
+    const T *gq = (const T *)p.q, *gg = (const T *)p.g;
+    const int d = p.d;
+    // loaders: query slot qr = tid / 4 (32 slots), 8 consecutive k; moment row gr = tid / 2 (64 rows), 16 consecutive k
+    const int qr = tid >> 2, qk = (tid & 3) * 8, q_sw = (tid & 3) << 3;
+    const int gr = tid >> 1, gk = (tid & 1) * 16, g_sw = (tid & 1) << 4;
+    for (int pc = p0; pc < p1; pc += VQT) {  // chunk of the video's queries
+        __syncthreads();
+        if (tid < VQT) s_pair[tid] = pc + tid < p1 ? plist[pc + tid] : -1;
+        __syncthreads();
+        const int pr = s_pair[qr];
+        const int64_t qrow = pr >= 0 ? (int64_t)(pr / p.kprime) : -1;
+        uint64_t best[4] = {~0ull, ~0ull, ~0ull, ~0ull};  // running (d2, row) minima of queries ty*4 .. ty*4+3 over lane tx's moments
+        for (int64_t mc = s0; mc < s1; mc += VMT) {  // chunk of the video's moments
+            unsigned long long acc[4][2];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) acc[a][0] = acc[a][1] = 0ull;
+            float rq[8], rg[16];
+            auto fetch = [&](int k0) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                    const int k = k0 + qk + e;
+                    rq[e] = (k < d && qrow >= 0) ? to_f32<T>(gq[qrow * d + k]) : 0.f;
+                }
+#pragma unroll
+                for (int e = 0; e < 16; ++e) {
+                    const int k = k0 + gk + e;
+                    rg[e] = (k < d && mc + gr < s1) ? to_f32<T>(gg[(mc + gr) * d + k]) : 0.f;
+                }
+            };
+            fetch(0);
+            for (int k0 = 0; k0 < d; k0 += VK) {
+                __syncthreads();
+#pragma unroll
+                for (int e = 0; e < 8; ++e) sQ[qk + e][qr ^ q_sw] = rq[e];
+#pragma unroll
+                for (int e = 0; e < 16; ++e) sG[gk + e][gr ^ g_sw] = rg[e];
+                __syncthreads();
+                if (k0 + VK < d) fetch(k0 + VK);
+#pragma unroll
+                for (int kk = 0; kk < VK; ++kk) {
+                    const int swq = (kk >> 3) << 3, swg = (kk >> 4) << 4;
+                    const float4 a4 = *reinterpret_cast<const float4 *>(&sQ[kk][(ty * 4) ^ swq]);
+                    const ulonglong2 b2 = *reinterpret_cast<const ulonglong2 *>(&sG[kk][(tx * 4) ^ swg]);
+                    const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+                    for (int a = 0; a < 4; ++a) {
+                        unsigned long long qv;
+                        asm("mov.b64 %0, {%1, %1};" : "=l"(qv) : "f"(av[a]));
+                        acc[a][0] = canon_step2(acc[a][0], qv, b2.x);
+                        acc[a][1] = canon_step2(acc[a][1], qv, b2.y);
+                    }
+                }
+            }
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const float r[4] = {__uint_as_float((uint32_t)acc[a][0]), __uint_as_float((uint32_t)(acc[a][0] >> 32)),
+                                    __uint_as_float((uint32_t)acc[a][1]), __uint_as_float((uint32_t)(acc[a][1] >> 32))};
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const int64_t row = mc + tx * 4 + b;
+                    if (row < s1) {
+                        const uint64_t kk = make_key_asc(r[b], (uint32_t)row);
+                        best[a] = kk < best[a] ? kk : best[a];
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {  // the 16 lanes tx = 0..15 of a half warp hold one query's partial minima
+            uint64_t b = best[a];
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) {
+                const uint64_t other = __shfl_xor_sync(0xffffffffu, b, o);
+                b = other < b ? other : b;
+            }
+            const int pr2 = s_pair[ty * 4 + a];
+            if (tx == 0 && pr2 >= 0) exact[pr2] = b;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kSelThreads) segmax_finish_kernel(const SelectParams p, const uint64_t *__restrict__ exact) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    const int ksort = next_pow2(p.kprime);
+    uint64_t *ex = (uint64_t *)sm;
+    __shared__ float qn_w[kSelThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t q = blockIdx.x;
+    const int m = p.pair_m[q];
+    const float tau = p.pair_tau[q];
+    for (int i = tid; i < ksort; i += kSelThreads) ex[i] = i < m ? exact[q * p.kprime + i] : ~0ull;
+    float qn = 0.f;
+    if (p.dtype == VQ_F32) {
+        const float *qrow = (const float *)p.q + q * p.d;
+        for (int i = tid; i < p.d; i += kSelThreads) qn = fmaf(qrow[i], qrow[i], qn);
+    } else {
+        const __nv_bfloat16 *qrow = (const __nv_bfloat16 *)p.q + q * p.d;
+        for (int i = tid; i < p.d; i += kSelThreads) {
+            const float x = __bfloat162float(qrow[i]);
+            qn = fmaf(x, x, qn);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) qn += __shfl_xor_sync(0xffffffffu, qn, o);
+    if (lane == 0) qn_w[warp] = qn;
+    __syncthreads();
+    block_bitonic_sort(ex, ksort);
+    qn = 0.f;
+    for (int w = 0; w < kSelThreads / 32; ++w) qn += qn_w[w];
+    const int kout = p.k;
+    bool proven = true;
+    if (tau != -INFINITY) {
+        if (m < kout) {
+            proven = false;
+        } else {
+            const float gmax2 = __uint_as_float(*p.gmax_norm2_bits);
+            const float eps = p.eps_rel * sqrtf(qn) * sqrtf(gmax2) + p.eps_abs * (qn + gmax2);
+            const float d2k = ordered_to_f32((uint32_t)(ex[kout - 1] >> 32));
+            proven = qn - tau - eps > d2k;  // every dropped video's best moment has d2 >= qn - tau - eps
+        }
+    }
+    for (int i = tid; i < kout; i += kSelThreads) {
+        const uint64_t kk = ex[i];
+        const bool ok = (i < m) && kk != ~0ull;
+        const uint32_t row = (uint32_t)kk;
+        p.out_d2[q * kout + i] = ok ? ordered_to_f32((uint32_t)(kk >> 32)) : INFINITY;
+        p.out_idx[q * kout + i] = ok ? (int64_t)row : -1;
+        if (p.out_seg) p.out_seg[q * kout + i] = ok ? (int64_t)p.seg_of_row[row] : -1;
+    }
+    if (!proven && tid == 0) {
+        const int slot = atomicAdd(p.unproven_count, 1);
+        p.unproven[slot] = (int32_t)q;
+    }
+}
+
 size_t select_smem_bytes(const SelectParams &p) {
     const size_t ks = (size_t)next_pow2(p.kprime);
     return select_keys_bytes(p.segs_per_group, p.kprime) + ks * 8 + ks * 4 + (size_t)p.d * 4 + 40 * 4 + ((size_t)2 * p.segs_per_group + 2) * 4 +
@@ -247,6 +451,38 @@ static int launch_sel(const SelectParams &p, cudaStream_t st) {
     auto kern = select_kernel<T, SEGMAX>;
     VQ_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(unsigned)p.nq, kSelThreads, smem, st>>>(p);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
+size_t select_vmajor_scratch_bytes(int64_t nq, int kprime, int64_t nseg) {
+    // pair_vid i32 | plist i32 | exact u64 (per pair)   pair_m i32 | pair_tau f32 (per query)   vcount | vfill | voff (per video)
+    return (size_t)nq * kprime * 16 + (size_t)nq * 8 + (size_t)(nseg + 1) * 12 + 64;
+}
+
+// SEGMAX with the video-major re-scoring; scratch: select_vmajor_scratch_bytes(), device memory
+int launch_select_segmax_vmajor(SelectParams p, int64_t nseg, void *scratch, cudaStream_t st) {
+    if (p.nq == 0) return VQ_OK;
+    const int64_t npairs = p.nq * p.kprime;
+    uint64_t *exact = (uint64_t *)scratch;
+    int32_t *pair_vid = (int32_t *)(exact + npairs);
+    int32_t *plist = pair_vid + npairs;
+    int32_t *pair_m = plist + npairs;
+    float *pair_tau = (float *)(pair_m + p.nq);
+    int32_t *vcount = (int32_t *)(pair_tau + p.nq);
+    int32_t *vfill = vcount + (nseg + 1);
+    int32_t *voff = vfill + (nseg + 1);
+    VQ_CUDA(cudaMemsetAsync(vcount, 0, (size_t)(nseg + 1) * 8, st));  // vcount and vfill
+    p.pair_vid = pair_vid; p.pair_m = pair_m; p.pair_tau = pair_tau; p.vcount = vcount;
+    VQ_TRY(launch_select(p, st));  // phase A: the k' surviving videos of every query -> pairs
+    scan_i32_kernel<<<1, 1024, 0, st>>>(vcount, voff, nseg);
+    segmax_fill_kernel<<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(pair_vid, npairs, voff, vfill, plist);
+    if (p.dtype == VQ_F32)
+        segmax_rescore_kernel<float><<<(unsigned)nseg, VTHREADS, 0, st>>>(p, voff, plist, exact);
+    else
+        segmax_rescore_kernel<__nv_bfloat16><<<(unsigned)nseg, VTHREADS, 0, st>>>(p, voff, plist, exact);
+    const size_t smem = (size_t)next_pow2(p.kprime) * 8;
+    segmax_finish_kernel<<<(unsigned)p.nq, kSelThreads, smem, st>>>(p, exact);
     VQ_CUDA(cudaGetLastError());
     return VQ_OK;
 }
