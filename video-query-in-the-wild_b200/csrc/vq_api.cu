@@ -20,13 +20,13 @@ static int *hook_slot(const char *name) {
         {"DENSE_ROWS", &g_hooks.dense_rows}, {"NO_TC_TRIPLET", &g_hooks.no_tc_triplet},
         {"TRIPLET_CLOCKS", &g_hooks.triplet_clocks}, {"NO_TC_EVAL", &g_hooks.no_tc_eval},
         {"NO_INSERT", &g_hooks.no_insert}, {"KPRIME", &g_hooks.kprime}, {"TRIGGER", &g_hooks.trigger},
-        {"NO_VMAJOR", &g_hooks.no_vmajor}};
+        {"NO_VMAJOR", &g_hooks.no_vmajor}, {"NO_NMS_MASKS", &g_hooks.no_nms_masks}};
     for (auto &t : tab)
         if (!strcmp(name, t.n)) return t.p;
     return nullptr;
 }
 static const bool g_hooks_from_env = [] {
-    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER", "NO_VMAJOR"}) {
+    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER", "NO_VMAJOR", "NO_NMS_MASKS"}) {
         char env[64];
         snprintf(env, sizeof(env), "VQ_DEBUG_%s", n);
         if (const char *e = getenv(env)) *hook_slot(n) = atoi(e);
@@ -234,6 +234,8 @@ struct vq_index {
     // moment evaluation (a8): per-row moment metadata, videos split by size class for the NMS kernel
     float *m_start = nullptr, *m_end = nullptr, *m_iou = nullptr;
     int32_t *m_hit = nullptr;
+    unsigned long long *m_sup = nullptr;  // NMS suppression masks (videos of <= 64 moments) for threshold m_sup_thresh
+    double m_sup_thresh = -1.0;
     int32_t *seg_small = nullptr, *seg_large = nullptr;
     int n_seg_small = 0, n_seg_large = 0;
     int64_t seg_max_len = 0;
@@ -313,7 +315,7 @@ int vq_index_destroy(vq_index *ix) {
     void *ptrs[] = {ix->raw,   ix->hi,         ix->lo,           ix->norm2,    ix->gmax_bits,
                     ix->label, ix->video,      ix->seg_of_row,   ix->seg_start_dev, ix->cand,     ix->cand_cnt,
                     ix->cand_tau, ix->cand_cum, ix->plan_rows_dev, ix->plan_ints_dev, ix->unproven, ix->unproven_count,
-                    ix->m_start, ix->m_end, ix->m_iou, ix->m_hit, ix->seg_small, ix->seg_large};
+                    ix->m_start, ix->m_end, ix->m_iou, ix->m_hit, ix->seg_small, ix->seg_large, ix->m_sup};
     for (void *p : ptrs)
         if (p) cudaFree(p);
     if (ix->stat_pinned) cudaFreeHost(ix->stat_pinned);
@@ -386,8 +388,9 @@ int vq_index_add(vq_index *ix, const void *xb, int64_t n, int dtype, void *strea
     if (ix->video) { cudaFree(ix->video); ix->video = nullptr; }
     if (ix->seg_of_row) { cudaFree(ix->seg_of_row); ix->seg_of_row = nullptr; }
     ix->seg_start.clear();
-    for (void **pp : {(void **)&ix->m_start, (void **)&ix->m_end, (void **)&ix->m_iou, (void **)&ix->m_hit})
+    for (void **pp : {(void **)&ix->m_start, (void **)&ix->m_end, (void **)&ix->m_iou, (void **)&ix->m_hit, (void **)&ix->m_sup})
         if (*pp) { cudaFree(*pp); *pp = nullptr; }
+    ix->m_sup_thresh = -1.0;
     return VQ_OK;
 }
 
@@ -418,6 +421,7 @@ int vq_index_set_segments(vq_index *ix, const int64_t *seg_start, int64_t nseg, 
     for (int64_t v = 0; v < nseg; ++v)
         VQ_CHECK(seg_start[v] <= seg_start[v + 1], VQ_ERR_INVALID, "seg_start not monotone at %lld", (long long)v);
     cudaStream_t st = (cudaStream_t)stream;
+    ix->m_sup_thresh = -1.0;  // the suppression masks follow the segmentation
     ix->seg_start.assign(seg_start, seg_start + nseg + 1);
     std::vector<int32_t> sor((size_t)ix->n);
     for (int64_t v = 0; v < nseg; ++v)
@@ -458,6 +462,7 @@ int vq_index_set_moments(vq_index *ix, const float *start_sec, const float *end_
     VQ_CHECK(ix->n > 0, VQ_ERR_STATE, "vq_index_set_moments before vq_index_add");
     cudaStream_t st = (cudaStream_t)stream;
     const size_t bytes = (size_t)ix->n * 4;
+    ix->m_sup_thresh = -1.0;
     const void *src[4] = {start_sec, end_sec, iou, hit_label};
     void **dst[4] = {(void **)&ix->m_start, (void **)&ix->m_end, (void **)&ix->m_iou, (void **)&ix->m_hit};
     for (int i = 0; i < 4; ++i) {

@@ -528,6 +528,13 @@ int vq_index_eval_moment(vq_index *ix, const void *xq, int64_t nq, int dtype, co
     VQ_TRY(vbest.alloc((size_t)tile_q * nseg * 8, st));
     VQ_TRY(ovf.alloc(4, st));
     int launches = 0;
+    if (ix->n_seg_small > 0 && !g_hooks.no_nms_masks && (!ix->m_sup || ix->m_sup_thresh != nms_thresh)) {
+        // the suppression relation between the moments of a video does not depend on the query: once per threshold
+        if (!ix->m_sup) VQ_CUDA(cudaMalloc(&ix->m_sup, (size_t)ix->n * 8));
+        VQ_TRY(launch_nms_masks(ix->seg_start_dev, ix->seg_small, ix->n_seg_small, ix->m_start, ix->m_end, nms_thresh, ix->m_sup, st));
+        ix->m_sup_thresh = nms_thresh;
+        ++launches;
+    }
     for (int attempt = 0; attempt < 2; ++attempt) {
         const int pcap2 = attempt == 0 ? 1024 : kMaxPositives;
         VQ_CUDA(cudaMemsetAsync(ovf.p, 0, 4, st));
@@ -539,6 +546,7 @@ int vq_index_eval_moment(vq_index *ix, const void *xq, int64_t nq, int dtype, co
             MomentNmsParams m{};
             m.nq_tile = tq; m.n = ix->n; m.nseg = nseg; m.d2 = (const float *)d2.p; m.seg_start = ix->seg_start_dev;
             m.start = ix->m_start; m.end = ix->m_end; m.thresh = nms_thresh; m.kept = kp; m.vbest = (uint64_t *)vbest.p;
+            m.sup = (!g_hooks.no_nms_masks && ix->m_sup_thresh == nms_thresh) ? ix->m_sup : nullptr;
             VQ_TRY(launch_moment_nms(m, ix->seg_small, ix->n_seg_small, ix->seg_large, ix->n_seg_large, st));
             ApRowsParams a{};
             a.nq_tile = tq; a.n = ix->n; a.d2 = (const float *)d2.p; a.g_label = ix->m_hit; a.g_video = ix->video;

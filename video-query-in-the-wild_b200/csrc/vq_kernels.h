@@ -10,7 +10,7 @@ namespace vq {
 // loaded and changed afterwards only through vq_debug_set() -- never getenv() on a search path.
 struct DebugHooks {
     int force_fallback = 0, no_pair = 0, no_chain = 0, dense_rows = -1, no_tc_triplet = 0, triplet_clocks = 0,
-        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0, no_vmajor = 0;
+        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0, no_vmajor = 0, no_nms_masks = 0;
 };
 extern DebugHooks g_hooks;
 
@@ -180,7 +180,10 @@ struct MomentNmsParams {
     double thresh;
     uint8_t *kept;               // [nq_tile, n]
     uint64_t *vbest;             // [nq_tile, nseg]
+    const unsigned long long *sup;  // [n] suppression masks of the videos of <= 64 moments (launch_nms_masks) or null
 };
+int launch_nms_masks(const int64_t *seg_start, const int32_t *small_list, int n_small, const float *start, const float *end,
+                     double thresh, unsigned long long *sup, cudaStream_t st);
 int launch_window_means(const float *feat, int C, int64_t Ttot, const int64_t *vid_t0, const int64_t *win_start, int64_t V,
                         int64_t Tmax, const int32_t *lo, const int32_t *hi, float *out, cudaStream_t st);
 // vq_losses.cu (f3 / f4)

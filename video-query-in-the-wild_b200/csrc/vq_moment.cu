@@ -46,6 +46,38 @@ __device__ __forceinline__ bool nms_suppressed(double xa1, double xa2, double la
     return nms_quotient(inter, uni, thresh);
 }
 
+// Suppression relation of the moments of one video, as bit masks: sup[row] bit j = "moment j of the same video is
+// suppressed by this one" (nms_suppressed: IoU >= thresh, the reference's float64 test).  It depends on the video and the
+// threshold only -- not on the query -- so it is built once per (index, threshold) for the videos of <= 64 moments and
+// the per-(query, video) greedy pass becomes bit arithmetic: dead |= sup[a] for every survivor a in ranked order.
+__global__ void __launch_bounds__(256) nms_masks_kernel(const int64_t *__restrict__ seg_start, const int32_t *__restrict__ seg_list,
+                                                        int nlist, const float *__restrict__ start, const float *__restrict__ end,
+                                                        double thresh, unsigned long long *__restrict__ sup) {
+    const int li = blockIdx.x * 8 + (threadIdx.x >> 5), t = threadIdx.x & 31;
+    if (li >= nlist) return;
+    const int v = seg_list[li];
+    const int64_t s0 = seg_start[v];
+    const int S = (int)(seg_start[v + 1] - s0);
+    if (S > 64) return;
+    for (int i = t; i < S; i += 32) {
+        const double xa1 = (double)start[s0 + i], xa2 = (double)end[s0 + i], la = xa2 - xa1 + 1.0;
+        unsigned long long m = 0ull;
+        for (int j = 0; j < S; ++j) {
+            const double xb1 = (double)start[s0 + j], xb2 = (double)end[s0 + j];
+            if (j != i && nms_suppressed(xa1, xa2, la, xb1, xb2, xb2 - xb1 + 1.0, thresh)) m |= 1ull << j;
+        }
+        sup[s0 + i] = m;
+    }
+}
+
+int launch_nms_masks(const int64_t *seg_start, const int32_t *small_list, int n_small, const float *start, const float *end,
+                     double thresh, unsigned long long *sup, cudaStream_t st) {
+    if (n_small == 0) return VQ_OK;
+    nms_masks_kernel<<<(unsigned)((n_small + 7) / 8), 256, 0, st>>>(seg_start, small_list, n_small, start, end, thresh, sup);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
 template <int NT, int CAP>
 __global__ void __launch_bounds__(256, NT == 32 ? 4 : 1) moment_nms_kernel(const MomentNmsParams p, const int32_t *__restrict__ seg_list,
                                                          int nlist, int per_group) {
@@ -102,6 +134,25 @@ __global__ void __launch_bounds__(256, NT == 32 ? 4 : 1) moment_nms_kernel(const
             for (int j = 16; j > 0; j >>= 1) {
                 cx(k0, j, true);
                 cx(k1, j, true);
+            }
+            if (p.sup) {
+                // greedy NMS as bit arithmetic on the precomputed suppression masks (uniform across the warp): walk the
+                // ranks, a moment that is still alive is kept and kills what it overlaps
+                const unsigned long long m0 = t < S ? p.sup[s0 + t] : 0ull, m1 = t + 32 < S ? p.sup[s0 + t + 32] : 0ull;
+                const uint32_t i0 = (uint32_t)k0, i1 = (uint32_t)k1;  // moment (index inside the video) at ranks t, t + 32
+                unsigned long long dead = 0ull, keep = 0ull;
+                for (int r = 0; r < S; ++r) {
+                    const uint32_t a = r < 32 ? __shfl_sync(0xffffffffu, i0, r) : __shfl_sync(0xffffffffu, i1, r - 32);
+                    if (!((dead >> a) & 1ull)) {  // uniform
+                        keep |= 1ull << a;
+                        dead |= a < 32 ? __shfl_sync(0xffffffffu, m0, a) : __shfl_sync(0xffffffffu, m1, a - 32);
+                    }
+                }
+                if (t < S) kept[s0 + t] = (uint8_t)((keep >> t) & 1ull);
+                if (t + 32 < S) kept[s0 + t + 32] = (uint8_t)((keep >> (t + 32)) & 1ull);
+                const uint64_t kb = __shfl_sync(0xffffffffu, k0, 0);
+                if (t == 0) p.vbest[q * p.nseg + v] = (kb & 0xffffffff00000000ull) | (uint64_t)(s0 + (uint32_t)kb);
+                continue;
             }
             keys[t] = k0;
             keys[t + 32] = k1;
