@@ -25,7 +25,9 @@ print("search", ix.last_timing())
 # merge of 8 shard lists
 keys = torch.stack([ops.topk_pack(D + 0.001 * g, I, g * n) for g in range(8)])
 od, oi = ops.topk_merge_keys(keys)
+hd, hi_, inc = ops.topk_merge_heads(keys[:, :, :40].contiguous(), 100)   # round 1 of the exchange at G = 8
 torch.cuda.synchronize()
+print("heads incomplete:", int(inc.item()))
 del ix, keys, D, I
 # configs[0] evaluation
 g0, label, video, qrow = bench.cfg0_problem(np)
@@ -57,6 +59,8 @@ im.add(g2)
 im.set_meta(hit, vid2)
 im.set_segments(np.arange(0, n2 + 1, S, dtype=np.int64))
 im.set_moments(start, end, iou, hit)
+Vs, Rs, Ds = im.search_segmax(q2, 100)          # SEGMAX GEMM + video-major re-scoring (f32 gallery)
+torch.cuda.synchronize()
 apm, recm, _, _ = im.eval_moment(q2, torch.from_numpy(rng.integers(0, 180, nq2).astype(np.int32)).to(dev),
                                  torch.from_numpy(rng.integers(0, V, (nq2, 5)).astype(np.int32)).to(dev))
 torch.cuda.synchronize()
