@@ -118,7 +118,8 @@ VQ_API int vq_index_search_segmax(vq_index *ix, const void *xq, int64_t nq, int 
 
 /* Statistics of the last search on this index (host ints): [0] queries that needed the exact
  * fallback, [1] tensor-core tiles issued, [2] candidate slots per query, [3] work units,
- * [4] gallery segments (stream-K pieces of the query-group x gallery space), [5] kernels launched. */
+ * [4] gallery segments (stream-K pieces of the query-group x gallery space), [5] kernels launched.  After
+ * vq_index_eval_trimmed: [4] = queries its tensor-core form handed back to the canonical all-pairs path. */
 VQ_API int vq_index_last_stats(const vq_index *ix, int64_t *out6);
 /* Device time (ms, CUDA events on the caller's stream) of the phases of the last tensor-core
  * search on this index: [0] query operand preparation, [1] the tcgen05 GEMM + streaming
@@ -132,7 +133,9 @@ VQ_API int vq_index_last_timing(const vq_index *ix, float *out4);
  *   ap float64[nq]; recall float64[nq,3] (R@30/50/100, :332); top_idx int64[nq,100] (the first
  *   100 survivors in rank order -- the rows behind cm_dict["label"], :441-442); may be NULL.
  * Requires vq_index_set_meta.  Full-list semantics (k = ntotal): AP over all survivors with
- * the last one forced positive (:434).
+ * the last one forced positive (:434).  Scores come from the tensor cores (coarse) and canonical arithmetic is spent only
+ * on the query's positives and on survivors within the proven error bound of one of them; the numbers returned are
+ * those of the canonical all-pairs evaluation (which queries with > 1022 positives or > 2048 such survivors still take).
  * ---------------------------------------------------------------------------------- */
 VQ_API int vq_index_eval_trimmed(vq_index *ix, const void *xq, int64_t nq, int dtype,
                                  const int32_t *q_label, const int32_t *ignore_video,

@@ -42,8 +42,29 @@ ix.add(g)
 ix.set_meta(label, video)
 ql = torch.randint(0, 180, (nq,), device=dev, dtype=torch.int32)
 ign = torch.randint(0, n, (nq, 5), device=dev, dtype=torch.int32)
-ms = ev_time(lambda: ix.eval_trimmed(q, ql, ign))
-print("eval_trimmed configs[0]: %.3f ms" % ms)
+from vqwild_b200 import _lib as L
+import bench
+for nm, gg, lab in (("random labels, unit rows", g, label),):
+    for hook in (0, 1):
+        L.debug_set("NO_TC_EVAL", hook)
+        ms = ev_time(lambda: ix.eval_trimmed(q, ql, ign))
+        print("eval_trimmed configs[0] shape, %s, %s: %.3f ms (handed back: %d)" % (nm, "canonical all-pairs" if hook else "tensor-core form", ms, ix.last_stats()["segments"]))
+L.debug_set("NO_TC_EVAL", 0)
+g0, label0, video0, qrow0 = bench.cfg0_problem(np)
+gd = torch.from_numpy(g0).to(dev)
+ix0 = vq.IndexFlatL2(d)
+ix0.add(gd)
+ix0.set_meta(torch.from_numpy(label0).to(dev), torch.from_numpy(video0).to(dev))
+qd = gd[torch.from_numpy(qrow0).to(dev)].contiguous()
+ql0 = torch.from_numpy(label0[qrow0]).to(dev)
+ig0 = torch.from_numpy(video0[qrow0][:, None].astype(np.int32)).to(dev)
+for hook in (0, 1):
+    L.debug_set("NO_TC_EVAL", hook)
+    ms = ev_time(lambda: ix0.eval_trimmed(qd, ql0, ig0))
+    ap = ix0.eval_trimmed(qd, ql0, ig0)[0]
+    print("eval_trimmed configs[0] (bench data, class-structured), %s: %.3f ms (handed back: %d) mAP %.6f" % ("canonical all-pairs" if hook else "tensor-core form", ms, ix0.last_stats()["segments"], float(ap.double().mean())))
+L.debug_set("NO_TC_EVAL", 0)
+del ix0, gd
 qb, gb = q.bfloat16(), g.bfloat16()
 ms = ev_time(lambda: ops.l2sq(qb.float(), gb.float()))
 # moment slice

@@ -236,6 +236,7 @@ struct vq_index {
     int32_t *m_hit = nullptr;
     unsigned long long *m_sup = nullptr;  // NMS suppression masks (videos of <= 64 moments) for threshold m_sup_thresh
     double m_sup_thresh = -1.0;
+    bool tc_eval_off = false;  // the tensor-core form of eval_trimmed handed most queries back last time (labels unrelated to the features)
     int32_t *seg_small = nullptr, *seg_large = nullptr;
     int n_seg_small = 0, n_seg_large = 0;
     int64_t seg_max_len = 0;
@@ -401,6 +402,7 @@ int vq_index_set_meta(vq_index *ix, const int32_t *label, const int32_t *video, 
     const size_t bytes = (size_t)ix->n * 4;
     if (ix->label) { cudaFree(ix->label); ix->label = nullptr; }
     if (ix->video) { cudaFree(ix->video); ix->video = nullptr; }
+    ix->tc_eval_off = false;
     if (label) {
         VQ_CUDA(cudaMalloc(&ix->label, bytes));
         VQ_CUDA(cudaMemcpyAsync(ix->label, label, bytes, cudaMemcpyDefault, st));

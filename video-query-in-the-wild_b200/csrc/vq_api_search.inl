@@ -288,6 +288,48 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     return VQ_OK;
 }
 
+// Coarse scores of every (query, gallery row) pair on the tensor cores: out[q, j] = 2<q,g_j> - |g_j|^2 (gemm_topk STORE
+// mode: same operand planes, same pipeline, no candidate handling).  |out - (|q|^2 - d2)| <= error_model().  Device pointers.
+static int coarse_core(vq_index *ix, const void *xq, int64_t nq, int dtype, float *out, int64_t ld, cudaStream_t st) {
+    SearchPlan spn;
+    make_search_plan(ix, nq, dtype, 100, false, &spn);
+    const bool pair = spn.pair, split = spn.split;
+    const SegPlan &pl = spn.pl;
+    Tmp qhi, qlo;
+    VQ_TRY(qhi.alloc((size_t)nq * ix->dpa * 2, st));
+    if (split) VQ_TRY(qlo.alloc((size_t)nq * ix->dpa * 2, st));
+    VQ_TRY(launch_prepare_rows(xq, dtype, nq, ix->d, ix->dp, true, (__nv_bfloat16 *)qhi.p,
+                               split ? (__nv_bfloat16 *)qlo.p : nullptr, nullptr, nullptr, st));
+    CUtensorMap maps[4];
+    if (pair) {
+        VQ_TRY(make_map(&maps[0], qhi.p, nq, ix->dpa, kTileM));
+        VQ_TRY(make_map(&maps[1], ix->hi, ix->n, ix->dpa, kTileN / 2));
+    } else {
+        VQ_TRY(make_map(&maps[0], qhi.p, nq, ix->dpa, kTileM));
+        VQ_TRY(make_map(&maps[1], split ? qlo.p : qhi.p, nq, ix->dpa, kTileM));
+        VQ_TRY(make_map(&maps[2], ix->hi, ix->n, ix->dpa, kTileN));
+        VQ_TRY(make_map(&maps[3], split ? (void *)ix->lo : (void *)ix->hi, ix->n, ix->dpa, kTileN));
+    }
+    VQ_TRY(ensure_workspace(ix, spn, nq, st));
+    VQ_CUDA(cudaMemcpyAsync(ix->plan_rows_dev, pl.rows.data(), pl.rows.size() * 8, cudaMemcpyHostToDevice, st));
+    VQ_CUDA(cudaMemcpyAsync(ix->plan_ints_dev, pl.ints.data(), pl.ints.size() * 4, cudaMemcpyHostToDevice, st));
+    GemmTopkParams gp{};
+    gp.nq = nq; gp.n = ix->n; gp.kb_count = ix->dp / 64; gp.n_qblocks = spn.n_qblocks; gp.n_seg = pl.nseg;
+    gp.seg_begin = ix->plan_rows_dev; gp.seg_end = ix->plan_rows_dev + pl.nseg;
+    gp.seg_group = ix->plan_ints_dev; gp.cta_seg_start = ix->plan_ints_dev + pl.nseg;
+    gp.seg_pred = ix->plan_ints_dev + pl.nseg + pl.n_cta + 1;
+    VQ_CUDA(cudaMemsetAsync(ix->cand_tau, 0xff, spn.units * kTileM * 4, st));
+    gp.kprime = spn.kprime; gp.dense_rows = 4;
+    gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau; gp.cand_cum = ix->cand_cum;
+    gp.store = out; gp.store_ld = ld;
+    if (pair) {
+        VQ_TRY(launch_gemm_topk_pair(maps, gp, false, pl.n_cta, st));
+    } else {
+        VQ_TRY(launch_gemm_topk(maps, gp, split ? 3 : 1, false, pl.n_cta, st));
+    }
+    return VQ_OK;
+}
+
 // Bytes of the [tile_q, n] canonical score matrix the evaluators work on at a time.  One block per query ranks a row,
 // so the tile has to hold several queries per SM to keep the memory system busy: a quarter of the free HBM, between
 // 256 MiB and 8 GiB (kept mask and per-video keys add ~ 1/3 of that on the moment path).
@@ -444,16 +486,55 @@ int vq_index_eval_trimmed(vq_index *ix, const void *xq, int64_t nq, int dtype, c
     VQ_TRY(oA.bind(ap, (size_t)nq * 8, st));
     VQ_TRY(oR.bind(recall, (size_t)nq * 3 * 8, st));
     VQ_TRY(oT.bind(top_idx, (size_t)nq * 100 * 8, st));
-    // full-list AP / R@N: canonical scores for a tile of queries, then the rank-count reduction
-    const int64_t tile_q = std::max<int64_t>(1, std::min<int64_t>(nq, score_tile_bytes() / std::max<int64_t>(1, ix->n * 4)));
-    Tmp d2, ovf;
-    VQ_TRY(d2.alloc((size_t)tile_q * ix->n * 4, st));
+    // full-list AP / R@N: scores for a tile of queries, then the rank-count reduction
+    const int64_t ld = (ix->n + 3) / 4 * 4;
+    const int64_t tile_q = std::max<int64_t>(1, std::min<int64_t>(nq, score_tile_bytes() / std::max<int64_t>(1, ld * 4)));
+    const int64_t ntile = (nq + tile_q - 1) / tile_q;
+    Tmp d2, ovf, redo, redo_cnt;
+    VQ_TRY(d2.alloc((size_t)tile_q * ld * 4, st));
     VQ_TRY(ovf.alloc(4, st));
     int launches = 0;
-    for (int attempt = 0; attempt < 2; ++attempt) {
+    // Tensor-core form (ap_rows_tc_kernel): coarse scores from the tcgen05 GEMM, canonical arithmetic only for the
+    // positives and for the survivors inside an eps band of one of them; queries it hands back (list overflow) make
+    // their whole tile go through the canonical path below.
+    const bool use_tc = !g_hooks.no_tc_eval && !ix->tc_eval_off && resolve_prec(ix) != VQ_PREC_EXACT;
+    std::vector<int32_t> tile_redo((size_t)ntile, use_tc ? 0 : 1);
+    if (use_tc) {
+        VQ_TRY(redo.alloc((size_t)nq * 4, st));
+        VQ_TRY(redo_cnt.alloc((size_t)ntile * 4, st));
+        VQ_CUDA(cudaMemsetAsync(redo_cnt.p, 0, (size_t)ntile * 4, st));
+        for (int64_t q0 = 0, ti = 0; q0 < nq; q0 += tile_q, ++ti) {
+            const int64_t tq = std::min(tile_q, nq - q0);
+            const char *qt = (const char *)q.dev + (size_t)q0 * ix->d * esize(dtype);
+            VQ_TRY(coarse_core(ix, qt, tq, dtype, (float *)d2.p, ld, st));
+            ApTcParams t{};
+            t.nq_tile = tq; t.n = ix->n; t.ld = ld; t.d = ix->d; t.dtype = dtype; t.coarse = (const float *)d2.p;
+            t.q = qt; t.g = ix->raw; t.g_label = ix->label; t.g_video = ix->video;
+            t.q_label = ql.as<int32_t>() + q0;
+            t.q_ignore = n_ign ? ig.as<int32_t>() + q0 * n_ign : nullptr;
+            t.n_ign = n_ign;
+            error_model(resolve_prec(ix), ix->dtype, ix->dp, &t.eps_rel, &t.eps_abs);
+            t.gmax_norm2_bits = ix->gmax_bits;
+            t.ap = oA.as<double>() + q0; t.recall = oR.as<double>() + q0 * 3;
+            t.redo = (int32_t *)redo.p + q0; t.redo_count = (int32_t *)redo_cnt.p + ti;
+            VQ_TRY(launch_ap_rows_tc(t, st));
+            launches += 3;
+        }
+        VQ_CUDA(cudaMemcpyAsync(tile_redo.data(), redo_cnt.p, (size_t)ntile * 4, cudaMemcpyDeviceToHost, st));
+        VQ_CUDA(cudaStreamSynchronize(st));
+    }
+    bool any_redo = false;
+    for (int32_t r : tile_redo) any_redo |= r != 0;
+    ix->stats[4] = 0;
+    for (int32_t r : tile_redo) ix->stats[4] += use_tc ? r : 0;  // queries handed back to the canonical path
+    // positives spread through the bulk of the list (labels unrelated to the features): the eps bands cover too much of
+    // the gallery for the tensor-core form to pay -- later calls on this index go straight to the canonical path
+    if (use_tc && ix->stats[4] * 4 > nq) ix->tc_eval_off = true;
+    for (int attempt = 0; attempt < 2 && any_redo; ++attempt) {
         const int pcap2 = attempt == 0 ? 1024 : kMaxPositives;
         VQ_CUDA(cudaMemsetAsync(ovf.p, 0, 4, st));
-        for (int64_t q0 = 0; q0 < nq; q0 += tile_q) {
+        for (int64_t q0 = 0, ti = 0; q0 < nq; q0 += tile_q, ++ti) {
+            if (!tile_redo[(size_t)ti]) continue;
             const int64_t tq = std::min(tile_q, nq - q0);
             const char *qt = (const char *)q.dev + (size_t)q0 * ix->d * esize(dtype);
             VQ_TRY(launch_l2sq_all(qt, ix->raw, dtype, tq, ix->n, ix->d, (float *)d2.p, st));

@@ -281,6 +281,26 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                     if (PAIR) mbar_arrive_cluster(tempty_leader + 8u * as);  // it waits on the leader's barrier
                     else mbar_arrive(&tempty_bar[as]);
                 }
+                if (p.store) {
+                    // STORE mode (full-list evaluators): the coarse scores themselves, 2 * acc = 2<q,g> - |g|^2, go to
+                    // store[q, j]; no candidate handling.  A thread writes its row's 32 columns as eight 16-byte stores
+                    // (one full 128-byte line per row and step).
+                    if (qvalid) {
+                        float *dst = p.store + q * p.store_ld + j0 + ch * 32;
+                        if (ncols == BN && ((p.store_ld & 3) == 0)) {
+#pragma unroll
+                            for (int i = 0; i < 32; i += 4)
+                                *reinterpret_cast<float4 *>(dst + i) =
+                                    make_float4(2.0f * __uint_as_float(r[i]), 2.0f * __uint_as_float(r[i + 1]),
+                                                2.0f * __uint_as_float(r[i + 2]), 2.0f * __uint_as_float(r[i + 3]));
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 32; ++i)
+                                if (ch * 32 + i < ncols) dst[i] = 2.0f * __uint_as_float(r[i]);
+                        }
+                    }
+                    continue;
+                }
                 if (ncols < BN) {  // columns past the chunk end (zero-filled operands) can never qualify
                     if (ch * 32 >= ncols) continue;
 #pragma unroll

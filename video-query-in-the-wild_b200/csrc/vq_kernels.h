@@ -47,6 +47,8 @@ struct GemmTopkParams {
     const int32_t *q_ignore;     // device [nq, n_ign] or null
     int n_ign;
     int kprime;
+    float *store;       // STORE mode: coarse scores out [nq, store_ld] (or null: top-k pre-filter mode)
+    int64_t store_ld;
     int dbg_no_insert;  // debug hook NO_INSERT
     int trigger;        // list fill level that triggers an intermediate compaction (0: 2 k')
     int dense_rows;  // rows of a warp with candidates in one 32-column step from which every thread scans its own row
@@ -172,6 +174,20 @@ struct ApRowsParams {
     int64_t nseg;
     int64_t *n_kept;             // [nq_tile] or null
 };
+// tensor-core form of the trimmed / clip evaluation (vq_metrics.cu: ap_rows_tc_kernel)
+struct ApTcParams {
+    int64_t nq_tile, n, ld;
+    int d, dtype;
+    const float *coarse;         // [nq_tile, ld] coarse scores 2<q,g> - |g|^2 (gemm_topk STORE mode)
+    const void *q, *g;           // original rows (canonical re-scoring)
+    const int32_t *g_label, *g_video, *q_label, *q_ignore;
+    int n_ign;
+    float eps_rel, eps_abs;      // |coarse - (|q|^2 - d2)| <= eps_rel*|q|*gmax + eps_abs*(|q|^2 + gmax^2)
+    const uint32_t *gmax_norm2_bits;
+    double *ap, *recall;
+    int32_t *redo, *redo_count;  // queries (tile-relative) the canonical path has to evaluate
+};
+int launch_ap_rows_tc(const ApTcParams &p, cudaStream_t st);
 struct MomentNmsParams {
     int64_t nq_tile, n, nseg;
     const float *d2;             // [nq_tile, n] canonical

@@ -365,6 +365,290 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// ap_rows_tc: the trimmed / clip evaluation on TENSOR-CORE scores.  Input: the coarse score row c[j] = 2<q,g> - |g|^2
+// of a query (gemm_topk STORE mode; |c - (|q|^2 - d2)| <= eps, the proven bound of vq_api_search.inl:error_model).
+// AP and R@N need, for every positive p, the number of survivors ahead of it in the CANONICAL (d2, row) order:
+//   * the positives' canonical d2 come from a gather of their rows (P of them, ~n / classes);
+//   * a non-positive survivor whose coarse distance e = |q|^2 - c is more than eps away from every positive's d2 falls
+//     into a definite gap between two positives: one counter increment, no canonical arithmetic;
+//   * the others -- within eps of some positive, or within 2 eps of the largest coarse distance (the forced last
+//     positive of :434 is the canonically LAST survivor) -- are queued, re-scored canonically (gather) and placed exactly.
+// With class-structured features the queue holds ~1 % of the gallery; a query whose queue or positive list overflows
+// is reported in `redo` and evaluated by the canonical all-pairs path.  Results are the same numbers as ap_rows_kernel.
+// ---------------------------------------------------------------------------------------------------------------
+static constexpr int kTcThreads = 128, kTcPos = 512, kTcAmb = 1024;  // 56 KB of shared memory per block: four blocks per SM
+
+template <typename T>
+__global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams p) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    uint64_t *pos = (uint64_t *)sm;                       // [kTcPos] exact keys of the positives (sorted), then + forced last
+    uint64_t *ambk = pos + kTcPos;                        // [kTcAmb] exact keys of the queued survivors
+    unsigned long long *lastp = (unsigned long long *)(ambk + kTcAmb);  // [2] key of the canonically last survivor (+ pad)
+    float *qs = (float *)(lastp + 2);                     // [d rounded up to 4] 16-byte aligned: read as float4
+    uint32_t *ambr = (uint32_t *)(qs + ((p.d + 3) & ~3)); // [kTcAmb] rows of the queued survivors
+    uint32_t *posr = ambr + kTcAmb;                       // [kTcPos] rows of the positives (before their keys exist)
+    int *gap = (int *)(posr + kTcPos);                    // [kTcPos + 2] non-positive survivors between positives i-1 and i (by d2)
+    int *eqc = gap + kTcPos + 2;                          // [kTcPos + 1] ... of which with d2 equal to positive i's
+    int *part = eqc + kTcPos + 1;                         // [40]
+    int *misc = part + 40;                                // [0] npos [1] nvalid [2] namb [3] bad [4] cmin bits [5..7] topn  [8..16) ignore
+    uint8_t *tile = (uint8_t *)((((uintptr_t)(misc + 16)) + 127) & ~(uintptr_t)127);  // [warps][kRescoreTileBytes]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int64_t q = blockIdx.x;
+    const float *row = p.coarse + q * p.ld;
+    const int ql = p.q_label[q];
+    const int n_ign = p.q_ignore ? p.n_ign : 0;
+    const T *qrow = (const T *)p.q + q * p.d;
+    for (int i = tid; i < p.d; i += kTcThreads) qs[i] = to_f32<T>(qrow[i]);
+    if (tid < kMaxIgnore) misc[8 + tid] = tid < n_ign ? p.q_ignore[q * p.n_ign + tid] : -1;
+    if (tid < 8) misc[tid] = tid == 4 ? -1 : 0;  // [4]: ordered-uint image of the smallest coarse score, starts at the maximum
+    for (int i = tid; i < kTcPos + 2; i += kTcThreads) gap[i] = 0;
+    for (int i = tid; i < kTcPos + 1; i += kTcThreads) eqc[i] = 0;
+    __syncthreads();
+    const int *ign = misc + 8;
+    float qn = 0.f;
+    for (int i = tid; i < p.d; i += kTcThreads) qn = fmaf(qs[i], qs[i], qn);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) qn += __shfl_xor_sync(0xffffffffu, qn, o);
+    if (lane == 0) part[32 + warp] = __float_as_int(qn);
+    __syncthreads();
+    qn = 0.f;
+    for (int w = 0; w < kTcThreads / 32; ++w) qn += __int_as_float(part[32 + w]);
+    const float gmax2 = __uint_as_float(*p.gmax_norm2_bits);
+    const float eps = p.eps_rel * sqrtf(qn) * sqrtf(gmax2) + p.eps_abs * (qn + gmax2);
+
+    // Both passes stream the row four columns per thread with every load of a step issued up front (16-byte loads of
+    // the score, video and label columns): one block is alone with its row, so what bounds a pass is the number of
+    // loads in flight (the first version walked column by column with dependent loads: 4.4 ms for 4 096 queries).
+    const bool vec4 = ((((uintptr_t)p.coarse) | ((uintptr_t)p.g_label) | ((uintptr_t)p.g_video)) & 15) == 0 && (p.ld & 3) == 0;
+    const int64_t n4 = vec4 ? (p.n & ~(int64_t)3) : 0;
+    auto scan_row = [&](auto &&body) {  // body(j, coarse, video, label)
+        for (int64_t j = (int64_t)tid * 4; j < n4; j += kTcThreads * 8) {
+            const int64_t j2 = j + kTcThreads * 4;
+            const bool two = j2 < n4;
+            const float4 r4 = *reinterpret_cast<const float4 *>(row + j);
+            const int4 v4 = n_ign ? __ldg(reinterpret_cast<const int4 *>(p.g_video + j)) : make_int4(0, 0, 0, 0);
+            const int4 l4 = __ldg(reinterpret_cast<const int4 *>(p.g_label + j));
+            const float4 s4 = two ? *reinterpret_cast<const float4 *>(row + j2) : make_float4(0.f, 0.f, 0.f, 0.f);
+            const int4 w4 = two && n_ign ? __ldg(reinterpret_cast<const int4 *>(p.g_video + j2)) : make_int4(0, 0, 0, 0);
+            const int4 m4 = two ? __ldg(reinterpret_cast<const int4 *>(p.g_label + j2)) : make_int4(0, 0, 0, 0);
+            body(j, r4.x, v4.x, l4.x);
+            body(j + 1, r4.y, v4.y, l4.y);
+            body(j + 2, r4.z, v4.z, l4.z);
+            body(j + 3, r4.w, v4.w, l4.w);
+            if (two) {
+                body(j2, s4.x, w4.x, m4.x);
+                body(j2 + 1, s4.y, w4.y, m4.y);
+                body(j2 + 2, s4.z, w4.z, m4.z);
+                body(j2 + 3, s4.w, w4.w, m4.w);
+            }
+        }
+        for (int64_t j = n4 + tid; j < p.n; j += kTcThreads) body(j, row[j], n_ign ? p.g_video[j] : 0, p.g_label[j]);
+    };
+    // ---- pass 1: survivors, positives, smallest coarse score ----
+    int nvalid_t = 0;
+    float cmin_t = INFINITY;
+    scan_row([&](int64_t j, float c, int vid, int lab) {
+        if (n_ign && is_ignored(vid, ign, n_ign)) return;
+        ++nvalid_t;
+        cmin_t = fminf(cmin_t, c);
+        if (lab == ql) {
+            const int slot = atomicAdd(&misc[0], 1);
+            if (slot < kTcPos - 1) posr[slot] = (uint32_t)j;
+        }
+    });
+    atomicAdd(&misc[1], nvalid_t);
+    // float min through the ordered-uint image (coarse scores may be negative)
+    atomicMin((unsigned int *)&misc[4], f32_to_ordered(cmin_t));
+    __syncthreads();
+    const int ntrue = misc[0], nvalid = misc[1];
+    if (nvalid == 0) {  // the reference would raise on y_true[-1] of an empty list
+        if (tid == 0) {
+            p.ap[q] = 0.0;
+            p.recall[q * 3] = p.recall[q * 3 + 1] = p.recall[q * 3 + 2] = 0.0;
+        }
+        return;
+    }
+    if (ntrue > kTcPos - 1) {  // uniform: the canonical path takes this query
+        if (tid == 0) p.redo[atomicAdd(p.redo_count, 1)] = (int32_t)q;
+        return;
+    }
+    const float cmin = ordered_to_f32((unsigned int)misc[4]);
+    const float emax = qn - cmin;  // largest coarse distance of a survivor
+    const bool tiled = ((size_t)p.d * sizeof(T)) % 128 == 0 && (((uintptr_t)p.g) & 15) == 0;
+    uint8_t *wtile = tile + warp * kRescoreTileBytes;
+    auto rescore = [&](const uint32_t *rows, uint64_t *keys, int cnt) {  // canonical (d2, row) keys of gathered rows
+        if (tiled) {
+            for (int i0 = warp * 32; i0 < cnt; i0 += kTcThreads) {
+                const int i = i0 + lane;
+                const uint32_t r = rows[i < cnt ? i : i0];
+                const float d2 = warp_canon_d2_rows<T>(qs, (const T *)p.g + (int64_t)r * p.d, p.d, wtile, lane);
+                if (i < cnt) keys[i] = make_key_asc(d2, r);
+            }
+        } else {
+            for (int i = tid; i < cnt; i += kTcThreads)
+                keys[i] = make_key_asc(canon_d2_row<T>(qs, (const T *)p.g + (int64_t)rows[i] * p.d, p.d), rows[i]);
+        }
+    };
+    // ---- the positives' canonical keys, sorted ----
+    const int n2p = next_pow2(ntrue + 1);
+    for (int i = ntrue + tid; i < n2p; i += kTcThreads) pos[i] = ~0ull;
+    rescore(posr, pos, ntrue);
+    __syncthreads();
+    block_bitonic_sort(pos, n2p);
+    auto posd = [&](int i) { return (uint32_t)(pos[i] >> 32); };  // ordered image of positive i's d2
+
+    // ---- pass 2: every non-positive survivor either falls into a definite gap or is queued ----
+    int tail_t = 0;
+    const uint32_t last_pos_o = ntrue > 0 ? posd(ntrue - 1) : 0u;
+    scan_row([&](int64_t j, float c, int vid, int lab) {
+        if (lab == ql) return;
+        if (n_ign && is_ignored(vid, ign, n_ign)) return;
+        const float e = qn - c;
+        bool queue = e >= emax - 2.0f * eps;  // could be the canonically last survivor
+        int lb = 0;
+        if (!queue) {
+            const uint32_t lo_o = f32_to_ordered(e - eps), hi_o = f32_to_ordered(e + eps);
+            if (lo_o > last_pos_o) {  // behind every positive (the bulk of a class-structured gallery): no search, no atomic
+                ++tail_t;
+                return;
+            }
+            int lo = 0, hi = ntrue;  // first positive with d2 >= e - eps
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (posd(mid) < lo_o) lo = mid + 1; else hi = mid;
+            }
+            lb = lo;
+            queue = lb < ntrue && posd(lb) <= hi_o;  // a positive inside [e - eps, e + eps]
+        }
+        if (!queue) {
+            atomicAdd(&gap[lb], 1);
+        } else {
+            const int slot = atomicAdd(&misc[2], 1);
+            if (slot < kTcAmb) ambr[slot] = (uint32_t)j;
+        }
+    });
+    if (tail_t) atomicAdd(&gap[ntrue], tail_t);
+    __syncthreads();
+    const int namb = misc[2];
+    if (namb > kTcAmb) {  // uniform
+        if (tid == 0) p.redo[atomicAdd(p.redo_count, 1)] = (int32_t)q;
+        return;
+    }
+    rescore(ambr, ambk, namb);
+    __syncthreads();
+    // ---- the last survivor in canonical order (forced positive, AP only) ----
+    unsigned long long lk = 0ull;
+    for (int i = tid; i < namb; i += kTcThreads) lk = ambk[i] > lk ? ambk[i] : lk;
+    if (tid == 0) *lastp = ntrue > 0 ? pos[ntrue - 1] : 0ull;
+    __syncthreads();
+    atomicMax(lastp, lk);
+    __syncthreads();
+    const uint64_t lastk = *lastp;
+    const bool last_is_true = ntrue > 0 && lastk == pos[ntrue - 1];
+    int npos = ntrue;
+    if (!last_is_true) {
+        if (tid == 0) pos[ntrue] = lastk;  // the largest key: the list stays sorted
+        npos = ntrue + 1;
+    }
+    __syncthreads();
+    // ---- queued survivors: exact place among the positives (by d2), ties noted ----
+    for (int i = tid; i < namb; i += kTcThreads) {
+        const uint64_t k = ambk[i];
+        if (!last_is_true && k == lastk) continue;  // promoted to a positive
+        const uint32_t s = (uint32_t)(k >> 32);
+        int lo = 0, hi = npos;  // first positive with d2 >= mine
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (posd(mid) < s) lo = mid + 1; else hi = mid;
+        }
+        atomicAdd(&gap[lo], 1);
+        if (lo < npos && posd(lo) == s) atomicAdd(&eqc[lo], 1);
+    }
+    __syncthreads();
+    // inclusive scan: gap[i] = non-positive survivors with d2 < positive i's d2, or equal to it when i starts its tie group
+    if (warp == 0) {
+        int run = 0;
+        for (int c0 = 0; c0 <= npos; c0 += 32) {
+            const int v = c0 + lane <= npos ? gap[c0 + lane] : 0;
+            int inc = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += u;
+            }
+            if (c0 + lane <= npos) gap[c0 + lane] = run + inc;
+            run += __shfl_sync(0xffffffffu, inc, 31);
+        }
+    }
+    __syncthreads();
+    // ---- AP over tie groups (float64, sklearn's order of operations): the groups' terms in parallel -- the divisions --,
+    // then ONE thread adds them up in list order (the sum is what has an order; a non-final entry of a group adds +0.0) ----
+    double *term = (double *)ambr;  // the queued rows are no longer needed: [kTcPos] doubles fit (kTcAmb * 4 bytes)
+    for (int i = tid; i < npos; i += kTcThreads) {
+        const uint32_t t = posd(i);
+        double v = 0.0;
+        if (i == npos - 1 || posd(i + 1) != t) {  // last positive of its tie group
+            int f = i;
+            while (f > 0 && posd(f - 1) == t) --f;
+            const double P = (double)npos, tps = (double)(i + 1);
+            const double jcount = (double)gap[f] + tps;  // survivors with d2 <= t: non-positives incl. ties + positives so far
+            const double recall = tps / P, prev = f > 0 ? (double)f / P : 0.0;
+            v = (recall - prev) * (tps / jcount);
+        }
+        term[i] = v;
+    }
+    __syncthreads();
+    double apv = 0.0;
+    if (tid == 0)
+        for (int i = 0; i < npos; ++i) apv += term[i];
+    // ---- R@N: exact rank of every TRUE positive under the (d2, row) order ----
+    for (int i = tid; i < ntrue; i += kTcThreads) {
+        const uint32_t t = posd(i);
+        int f = i;
+        while (f > 0 && posd(f - 1) == t) --f;
+        int ahead = gap[f] - eqc[f];  // non-positives with d2 < t
+        if (ahead + i >= 100) continue;
+        if (eqc[f] > 0) {  // non-positives with the same d2 and a lower row (rare): look them up among the queued keys
+            const uint64_t key = pos[i];
+            for (int a = 0; a < namb; ++a) {
+                const uint64_t k = ambk[a];
+                if ((uint32_t)(k >> 32) == t && k < key && !(!last_is_true && k == lastk)) ++ahead;
+            }
+        }
+        const int rank = ahead + i + 1;
+        if (rank <= 30) atomicAdd(&misc[5], 1);
+        if (rank <= 50) atomicAdd(&misc[6], 1);
+        if (rank <= 100) atomicAdd(&misc[7], 1);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        p.ap[q] = apv;
+        const double npos_true = (double)ntrue + 1e-10;  // :476
+        for (int r = 0; r < 3; ++r) p.recall[q * 3 + r] = (double)misc[5 + r] * 1.0 / npos_true;
+    }
+}
+
+size_t ap_rows_tc_smem(int d) {
+    return (size_t)kTcPos * 8 + (size_t)kTcAmb * 8 + 16 + (size_t)kTcAmb * 4 + (size_t)kTcPos * 4 + (size_t)(kTcPos + 2) * 4 +
+           (size_t)(kTcPos + 1) * 4 + (size_t)((d + 3) & ~3) * 4 + 40 * 4 + 16 * 4 + 128 + (size_t)(kTcThreads / 32) * kRescoreTileBytes + 64;
+}
+
+int launch_ap_rows_tc(const ApTcParams &p, cudaStream_t st) {
+    if (p.nq_tile == 0) return VQ_OK;
+    const size_t smem = ap_rows_tc_smem(p.d);
+    VQ_CHECK(smem <= 200 * 1024, VQ_ERR_CAPACITY, "ap_rows_tc: dimension %d too large", p.d);
+    if (p.dtype == VQ_F32) {
+        VQ_CUDA(cudaFuncSetAttribute(ap_rows_tc_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ap_rows_tc_kernel<float><<<(unsigned)p.nq_tile, kTcThreads, smem, st>>>(p);
+    } else {
+        VQ_CUDA(cudaFuncSetAttribute(ap_rows_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ap_rows_tc_kernel<__nv_bfloat16><<<(unsigned)p.nq_tile, kTcThreads, smem, st>>>(p);
+    }
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
 static size_t ap_rows_smem(int pcap2) {
     return (size_t)pcap2 * 8 + (size_t)(pcap2 + 1) * 4 + (size_t)pcap2 * 4 * 2 + (kApThreads + 1) * 4 + 16 * 4 + 16 +
            8 + 16 + 128 * 8 + 128 * 4 + 64;
