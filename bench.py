@@ -275,10 +275,11 @@ def aux_measurements(torch, vq):
     out["map_eval_cfg0"] = {"workload": "configs[0]: 4096 queries x 20480 gallery x 512-d f32, full-list AP + R@30/50/100",
                             "wall_ms": min(ts[1:]) * 1e3, "mAP": float(ap.double().mean().item()),
                             "pairs_per_s": nq * n / min(ts[1:]),
+                            "handed_back_to_canonical": ix.last_stats()["segments"],
                             "roofline": tc_roof(2.0 * nq * n * d, min(ts[1:]) * 1e3,
-                                                "2*Q*N*D against the burst bf16 peak as SURVEY.md 8d scores it; the evaluator "
-                                                "scores every pair with the canonical fp32 chain on the packed FFMA2/FADD2 "
-                                                "CUDA-core pipes (DESIGN.md 4.4 says why not tensor cores)")}
+                                                "2*Q*N*D against the burst bf16 peak as SURVEY.md 8d scores it, WHOLE evaluation "
+                                                "(3-pass split GEMM in STORE mode 0.31 ms = 3x these flops issued, then "
+                                                "ap_rows_tc: gathers + rank counting, not tensor work; DESIGN.md 4.4)")}
     # the same evaluation by the CPU port (oracle, all host threads) on a bounded sample of the queries
     try:
         from oracle import oracle as orc
@@ -505,8 +506,9 @@ def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512, tc_roof=None):
                                "AP@tIoU0.5, grouped R@30/50/100), %d queries" % (n, nq), "wall_ms": t * 1e3,
                                "ms_per_query": t * 1e3 / nq, "pairs_per_s": nq * n / t, "mAP": float(r[0].mean().item())}
     if tc_roof:
-        out["moment_eval_cfg2"]["roofline"] = tc_roof(2.0 * nq * n * d, t * 1e3, "whole evaluation (canonical scores on FFMA2/FADD2 + "
-                                                      "per-video NMS + AP) against the tensor peak, as SURVEY.md 8d scores it")
+        out["moment_eval_cfg2"]["roofline"] = tc_roof(2.0 * nq * n * d, t * 1e3, "whole evaluation (canonical scores on FFMA2/FADD2 CUDA-core pipes + "
+                                                      "per-video NMS + AP) against the tensor peak, as SURVEY.md 8d scores it; "
+                                                      "DESIGN.md 4.4 says why this one stays canonical")
     return out
 
 
