@@ -480,6 +480,70 @@ def test_eval_trimmed_many_exact_ties_near_the_top(vq):
     assert np.array_equal(top, topo)
 
 
+@pytest.mark.parametrize("bf16", [False, True])
+def test_eval_trimmed_tensor_core_form_equals_canonical(vq, bf16):
+    """The trimmed evaluation on tensor-core scores (gemm_topk STORE mode + ap_rows_tc) returns the numbers of the canonical
+    all-pairs evaluation bit for bit: class-structured features (few survivors near a positive), duplicate rows that tie
+    positives with non-positives, an ignore list, a gallery size that is not a multiple of 4."""
+    import torch
+    from vqwild_b200 import _lib as L
+    rng = np.random.default_rng(31)
+    n, d, nq, ncls = 5003, 128, 300, 40
+    label = rng.integers(0, ncls, n).astype(np.int32)
+    g = _emb(rng, n, d, ncls=ncls, labels=label)
+    g[200:230] = g[200]                        # 30 identical rows ...
+    label[200:215], label[215:230] = 3, 4      # ... half of them another class: positive / non-positive ties
+    video = (np.arange(n) // 2).astype(np.int32)
+    qrow = rng.choice(n, nq, replace=False)
+    qrow[:3] = [200, 216, 7]
+    q = np.ascontiguousarray(g[qrow])
+    ql = label[qrow].copy()
+    ign = np.stack([video[qrow]] + [rng.integers(0, n // 2, nq).astype(np.int32) for _ in range(4)], 1).astype(np.int32)
+    if bf16:
+        gt, qt = torch.from_numpy(g).cuda().bfloat16(), torch.from_numpy(q).cuda().bfloat16()
+        g, q = gt.float().cpu().numpy(), qt.float().cpu().numpy()
+    else:
+        gt, qt = g, q
+    ix = vq.IndexFlatL2(d)
+    ix.add(gt)
+    ix.set_meta(label, video)
+    ap, rec, _ = ix.eval_trimmed(qt, ql, ign)
+    handed_back = ix.last_stats()["segments"]
+    L.debug_set("NO_TC_EVAL", 1)
+    try:
+        ap_c, rec_c, _ = ix.eval_trimmed(qt, ql, ign)
+    finally:
+        L.debug_set("NO_TC_EVAL", 0)
+    to_np = lambda x: x.cpu().numpy() if hasattr(x, "cpu") else x  # noqa: E731
+    ap, rec, ap_c, rec_c = map(to_np, (ap, rec, ap_c, rec_c))
+    assert handed_back < nq // 4, handed_back            # the tensor-core form did the work
+    assert np.array_equal(ap, ap_c) and np.array_equal(rec, rec_c)
+    apo, reco, _, _ = orc.eval_trimmed(q, g, label, video, ql, ign)
+    np.testing.assert_allclose(ap, apo, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-12)
+
+
+def test_eval_trimmed_tensor_core_form_hands_back_and_switches_off(vq):
+    """Labels unrelated to the features: the eps bands around ~n / classes positives spread through the list cover too much
+    of the gallery; the queries are handed back to the canonical path (same numbers) and the index stops trying."""
+    rng = np.random.default_rng(32)
+    n, d, nq = 20000, 64, 64
+    g, q = _emb(rng, n, d), _emb(rng, nq, d)
+    label = rng.integers(0, 10, n).astype(np.int32)
+    video = np.arange(n, dtype=np.int32)
+    ql = rng.integers(0, 10, nq).astype(np.int32)
+    ix = vq.IndexFlatL2(d)
+    ix.add(g)
+    ix.set_meta(label, video)
+    ap, rec, _ = ix.eval_trimmed(q, ql, None)
+    assert ix.last_stats()["segments"] == nq             # 2000 positives per query: every list overflows
+    apo, reco, _, _ = orc.eval_trimmed(q, g, label, video, ql, np.full((nq, 1), -1, np.int32))
+    np.testing.assert_allclose(ap, apo, rtol=0, atol=1e-12)
+    np.testing.assert_allclose(rec, reco, rtol=0, atol=1e-12)
+    ap2, _, _ = ix.eval_trimmed(q, ql, None)
+    assert ix.last_stats()["segments"] == 0 and np.array_equal(ap, ap2)   # canonical path directly
+
+
 def test_average_precision_lists_golden(vq, golden):
     yts, yss, want = [], [], []
     off = 0

@@ -584,24 +584,26 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
     __syncthreads();
     // ---- AP over tie groups (float64, sklearn's order of operations): the groups' terms in parallel -- the divisions --,
     // then ONE thread adds them up in list order (the sum is what has an order; a non-final entry of a group adds +0.0) ----
-    double *term = (double *)ambr;  // the queued rows are no longer needed: [kTcPos] doubles fit (kTcAmb * 4 bytes)
+    double *dr = (double *)ambr;   // recall steps: the queued rows are no longer needed ([kTcPos] doubles = kTcAmb * 4 bytes)
+    double *pr = (double *)tile;   // precisions: neither are the re-scoring tiles
     for (int i = tid; i < npos; i += kTcThreads) {
         const uint32_t t = posd(i);
-        double v = 0.0;
+        double d_ = 0.0, p_ = 0.0;
         if (i == npos - 1 || posd(i + 1) != t) {  // last positive of its tie group
             int f = i;
             while (f > 0 && posd(f - 1) == t) --f;
             const double P = (double)npos, tps = (double)(i + 1);
             const double jcount = (double)gap[f] + tps;  // survivors with d2 <= t: non-positives incl. ties + positives so far
-            const double recall = tps / P, prev = f > 0 ? (double)f / P : 0.0;
-            v = (recall - prev) * (tps / jcount);
+            d_ = tps / P - (f > 0 ? (double)f / P : 0.0);
+            p_ = tps / jcount;
         }
-        term[i] = v;
+        dr[i] = d_;
+        pr[i] = p_;
     }
     __syncthreads();
     double apv = 0.0;
-    if (tid == 0)
-        for (int i = 0; i < npos; ++i) apv += term[i];
+    if (tid == 0)  // ap += (recall - prev) * precision, contracted to one fma per group as in ap_rows_kernel: same bits
+        for (int i = 0; i < npos; ++i) apv = fma(dr[i], pr[i], apv);
     // ---- R@N: exact rank of every TRUE positive under the (d2, row) order ----
     for (int i = tid; i < ntrue; i += kTcThreads) {
         const uint32_t t = posd(i);
