@@ -178,6 +178,19 @@ VQ_API int vq_average_precision(const int32_t *y_true, const double *y_score,
 VQ_API int vq_nms1d_segmented(const double *dets, const int64_t *offsets, int64_t nseg,
                               double thresh, uint8_t *keep, void *stream);
 
+/* vq_nms1d_segmented for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  No counterpart in the reference.
+ * Same kernel and result as vq_nms1d_segmented; its scratch (one byte per detection) is a file-scope device array
+ * of VQ_NMS1D_STATIC_MAX bytes that every GPU loading the library holds until exit (csrc/vq_noalloc.cu).  The call
+ * allocates nothing, copies nothing and synchronises nothing: dets, offsets (int64[nseg+1]) and keep must be DEVICE
+ * memory; total = offsets[nseg] is passed by the caller (the library does not read device memory on the host) and
+ * total > VQ_NMS1D_STATIC_MAX returns VQ_ERR_CAPACITY.  The first call on a device resolves the array's address
+ * (cudaGetSymbolAddress; a call with nseg == 0 does only that -- make it before a graph capture).  All calls on a
+ * device share the array: calls that overlap on the GPU race and must be ordered by the caller. */
+#define VQ_NMS1D_STATIC_MAX 1048576
+VQ_API int vq_nms1d_segmented_static(const double *dets, const int64_t *offsets, int64_t nseg, int64_t total,
+                                     double thresh, uint8_t *keep, void *stream);
+
 /* ------------------------------------------------------------------------------------
  * b4. Metric-learning loss (misc_utils/metric_learning_loss.py).
  *   vq_pdist            Sampler.pdist :276-289          A f32[B,d] -> dist f32[B,B]

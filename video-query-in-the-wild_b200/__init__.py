@@ -6,7 +6,7 @@ from ._lib import (PREC_AUTO, PREC_BF16, PREC_EXACT, PREC_SPLIT3, SO_PATH, VQ_BF
                    lib)
 from .index import IndexFlatL2, faiss_module
 from .metrics import (Average, average_precision_batch, average_precision_score, evaluation_metric,
-                      generate_multi_query, nms_cpu, nms_segmented, recall_at_k, ap_at_k)
+                      generate_multi_query, nms_cpu, nms_segmented, nms_segmented_static, recall_at_k, ap_at_k)
 from .retrieval import ARV_Retrieval, ARV_Retrieval_Clip, ARV_Retrieval_Moment, wordembed_topk
 
 

@@ -7,7 +7,7 @@ OUT="$HERE/../libvqwild.so"
 OBJ="$HERE/_obj"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC,-fvisibility=hidden"
-SRCS="vq_api vq_gemm_topk vq_select vq_sort vq_exact vq_prepare vq_metrics vq_triplet vq_triplet_tc vq_moment vq_windows vq_losses"
+SRCS="vq_api vq_gemm_topk vq_select vq_sort vq_exact vq_prepare vq_metrics vq_triplet vq_triplet_tc vq_moment vq_windows vq_losses vq_noalloc"
 mkdir -p "$OBJ"
 echo "$FLAGS $*" > "$OBJ/.flags.new"
 if ! cmp -s "$OBJ/.flags.new" "$OBJ/.flags"; then rm -f "$OBJ"/*.o; mv "$OBJ/.flags.new" "$OBJ/.flags"; fi

@@ -63,6 +63,24 @@ def nms_segmented(dets, offsets, thresh):
     return keep
 
 
+NMS1D_STATIC_MAX = 1048576  # VQ_NMS1D_STATIC_MAX (include/vqwild.h)
+
+
+def nms_segmented_static(dets, offsets, thresh, out=None):
+    """nms_segmented without any allocation inside the library (vq_nms1d_segmented_static: the scratch is a static
+    device array of NMS1D_STATIC_MAX bytes).  dets float64[total,3] and offsets int64[nseg+1] are CUDA tensors; `out`
+    (uint8[total], CUDA) is allocated here when the caller does not pass one.  Runs on the current stream, no sync;
+    calls that overlap on the GPU race on the shared scratch.  No counterpart in the reference."""
+    import torch
+    assert dets.is_cuda and offsets.is_cuda and dets.dtype == torch.float64 and offsets.dtype == torch.int64
+    total = dets.shape[0]
+    if out is None:
+        out = torch.empty(total, dtype=torch.uint8, device=dets.device)
+    L.check(L.lib().vq_nms1d_segmented_static(L.ptr(dets), L.ptr(offsets), C.c_int64(offsets.shape[0] - 1),
+                                              C.c_int64(total), C.c_double(thresh), L.ptr(out), L.stream_of(dets)))
+    return out
+
+
 def nms_cpu(dets, thresh):
     """Same contract as the reference's nms_cpu: indices into dets in descending-score order."""
     dets = np.ascontiguousarray(dets, dtype=np.float64).reshape(-1, 3)
