@@ -655,9 +655,10 @@ def _check_groups(vq, embs, labs, margin):
 
 
 @pytest.mark.parametrize("G,B,d,ncls", [(5, 256, 512, 64), (300, 64, 64, 8), (3, 100, 96, 10), (2, 256, 40, 32),
-                                        (4, 37, 132, 5)])
+                                        (4, 37, 132, 5), (310, 48, 96, 6)])
 def test_triplet_fused_shapes(vq, G, B, d, ncls):
-    """Fused tensor-core kernel (B <= 256, d % 4 == 0): ragged B / d, more groups than SMs."""
+    """Fused tensor-core kernel (B <= 256, d % 4 == 0): ragged B / d, more groups than SMs (a CTA's later groups run
+    their pass 1 interleaved with the previous group's pass 3; even and odd k-block counts)."""
     rng = np.random.default_rng(100 + B + d)
     labs = np.stack([rng.permutation(np.arange(B) % ncls) for _ in range(G)]).astype(np.int64)
     embs = np.stack([_emb(rng, B, d, ncls, labs[g], scale=(g % 2 == 0)) for g in range(G)])

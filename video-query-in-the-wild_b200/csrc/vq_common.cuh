@@ -112,6 +112,20 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
 }
+// The same wait with a suspend-time hint (ns): the thread sleeps in hardware until the phase completes or the hint
+// expires instead of re-polling shared memory every few cycles -- for warps that wait long (a producer on a full ring).
+__device__ __forceinline__ void mbar_wait_sleepy(uint64_t *bar, uint32_t parity, uint32_t hint_ns) {
+    uint32_t ok;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok)
+            : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+            : "memory");
+    } while (!ok);
+}
 
 // ---------------------------------------------------------------------------------------
 // PTX: TMA (cp.async.bulk.tensor) 2-D tile load, completion on an mbarrier

@@ -4,7 +4,8 @@
 //
 //   pass 1  TMA k-blocks [256 rows x 32 fp32] -> tcgen05.mma kind::tf32 Gram E E^T into TMEM
 //           (two M=128 x N=256 accumulators = all 512 TMEM columns); the row threads compute the
-//           canonical row norms from the same stages.
+//           canonical row norms from the same stages.  Only a CTA's first group runs this pass on its own: for
+//           later groups its k-blocks are interleaved with pass 3 of the group before (same ring).
 //   mine    thread = anchor reads its accumulator row (tcgen05.ld): coarse res = |a|^2+|j|^2-2G.
 //           The TF32 Gram is only a PRE-FILTER with a proven error bound eps: every j whose coarse
 //           value is within 2*eps of the coarse extreme stays a candidate (Sampler.pdist's clamps,
@@ -36,6 +37,7 @@ static constexpr int TSTAGES = 5;
 static constexpr int TROWT = 256;                 // row threads (warps 2..9)
 static constexpr int TTHREADS = 64 + TROWT;
 static constexpr int TCAND = 8;                   // candidates kept per role and anchor
+static constexpr uint32_t kTcSleepNs = 20000;   // suspend-time hint of the waits of the producer / MMA warp
 static constexpr int TEXTRA = 64;                 // candidate pairs beyond the first of a role, per warp
 
 struct TcLayout {
@@ -113,6 +115,16 @@ __device__ __forceinline__ float tc_sq4(float4 a, float4 b) {  // chunk chain of
     df = __fsub_rn(a.w, b.w); t = __fmaf_rn(df, df, t);
     return t;
 }
+__device__ __forceinline__ unsigned long long tc_sub2(unsigned long long a, unsigned long long b) {
+    unsigned long long r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ unsigned long long tc_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
 __device__ __forceinline__ float tc_dot4(float4 a, float4 b) {
     float t = __fmaf_rn(a.x, b.x, 0.f);
     t = __fmaf_rn(a.y, b.y, t);
@@ -175,23 +187,30 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
 
     if (warp == 0) {
         // ================================ TMA producer =================================
+        // Stream order per group: [pass 1 of the FIRST group only]  pass 2 (kb = 0..KB-1)  then pass 3 INTERLEAVED with
+        // pass 1 of this CTA's next group: P3(g, 0) P1(g', 0) P3(g, 1) P1(g', 1) ...  The next group's Gram (tensor
+        // pipe, HBM stream) and row norms are ready when this group's gradient rows are written.
         int stage = 0;
         uint32_t phase = 0;
+        auto load = [&](int g, int kb, uint64_t hint) {
+            mbar_wait_sleepy(&empty_bar[stage], phase ^ 1u, kTcSleepNs);
+            if (elect_one()) {
+                mbar_expect_tx(&full_bar[stage], TSTAGE);
+                tma_load_2d(&tm_e, &full_bar[stage], smem + stage * TSTAGE, kb * TKB, g * B, hint);
+            }
+            __syncwarp();
+            if (++stage == TSTAGES) {
+                stage = 0;
+                phase ^= 1u;
+            }
+        };
+        for (int kb = 0; kb < KB; ++kb) load(blockIdx.x, kb, kEvictLast);
         for (int g = blockIdx.x; g < p.G; g += gridDim.x) {
-            for (int pass = 0; pass < 3; ++pass) {
-                const uint64_t hint = pass == 2 ? kEvictFirst : kEvictLast;  // the rows are read again in the next pass
-                for (int kb = 0; kb < KB; ++kb) {
-                    mbar_wait(&empty_bar[stage], phase ^ 1u);
-                    if (elect_one()) {
-                        mbar_expect_tx(&full_bar[stage], TSTAGE);
-                        tma_load_2d(&tm_e, &full_bar[stage], smem + stage * TSTAGE, kb * TKB, g * B, hint);
-                    }
-                    __syncwarp();
-                    if (++stage == TSTAGES) {
-                        stage = 0;
-                        phase ^= 1u;
-                    }
-                }
+            const int gn = g + gridDim.x;
+            for (int kb = 0; kb < KB; ++kb) load(g, kb, kEvictLast);  // the rows are read again in pass 3
+            for (int kb = 0; kb < KB; ++kb) {
+                load(g, kb, kEvictFirst);
+                if (gn < p.G) load(gn, kb, kEvictLast);
             }
         }
     } else if (warp == 1) {
@@ -199,38 +218,49 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
         constexpr uint32_t idesc = umma_idesc_tf32(128, 256);
         int stage = 0;
         uint32_t phase = 0, tphase = 0;
-        for (int g = blockIdx.x; g < p.G; g += gridDim.x) {
-            mbar_wait(tempty_bar, tphase ^ 1u);  // the row threads have finished reading the previous Gram
+        auto advance = [&]() {
+            if (++stage == TSTAGES) {
+                stage = 0;
+                phase ^= 1u;
+            }
+        };
+        auto gram_block = [&](int kb) {  // one k-block of E E^T
+            mbar_wait_sleepy(&full_bar[stage], phase, kTcSleepNs);
+            tc_fence_after();
+            const uint32_t sa = smem_u32(smem + stage * TSTAGE);
+            const uint64_t d_top = umma_desc_sw128(sa), d_bot = umma_desc_sw128(sa + 128 * 128);
+            if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < TKB / 8; ++k) {  // K = 8 tf32 = 32 bytes per step
+                    umma_tf32(tmem_base, d_top + 2 * k, d_top + 2 * k, idesc, (kb | k) != 0);        // rows 0..127 x all
+                    umma_tf32(tmem_base + 256, d_bot + 2 * k, d_top + 2 * k, idesc, (kb | k) != 0);  // rows 128..255 x all
+                }
+                umma_commit(&empty_bar[stage]);
+                if (kb == KB - 1) umma_commit(tfull_bar);
+            }
+            __syncwarp();
+            advance();
+        };
+        auto pass_by = [&]() {  // a stage this warp does not read
+            mbar_wait_sleepy(&full_bar[stage], phase, kTcSleepNs);
+            if (lane == 0) mbar_arrive(&empty_bar[stage]);
+            __syncwarp();
+            advance();
+        };
+        auto gram_begin = [&]() {  // the row threads have finished reading the previous Gram
+            mbar_wait_sleepy(tempty_bar, tphase ^ 1u, kTcSleepNs);
             tphase ^= 1u;
             tc_fence_after();
-            for (int kb = 0; kb < KB; ++kb) {
-                mbar_wait(&full_bar[stage], phase);
-                tc_fence_after();
-                const uint32_t sa = smem_u32(smem + stage * TSTAGE);
-                const uint64_t d_top = umma_desc_sw128(sa), d_bot = umma_desc_sw128(sa + 128 * 128);
-                if (elect_one()) {
-#pragma unroll
-                    for (int k = 0; k < TKB / 8; ++k) {  // K = 8 tf32 = 32 bytes per step
-                        umma_tf32(tmem_base, d_top + 2 * k, d_top + 2 * k, idesc, (kb | k) != 0);        // rows 0..127 x all
-                        umma_tf32(tmem_base + 256, d_bot + 2 * k, d_top + 2 * k, idesc, (kb | k) != 0);  // rows 128..255 x all
-                    }
-                    umma_commit(&empty_bar[stage]);
-                    if (kb == KB - 1) umma_commit(tfull_bar);
-                }
-                __syncwarp();
-                if (++stage == TSTAGES) {
-                    stage = 0;
-                    phase ^= 1u;
-                }
-            }
-            for (int kb = 0; kb < 2 * KB; ++kb) {  // passes 2 and 3: this warp does not read the stages
-                mbar_wait(&full_bar[stage], phase);
-                if (lane == 0) mbar_arrive(&empty_bar[stage]);
-                __syncwarp();
-                if (++stage == TSTAGES) {
-                    stage = 0;
-                    phase ^= 1u;
-                }
+        };
+        gram_begin();
+        for (int kb = 0; kb < KB; ++kb) gram_block(kb);
+        for (int g = blockIdx.x; g < p.G; g += gridDim.x) {
+            const bool has_next = g + (int)gridDim.x < p.G;
+            for (int kb = 0; kb < KB; ++kb) pass_by();  // pass 2
+            if (has_next) gram_begin();
+            for (int kb = 0; kb < KB; ++kb) {            // pass 3, interleaved with the next group's pass 1
+                pass_by();
+                if (has_next) gram_block(kb);
             }
         }
     } else {
@@ -250,24 +280,28 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 phase ^= 1u;
             }
         };
+        // canonical |row|^2 partial of one k-block, from the stage the MMA reads
+        auto norm_block = [&](float acc) {
+            mbar_wait_sleepy(&full_bar[stage], phase, kTcSleepNs);
+            const uint8_t *sp = smem + stage * TSTAGE + row * 128;
+            float t[8];
+#pragma unroll
+            for (int cc = 0; cc < 8; ++cc) {
+                const float4 x = *reinterpret_cast<const float4 *>(sp + ((cc ^ sw) << 4));
+                t[cc] = tc_dot4(x, x);
+            }
+            acc = __fadd_rn(acc, tc_tree8(t));
+            next_stage();
+            return acc;
+        };
+        // ---------------- pass 1 of the first group (later groups: interleaved with the previous pass 3) ----------------
+        float na = 0.f;
+        for (int kb = 0; kb < KB; ++kb) na = norm_block(na);
         for (int g = blockIdx.x; g < p.G; g += gridDim.x) {
             const bool rvalid = row < B;
+            const bool has_next = g + (int)gridDim.x < p.G;
             long long tk[8];
             tk[0] = clock64();
-            // ---------------- pass 1: canonical |row|^2 from the stages the MMA reads ----------------
-            float na = 0.f;
-            for (int kb = 0; kb < KB; ++kb) {
-                mbar_wait(&full_bar[stage], phase);
-                const uint8_t *sp = smem + stage * TSTAGE + row * 128;
-                float t[8];
-#pragma unroll
-                for (int cc = 0; cc < 8; ++cc) {
-                    const float4 x = *reinterpret_cast<const float4 *>(sp + ((cc ^ sw) << 4));
-                    t[cc] = tc_dot4(x, x);
-                }
-                na = __fadd_rn(na, tc_tree8(t));
-                next_stage();
-            }
             tk[1] = clock64();
             s_nrm[row] = na;
             s_lab[row] = rvalid ? p.labels[(int64_t)g * B + row] : 0;
@@ -289,7 +323,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             const float eps = 4.2e-3f * sqrtf(na * nmax) + 1e-5f * (na + nmax);
 
             // ---------------- mine: coarse extremes, then candidates inside the band ----------------
-            mbar_wait(tfull_bar, tphase);
+            mbar_wait_sleepy(tfull_bar, tphase, kTcSleepNs);
             tphase ^= 1u;
             tc_fence_after();
             tk[2] = clock64();
@@ -388,21 +422,28 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 nex = 0;
             }
             if (__any_sync(0xffffffffu, bad) && lane == 0) s_misc[2] = 1;
-            if (nex > 0) {
+            if (nex > 0) {  // extra pair = swizzled chunk-0 byte offsets of the anchor row and the candidate row
+                auto base_of = [](uint32_t r) { return (r << 7) | ((r & 7u) << 4); };
                 int w = exoff;
-                for (int t = 1; t < ncp; ++t) s_tl[rw * TEXTRA + w++] = (uint32_t)row | ((uint32_t)((cpw >> (8 * t)) & 255u) << 8);
-                for (int t = 1; t < ncn; ++t) s_tl[rw * TEXTRA + w++] = (uint32_t)row | ((uint32_t)((cnw >> (8 * t)) & 255u) << 8);
+                for (int t = 1; t < ncp; ++t)
+                    s_tl[rw * TEXTRA + w++] = base_of((uint32_t)row) | (base_of((uint32_t)((cpw >> (8 * t)) & 255u)) << 16);
+                for (int t = 1; t < ncn; ++t)
+                    s_tl[rw * TEXTRA + w++] = base_of((uint32_t)row) | (base_of((uint32_t)((cnw >> (8 * t)) & 255u)) << 16);
             }
             const bool wvalid = __any_sync(0xffffffffu, avalid);
             __syncwarp();
 
             // ---------------- pass 2: canonical chains of the candidate pairs ----------------
-            // The 8 primaries a sub-group works on (lanes 4*i + m) give 32 partial sums per lane and k-block (4 chains x 8
-            // primaries), each to be summed over the 8 lanes in the oracle's tree order (c^4, c^2, c^1).  A transposing
-            // butterfly does that with 28 shuffles instead of 96: at every step a lane keeps the half of its values whose
-            // index bit matches its own lane bit and hands the other half to its partner.  Lane c ends up with the four
-            // sums of primary i = c, which it alone accumulates.  The swizzled stage offsets are k-block invariant.
-            float acc4[4] = {0.f, 0.f, 0.f, 0.f}, x_d[TEXTRA / 4], x_p[TEXTRA / 4];
+            // A sub-group of 8 lanes (lane c = 16-byte chunk c of a 128-byte row block) works on the primaries of lanes
+            // 4*i + m, four at a time ("half" h: i = 4h .. 4h+3): 16 partial sums per lane and half (4 primaries x 4
+            // chains), each to be summed over the 8 lanes in the oracle's tree order (c^4, c^2, c^1).  A transposing
+            // butterfly does that with 14 shuffles instead of 48: at every step a lane keeps the half of its values whose
+            // index bit matches its own lane bit and hands the other half to its partner.  Lane c ends up with two sums:
+            // primary 4h + (c >> 1), chains 2(c & 1) and 2(c & 1) + 1, which it alone accumulates over the k-blocks.
+            // Extra pairs go 16 to a step (4 per sub-group, 2 chains each): 7 shuffles, one sum per lane.
+            // The loads of half 0 of the NEXT k-block are issued before half 1 of this one is folded, so that a warp
+            // always has twelve 16-byte loads in flight under its arithmetic (the k-block barrier no longer drains it).
+            float accp[4] = {0.f, 0.f, 0.f, 0.f}, accx[TEXTRA / 16];
             uint32_t po[8], po2[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -413,52 +454,90 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 po2[i] = off(r2);
             }
 #pragma unroll
-            for (int i = 0; i < TEXTRA / 4; ++i) x_d[i] = x_p[i] = 0.f;
+            for (int i = 0; i < TEXTRA / 16; ++i) accx[i] = 0.f;
             const bool b4 = (c & 4) != 0, b2 = (c & 2) != 0, b1 = (c & 1) != 0;
+            const uint32_t cx2 = (uint32_t)c << 4;
+            const int nxs = (nex_total + 15) >> 4;  // steps of 16 extra pairs, warp-uniform
+            auto ld16 = [](const uint8_t *q) { return *reinterpret_cast<const float4 *>(q); };
+            auto load_half = [&](const uint8_t *sp, const int h, float4 (&xa)[4], float4 (&x1)[4], float4 (&x2)[4]) {
+#pragma unroll
+                for (int ii = 0; ii < 4; ++ii) {
+                    xa[ii] = ld16(sp + (po[4 * h + ii] & 0xffffu));
+                    x1[ii] = ld16(sp + (po[4 * h + ii] >> 16));
+                    x2[ii] = ld16(sp + po2[4 * h + ii]);
+                }
+            };
+            auto fold_half = [&](const float4 (&xa)[4], const float4 (&x1)[4], const float4 (&x2)[4], float &s0, float &s1) {
+                float v[16], w[8], u[4];
+#pragma unroll
+                for (int ii = 0; ii < 4; ++ii) {
+                    v[4 * ii] = tc_sq4(xa[ii], x1[ii]);
+                    v[4 * ii + 1] = tc_dot4(xa[ii], x1[ii]);
+                    v[4 * ii + 2] = tc_sq4(xa[ii], x2[ii]);
+                    v[4 * ii + 3] = tc_dot4(xa[ii], x2[ii]);
+                }
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    w[j] = __fadd_rn(b4 ? v[8 + j] : v[j], __shfl_xor_sync(0xffffffffu, b4 ? v[j] : v[8 + j], 4));
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    u[j] = __fadd_rn(b2 ? w[4 + j] : w[j], __shfl_xor_sync(0xffffffffu, b2 ? w[j] : w[4 + j], 2));
+                s0 = __fadd_rn(s0, __fadd_rn(b1 ? u[2] : u[0], __shfl_xor_sync(0xffffffffu, b1 ? u[0] : u[2], 1)));
+                s1 = __fadd_rn(s1, __fadd_rn(b1 ? u[3] : u[1], __shfl_xor_sync(0xffffffffu, b1 ? u[1] : u[3], 1)));
+            };
+            float4 xa[4], x1[4], x2[4];  // half 0 of the k-block at hand
+            if (wvalid) {
+                mbar_wait_sleepy(&full_bar[stage], phase, kTcSleepNs);
+                load_half(smem + stage * TSTAGE, 0, xa, x1, x2);
+            }
             for (int kb = 0; kb < KB; ++kb) {
-                mbar_wait(&full_bar[stage], phase);
+                mbar_wait_sleepy(&full_bar[stage], phase, kTcSleepNs);
                 const uint8_t *sp = smem + stage * TSTAGE;
                 if (wvalid) {
-                    float v[32];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {  // primary triple of lane 4*i + m
-                        const float4 xa = *reinterpret_cast<const float4 *>(sp + (po[i] & 0xffffu));
-                        const float4 x1 = *reinterpret_cast<const float4 *>(sp + (po[i] >> 16));
-                        const float4 x2 = *reinterpret_cast<const float4 *>(sp + po2[i]);
-                        v[4 * i] = tc_sq4(xa, x1);
-                        v[4 * i + 1] = tc_dot4(xa, x1);
-                        v[4 * i + 2] = tc_sq4(xa, x2);
-                        v[4 * i + 3] = tc_dot4(xa, x2);
+                    float4 ya[4], y1[4], y2[4];
+                    load_half(sp, 1, ya, y1, y2);
+                    fold_half(xa, x1, x2, accp[0], accp[1]);
+                    if (kb + 1 < KB) {  // half 0 of the next k-block (the stage after this one in the ring)
+                        const int ns = stage + 1 == TSTAGES ? 0 : stage + 1;
+                        mbar_wait_sleepy(&full_bar[ns], ns == 0 ? phase ^ 1u : phase, kTcSleepNs);
+                        load_half(smem + ns * TSTAGE, 0, xa, x1, x2);
                     }
-                    float w[16], u[8];
+                    fold_half(ya, y1, y2, accp[2], accp[3]);
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        w[j] = __fadd_rn(b4 ? v[16 + j] : v[j], __shfl_xor_sync(0xffffffffu, b4 ? v[j] : v[16 + j], 4));
+                    for (int s = 0; s < TEXTRA / 16; ++s) {
+                        if (s < nxs) {  // warp-uniform
+                            float x[8], w[4], u[2];
 #pragma unroll
-                    for (int j = 0; j < 8; ++j)
-                        u[j] = __fadd_rn(b2 ? w[8 + j] : w[j], __shfl_xor_sync(0xffffffffu, b2 ? w[j] : w[8 + j], 2));
+                            for (int ee = 0; ee < 4; ++ee) {
+                                const int idx = 16 * s + 4 * ee + m;
+                                const uint32_t e = idx < nex_total ? s_tl[rw * TEXTRA + idx] : 0u;
+                                const float4 za = ld16(sp + ((e & 0xffffu) ^ cx2)), zj = ld16(sp + ((e >> 16) ^ cx2));
+                                x[2 * ee] = tc_sq4(za, zj);
+                                x[2 * ee + 1] = tc_dot4(za, zj);
+                            }
 #pragma unroll
-                    for (int j = 0; j < 4; ++j)
-                        acc4[j] = __fadd_rn(acc4[j], __fadd_rn(b1 ? u[4 + j] : u[j], __shfl_xor_sync(0xffffffffu, b1 ? u[j] : u[4 + j], 1)));
+                            for (int j = 0; j < 4; ++j)
+                                w[j] = __fadd_rn(b4 ? x[4 + j] : x[j], __shfl_xor_sync(0xffffffffu, b4 ? x[j] : x[4 + j], 4));
 #pragma unroll
-                    for (int i = 0; i < TEXTRA / 4; ++i) {
-                        if (4 * i < nex_total) {  // warp-uniform
-                            const int idx = 4 * i + m;
-                            const uint32_t e = idx < nex_total ? s_tl[rw * TEXTRA + idx] : 0u;
-                            const int ra = e & 255u, r1 = (e >> 8) & 255u;
-                            const float4 xa = tc_ld_chunk(sp, ra, c), x1 = tc_ld_chunk(sp, r1, c);
-                            x_d[i] = __fadd_rn(x_d[i], tc_tree8_shfl(tc_sq4(xa, x1)));
-                            x_p[i] = __fadd_rn(x_p[i], tc_tree8_shfl(tc_dot4(xa, x1)));
+                            for (int j = 0; j < 2; ++j)
+                                u[j] = __fadd_rn(b2 ? w[2 + j] : w[j], __shfl_xor_sync(0xffffffffu, b2 ? w[j] : w[2 + j], 2));
+                            accx[s] = __fadd_rn(accx[s], __fadd_rn(b1 ? u[1] : u[0], __shfl_xor_sync(0xffffffffu, b1 ? u[0] : u[1], 1)));
                         }
                     }
                 }
                 next_stage();
             }
-            s_res[rw * 32 + 4 * c + m] = make_float4(acc4[0], acc4[1], acc4[2], acc4[3]);  // primary i = c is lane 4*c + m
+            {   // primary i = 4h + (c >> 1) belongs to lane 4i + m: (d2_p, prod_p | d2_n, prod_n), this lane holds one half
+                float *res = reinterpret_cast<float *>(s_res), *rex = reinterpret_cast<float *>(s_rex);
 #pragma unroll
-            for (int i = 0; i < TEXTRA / 4; ++i) {
-                const int idx = 4 * i + m;
-                if (c == 0 && idx < nex_total) s_rex[rw * TEXTRA + idx] = make_float2(x_d[i], x_p[i]);
+                for (int h = 0; h < 2; ++h)
+                    *reinterpret_cast<float2 *>(res + (rw * 32 + 4 * (4 * h + (c >> 1)) + m) * 4 + 2 * (c & 1)) =
+                        make_float2(accp[2 * h], accp[2 * h + 1]);
+#pragma unroll
+                for (int s = 0; s < TEXTRA / 16; ++s) {  // extra 16s + 4(c >> 1) + m: (d2, prod), one of the two per lane
+                    const int idx = 16 * s + 4 * (c >> 1) + m;
+                    if (idx < nex_total) rex[(rw * TEXTRA + idx) * 2 + (c & 1)] = accx[s];
+                }
             }
             __syncwarp();
             tk[4] = clock64();
@@ -606,44 +685,48 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             const int eb = piece(rw * 4 + m), ee = piece(rw * 4 + m + 1);
             const int nit = __reduce_max_sync(0xffffffffu, ee - eb);
             const uint32_t cx = (uint32_t)c << 4;
+            unsigned long long scale2;
+            asm("mov.b64 %0, {%1, %1};" : "=l"(scale2) : "r"(__float_as_uint(scale)));
+            float na_next = 0.f;
             for (int kb = 0; kb < KB; ++kb) {
-                mbar_wait(&full_bar[stage], phase);
+                mbar_wait_sleepy(&full_bar[stage], phase, kTcSleepNs);
                 if (p.grad) {
                     const uint8_t *sp = smem + stage * TSTAGE;
                     const int col = kb * TKB + c * 4;
-                    auto ldx = [&](uint32_t off) { return *reinterpret_cast<const float4 *>(sp + ((off & 0x7ff0u) ^ cx)); };
-                    // E <= 768 of the 1024 slots: reading two entries past a piece's end stays inside the array, and
+                    auto ldx = [&](uint32_t off) { return *reinterpret_cast<const ulonglong2 *>(sp + ((off & 0x7ff0u) ^ cx)); };
+                    // E <= 768 of the 1024 slots: reading three entries past a piece's end stays inside shared memory, and
                     // whatever is there only feeds loads inside the stage (offsets are masked) and a chain nobody stores
                     float *gb = p.grad + ((int64_t)g * B) * p.d + col;
                     const uint32_t rlim = col < p.d ? (uint32_t)B : 0u;
-                    uint2 en0 = s_en2[eb], en1 = s_en2[eb + 1];
-                    float4 xu0 = ldx(en0.x), xv0 = ldx(en0.x >> 16);
-                    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 2
+                    const uint2 *ep = s_en2 + eb;
+                    uint2 en0 = ep[0], en1 = ep[1], en2 = ep[2];
+                    ulonglong2 xu0 = ldx(en0.x), xv0 = ldx(en0.x >> 16), xu1 = ldx(en1.x), xv1 = ldx(en1.x >> 16);
+                    unsigned long long alo = 0ull, ahi = 0ull;  // packed fp32 pairs: FADD2 / FFMA2, same bits as the scalar chain
+#pragma unroll 3
                     for (int it = 0; it < nit; ++it) {
-                        const float4 xu1 = ldx(en1.x), xv1 = ldx(en1.x >> 16);
-                        const uint2 en2 = s_en2[eb + it + 2];
-                        acc.x = __fmaf_rn(scale, __fsub_rn(xu0.x, xv0.x), acc.x);
-                        acc.y = __fmaf_rn(scale, __fsub_rn(xu0.y, xv0.y), acc.y);
-                        acc.z = __fmaf_rn(scale, __fsub_rn(xu0.z, xv0.z), acc.z);
-                        acc.w = __fmaf_rn(scale, __fsub_rn(xu0.w, xv0.w), acc.w);
+                        const ulonglong2 xu2 = ldx(en2.x), xv2 = ldx(en2.x >> 16);  // loads run two entries ahead of the chain
+                        const uint2 en3 = ep[it + 3];
+                        alo = tc_fma2(scale2, tc_sub2(xu0.x, xv0.x), alo);
+                        ahi = tc_fma2(scale2, tc_sub2(xu0.y, xv0.y), ahi);
                         // straight-line tail: the four sub-groups of a warp finish their rows at different entries
                         const uint32_t r = en0.y & 255u;
                         const bool last = (en0.y & 256u) != 0u;
-                        float4 *dst = reinterpret_cast<float4 *>(gb + (size_t)(r * (uint32_t)p.d));
-                        if (last && eb + it < ee && r < rlim) *dst = acc;
-                        acc.x = last ? 0.f : acc.x;
-                        acc.y = last ? 0.f : acc.y;
-                        acc.z = last ? 0.f : acc.z;
-                        acc.w = last ? 0.f : acc.w;
-                        en0 = en1; xu0 = xu1; xv0 = xv1; en1 = en2;
+                        ulonglong2 *dst = reinterpret_cast<ulonglong2 *>(gb + (size_t)(r * (uint32_t)p.d));
+                        if (last && eb + it < ee && r < rlim) *dst = make_ulonglong2(alo, ahi);
+                        alo = last ? 0ull : alo;
+                        ahi = last ? 0ull : ahi;
+                        en0 = en1; xu0 = xu1; xv0 = xv1;
+                        en1 = en2; xu1 = xu2; xv1 = xv2;
+                        en2 = en3;
                     }
                 }
                 next_stage();
+                if (has_next) na_next = norm_block(na_next);  // pass 1 of this CTA's next group
             }
+            na = na_next;
             if (threadIdx.x == 64 && s_misc[2]) p.bad_list[atomicAdd(p.bad_count, 1)] = g;
             tk[6] = clock64();
-            if (p.dbg && threadIdx.x == 64 && g == (int)blockIdx.x)
+            if (p.dbg && threadIdx.x == 64 && g == (int)blockIdx.x + ((int)(blockIdx.x + gridDim.x) < p.G ? (int)gridDim.x : 0))  // steady state: the second group
                 for (int i = 0; i < 7; ++i) p.dbg[blockIdx.x * 8 + i] = tk[i];
             named_bar_sync(1, TROWT);  // shared lists are rebuilt by the next group
         }
@@ -690,7 +773,7 @@ int launch_triplet_batchhard(const float *emb, const int32_t *labels, int64_t G,
     if (p.dbg) {
         long long h[8];
         VQ_CUDA(cudaMemcpy(h, p.dbg, 64, cudaMemcpyDeviceToHost));
-        fprintf(stderr, "triplet_tc clocks (CTA 0, first group): pass1 %lld  wait_gram %lld  mine %lld  pass2 %lld  lists %lld  pass3 %lld\n",
+        fprintf(stderr, "triplet_tc clocks (CTA 0, its second group if it has one): pass1 %lld  wait_gram %lld  mine %lld  pass2 %lld  lists %lld  pass3 %lld\n",
                 h[1] - h[0], h[2] - h[1], h[3] - h[2], h[4] - h[3], h[5] - h[4], h[6] - h[5]);
     }
     // groups handed back (capacity overflow): CUDA-core path over the device list, a few resident blocks
