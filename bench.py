@@ -408,12 +408,17 @@ def sharded_map_eval(torch, dist, vq, ops, dev, G):
     ql = torch.from_numpy(label[qrow]).to(dev)
     igd = torch.from_numpy(video[qrow][:, None].astype(np.int32)).to(dev)
 
+    mid = []
+
     def eval_fn(q0, q1):
         ap, rec, _ = ix.eval_trimmed(qd[q0:q1].contiguous(), ql[q0:q1].contiguous(), igd[q0:q1].contiguous())
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        mid.append(e)
         return ap, rec
 
     best = None
-    for it in range(4):
+    for it in range(6):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         dist.barrier()
         torch.cuda.synchronize()
@@ -421,13 +426,15 @@ def sharded_map_eval(torch, dist, vq, ops, dev, G):
         ap, rec = ops.sharded_eval(eval_fn, nq)
         e1.record()
         torch.cuda.synchronize()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        # whole call and its local half (this rank's slice, before the all-gather), each as the max over ranks
+        ms = torch.tensor([e0.elapsed_time(e1), e0.elapsed_time(mid[-1])], device=dev)
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        if it > 0:
-            best = float(ms.item()) if best is None else min(best, float(ms.item()))
+        if it > 1 and (best is None or float(ms[0].item()) < best[0]):
+            best = ms.tolist()
     return {"workload": "configs[0]: 4096 queries x 20480 gallery x 512-d f32, full-list AP + R@30/50/100, queries sharded %d-way"
-            % G, "wall_ms": best, "mAP": float(ap.mean().item()), "pairs_per_s": nq * g.shape[0] / (best * 1e-3),
-            "timing": "CUDA events, max over ranks, best of 3 after 1 warm-up"}
+            % G, "wall_ms": best[0], "local_eval_ms": best[1], "mAP": float(ap.mean().item()),
+            "pairs_per_s": nq * g.shape[0] / (best[0] * 1e-3),
+            "timing": "CUDA events, max over ranks, best of 4 after 2 warm-ups; local_eval_ms = this rank's slice before the all-gather"}
 
 
 def aux_moment(torch, vq, nq=4096, V=20480, S=64, d=512, tc_roof=None):
@@ -561,10 +568,11 @@ def run_b200(a):
     xevents = []
 
     def step_device():
-        index.search(xq, k, out=(D, I))
         if G == 1:
+            index.search(xq, k, out=(D, I))
             return D, I
-        return ops.exchange_merge(D, I, r0, events=xevents)
+        # local search for the head of the shard's list (ops.local_k: 40 of 100 at 8 ranks), one all-gather, merge
+        return ops.sharded_search(index, xq, k, r0, n_global=a.n, events=xevents)
 
     xq_host = torch.empty(xq.shape, dtype=torch.bfloat16, pin_memory=True)
     xq_host.copy_(xq)
@@ -582,8 +590,7 @@ def run_b200(a):
                       file=sys.stderr)
             return Dh, Ih
         xd = xq_host.to(dev, non_blocking=True)
-        index.search(xd, k, out=(D, I))
-        Dm, Im = ops.exchange_merge(D, I, r0)
+        Dm, Im = ops.sharded_search(index, xd, k, r0, n_global=a.n)
         Dh.copy_(Dm, non_blocking=True)
         Ih.copy_(Im, non_blocking=True)
         torch.cuda.synchronize()
@@ -684,7 +691,7 @@ def run_b200(a):
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload_name(a), "nq": a.nq, "n": a.n, "d": a.d, "k": a.k,
-                   "parallelism": "gallery rows sharded %d-way, queries replicated, 1 all-gather of [Q,k] packed (d2,row) keys + merge" % G
+                   "parallelism": "gallery rows sharded %d-way, queries replicated, local top-%d (head of the shard's list), 1 all-gather of [Q,%d] packed (d2,row) keys + merge with completeness proof" % (G, ops.local_k(a.k, G), ops.local_k(a.k, G))
                    if G > 1 else "single GPU",
                    "l2_policy": "inputs larger than L2 (gallery shard %.1f GB per rank)" % ((r1 - r0) * a.d * 2 / 1e9),
                    "tie_break": "d2 ascending, lowest gallery row first", "result": "canonical fp32 d2, verified top-k"},

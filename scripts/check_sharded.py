@@ -36,6 +36,20 @@ for head in (80, 50):   # 50 = the mean share of a shard at 2 ranks: many heads 
     ok = ok and torch.equal(Ih, If) and torch.equal(Dh.view(torch.int32), Df.view(torch.int32))
     if rank == 0:
         print("head=%d: fell back to the full round: %s" % (head, bool(ops._head_failed)))
+# sharded_search with a head-only LOCAL search (forced head length at this world size): final at 80, at 50 the head
+# round is refused and the search is repeated for k entries -- same answer, and the refusal is remembered
+real_head_len = ops.head_len
+for head, want_fail in ((80, False), (50, True)):
+    ops._head_failed.clear()
+    ops.head_len = lambda k_, ws_: head
+    assert ops.local_k(k, world) == head
+    Ds, Is = vq.sharded_search(shard, xq, k, r0, n_global=n)
+    ok = ok and torch.equal(Is, If) and torch.equal(Ds.view(torch.int32), Df.view(torch.int32))
+    ok = ok and bool(ops._head_failed) == want_fail and ops.local_k(k, world) == (k if want_fail else head)
+    if rank == 0:
+        print("head-only local search, m=%d: repeated for k entries: %s" % (head, bool(ops._head_failed)))
+ops.head_len = real_head_len
+ops._head_failed.clear()
 flag = torch.tensor([1 if ok else 0], device=dev)
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:

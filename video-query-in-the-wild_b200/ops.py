@@ -123,6 +123,46 @@ def exchange_merge(D, I, row_offset, group=None, events=None, head=None):
     return out
 
 
+def local_k(k, ws):
+    """How many entries a rank asks of its own shard: only the head of its list (``head_len``) while the head exchange
+    works for this (k, world size) -- the merged top-k takes about k / ws entries from each shard, and a search for 40
+    instead of 100 neighbours keeps half as many candidates per query (k' 64 instead of 128: thresholds tighten sooner,
+    9 % less time on a 1.25 M-row shard) -- else k."""
+    m = head_len(k, ws)
+    return m if (m < k and not _head_failed.get((k, ws), False)) else k
+
+
+def exchange_heads(Dh, Ih, row_offset, k, group=None, events=None):
+    """One round on lists that ARE only heads (the local search asked for ``local_k`` entries): pack, ONE all-gather,
+    merge.  Returns (d2 [nq,k], global rows [nq,k]) when the merge is provably the global top-k on every query, else
+    None -- the caller searches again for k entries and runs ``exchange_merge`` (every rank sees the same gathered
+    heads, hence takes the same branch).  ``events``: receives four CUDA events (start, packed, gathered, merged)."""
+    import torch
+    import torch.distributed as dist
+    ws = dist.get_world_size(group)
+    nq, m = Dh.shape
+
+    def mark():
+        if events is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            events.append(e)
+
+    mark()
+    hk = topk_pack(Dh.contiguous(), Ih.contiguous(), row_offset)
+    mark()
+    gk = torch.empty((ws * nq, m), dtype=torch.int64, device=Dh.device)
+    dist.all_gather_into_tensor(gk, hk, group=group)
+    mark()
+    od, oi, inc = topk_merge_heads(gk.view(ws, nq, m), k)
+    mark()
+    if int(inc.item()) == 0:      # (one 4-byte read-back; identical on every rank)
+        return od, oi
+    if events is not None:
+        del events[-4:]
+    return None
+
+
 MAX_GLOBAL_ROWS = 1 << 32   # merge keys carry the global row in 32 bits
 
 
@@ -134,11 +174,13 @@ def check_global_rows(n_global):
         raise ValueError("row-sharded search supports at most 2^32 gallery rows in total, got %d" % int(n_global))
 
 
-def sharded_search(index, xq, k, row_offset, group=None, n_global=None, merge=None):
+def sharded_search(index, xq, k, row_offset, group=None, n_global=None, merge=None, events=None):
     """Row-sharded gallery: every rank searches its shard (`index` holds rows
-    [row_offset, row_offset + ntotal) of the global gallery), the per-rank top-k lists are
-    exchanged with ONE all-gather and merged on every rank.  xq: CUDA tensor (NCCL) or CPU
-    tensor / numpy (gloo tests call `merge_gathered` with an oracle-made local list).
+    [row_offset, row_offset + ntotal) of the global gallery), the per-rank lists are exchanged with ONE all-gather of
+    packed keys and merged on every rank.  On CUDA a rank first asks its shard only for the HEAD of its list
+    (``local_k``: 40 of 100 at 8 ranks); if the merged heads are not provably final for some query (a gallery ordered
+    by class, ...) the search is repeated for k entries, and later calls go there directly.
+    xq: CUDA tensor (NCCL) or CPU tensor / numpy (gloo tests call `merge_gathered` with an oracle-made local list).
     ``n_global``: total rows over all ranks; when omitted it is all-reduced (max of row_offset + ntotal)."""
     import torch
     import torch.distributed as dist
@@ -148,11 +190,20 @@ def sharded_search(index, xq, k, row_offset, group=None, n_global=None, merge=No
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
         n_global = int(t.item())
     check_global_rows(n_global)
+    if getattr(xq, "is_cuda", False):
+        ws = dist.get_world_size(group)
+        m = local_k(k, ws)
+        if m < k:
+            Dh, Ih = index.search(xq, m)
+            res = exchange_heads(Dh, Ih, row_offset, k, group, events)
+            if res is not None:
+                return res
+            _head_failed[(k, ws)] = True
     D, I = index.search(xq, k)
     D = torch.as_tensor(D)
     I = torch.as_tensor(I)
     if D.is_cuda:
-        return exchange_merge(D, I, row_offset, group)
+        return exchange_merge(D, I, row_offset, group, events)
     I = torch.where(I >= 0, I + int(row_offset), I)
     return merge_gathered(D, I, group, merge)
 
