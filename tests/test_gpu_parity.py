@@ -750,6 +750,43 @@ def test_topk_pack_merge_keys(vq):
     assert np.array_equal(oi, wi) and np.array_equal(od.view(np.uint32), wd.view(np.uint32))
 
 
+def test_head_only_local_search_is_the_head_of_the_full_list_and_merges_to_the_single_index_answer(vq):
+    """ops.sharded_search asks a shard only for local_k(k, G) neighbours: that list must be the first entries of the
+    shard's top-k list bit for bit (k' 64 instead of 128 inside the GEMM), and the merged heads must be the single-index
+    top-k with the completeness proof satisfied.  Four shards on one GPU, no collective."""
+    import torch
+    from vqwild_b200 import ops
+    rng = np.random.default_rng(21)
+    n, nq, d, k, G = 40000, 300, 64, 100, 4
+    g = rng.standard_normal((n, d)).astype(np.float32)
+    g[n - 3] = g[11]                                   # the same row on two shards: lower global row first
+    q = rng.standard_normal((nq, d)).astype(np.float32)
+    q[0] = g[11]
+    m = ops.head_len(k, G)
+    assert m == 56
+    ops._head_failed.clear()
+    assert ops.local_k(k, G) == m and ops.local_k(k, 2) == k
+    full = vq.IndexFlatL2(d)
+    full.add(g)
+    Df, If = full.search(q, k)
+    heads = []
+    for r in range(G):
+        r0, r1 = r * n // G, (r + 1) * n // G
+        sh = vq.IndexFlatL2(d)
+        sh.add(np.ascontiguousarray(g[r0:r1]))
+        Dk, Ik = sh.search(q, k)
+        Dm, Im = sh.search(q, m)
+        assert sh.last_stats()["kprime"] < 128
+        assert np.array_equal(Im, Ik[:, :m]) and np.array_equal(Dm.view(np.uint32), Dk[:, :m].view(np.uint32))
+        heads.append(ops.topk_pack(Dm, Im, r0))
+    od, oi, inc = ops.topk_merge_heads(np.stack(heads), k)
+    assert int(inc[0]) == 0
+    assert np.array_equal(oi, If) and np.array_equal(od.view(np.uint32), Df.view(np.uint32))
+    ops._head_failed[(k, G)] = True                    # a refused head round is remembered: the next search asks for k
+    assert ops.local_k(k, G) == k
+    ops._head_failed.clear()
+
+
 def test_topk_merge_heads_two_round_exchange(vq):
     """Round 1 of the exchange merges only the first m entries of every shard's list: final (and equal to the full merge)
     when every head reaches the merged k-th key, reported incomplete otherwise."""
