@@ -78,6 +78,9 @@ int launch_nms_masks(const int64_t *seg_start, const int32_t *small_list, int n_
     return VQ_OK;
 }
 
+static constexpr int kNmsRankPitch = 68;  // bytes per video of a batch: 17 words, so that the lanes' word loads of phase B hit 32 banks
+static constexpr int kNmsBatchBytes = 32 * kNmsRankPitch + 32 * 8 + 32 * 8 + 32;  // per warp: ranks | keep masks | first rows | lengths
+
 template <int NT, int CAP>
 __global__ void __launch_bounds__(256, NT == 32 ? 4 : 1) moment_nms_kernel(const MomentNmsParams p, const int32_t *__restrict__ seg_list,
                                                          int nlist, int per_group) {
@@ -94,11 +97,104 @@ __global__ void __launch_bounds__(256, NT == 32 ? 4 : 1) moment_nms_kernel(const
     const float *row = p.d2 + q * p.n;
     uint8_t *kept = p.kept + q * p.n;
     const int li0 = (blockIdx.x * GPB + gid) * per_group;
-    for (int li = li0; li < li0 + per_group; ++li) {
-        if (li >= nlist) break;  // uniform inside a group (NT == 256: one group per block)
+    // Videos of <= 64 moments with precomputed suppression masks, a batch of up to 32 per warp:
+    //   A  the WARP sorts one video after the other (two keys per lane, bitonic network on registers) and leaves the
+    //      ranked moment numbers in shared memory, one byte each;
+    //   B  LANE j walks video j of the batch: greedy NMS as bit arithmetic, dead |= sup[a] for every survivor a in ranked
+    //      order -- 64 dependent steps, but 32 videos per instruction instead of one (the walk was half of the
+    //      warp-per-video form's instructions);
+    //   C  the warp writes the survivor bytes of the batch, coalesced.
+    // A video of the list that does not qualify (65 .. 256 moments) takes the per-video path below.
+    static_assert(NT != 32 || kNmsBatchBytes <= GBYTES, "the batch arrays reuse the warp's sort / NMS arrays");
+    uint8_t *fbase = base;  // (the per-video path below runs after phase C of a batch and before phase A of the next)
+    uint8_t *b_rank = fbase;                                                          // [32][68] ranked moment numbers
+    unsigned long long *b_keep = (unsigned long long *)(fbase + 32 * kNmsRankPitch);   // [32] survivor masks
+    long long *b_s0 = (long long *)(b_keep + 32);                                     // [32] first row of the video
+    uint8_t *b_S = (uint8_t *)(b_s0 + 32);                                            // [32] moments (0: not in the batch)
+    const bool batched = NT == 32 && p.sup != nullptr;
+    for (int lb = li0; lb < li0 + per_group && lb < nlist; lb += (batched ? 32 : 1)) {
+      int li = lb;
+      if (batched) {
+        const int cnt = min(min(32, li0 + per_group - lb), nlist - lb);
+        __syncwarp();
+        for (int j = 0; j < cnt; ++j) {  // ---- A
+            const int v = seg_list[lb + j];
+            const int64_t s0 = p.seg_start[v];
+            const int S = (int)(p.seg_start[v + 1] - s0);
+            if (S == 0 || S > 64) {
+                if (t == 0) b_S[j] = 0;
+                if (S == 0 && t == 0) p.vbest[q * p.nseg + v] = ~0ull;
+                continue;
+            }
+            uint64_t k0 = t < S ? make_key_asc(row[s0 + t], (uint32_t)t) : ~0ull;
+            uint64_t k1 = t + 32 < S ? make_key_asc(row[s0 + t + 32], (uint32_t)(t + 32)) : ~0ull;
+            auto cx = [&](uint64_t &x, int jj, bool asc) {
+                const uint64_t o = __shfl_xor_sync(0xffffffffu, x, jj);
+                const bool takemin = ((t & jj) == 0) == asc;
+                x = ((o < x) == takemin) ? o : x;
+            };
+#pragma unroll
+            for (int k = 2; k <= 32; k <<= 1) {
+                const bool a0 = k < 32 ? (t & k) == 0 : true, a1 = k < 32 ? a0 : false;
+#pragma unroll
+                for (int jj = k >> 1; jj > 0; jj >>= 1) {
+                    cx(k0, jj, a0);
+                    cx(k1, jj, a1);
+                }
+            }
+            if (k1 < k0) {
+                const uint64_t tmp = k0;
+                k0 = k1;
+                k1 = tmp;
+            }
+#pragma unroll
+            for (int jj = 16; jj > 0; jj >>= 1) {
+                cx(k0, jj, true);
+                cx(k1, jj, true);
+            }
+            b_rank[j * kNmsRankPitch + t] = (uint8_t)k0;        // moment (index inside the video) at ranks t, t + 32;
+            b_rank[j * kNmsRankPitch + t + 32] = (uint8_t)k1;   // ranks >= S hold the pad key's low byte, never read
+            if (t == 0) {
+                b_S[j] = (uint8_t)S;
+                b_s0[j] = s0;
+                p.vbest[q * p.nseg + v] = (k0 & 0xffffffff00000000ull) | (uint64_t)(s0 + (uint32_t)k0);
+            }
+        }
+        __syncwarp();
+        {  // ---- B
+            const int S = t < cnt ? (int)b_S[t] : 0;
+            const int Smax = __reduce_max_sync(0xffffffffu, S);
+            const unsigned long long *sup = p.sup + (t < cnt && S ? b_s0[t] : 0);
+            const uint32_t *rk = (const uint32_t *)(b_rank + t * kNmsRankPitch);
+            unsigned long long dead = 0ull, keep = 0ull;
+            for (int r4 = 0; r4 < Smax; r4 += 4) {
+                const uint32_t four = rk[r4 >> 2];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const uint32_t a = (four >> (8 * e)) & 63u;
+                    if (r4 + e < S && !((dead >> a) & 1ull)) {
+                        keep |= 1ull << a;
+                        dead |= sup[a];
+                    }
+                }
+            }
+            b_keep[t] = keep;
+        }
+        __syncwarp();
+        for (int j = 0; j < cnt; ++j) {  // ---- C
+            const int S = b_S[j];
+            if (S == 0) continue;
+            const unsigned long long keep = b_keep[j];
+            uint8_t *kd = kept + b_s0[j];
+            if (t < S) kd[t] = (uint8_t)((keep >> t) & 1ull);
+            if (t + 32 < S) kd[t + 32] = (uint8_t)((keep >> (t + 32)) & 1ull);
+        }
+      }
+      for (; li < (batched ? lb + min(min(32, li0 + per_group - lb), nlist - lb) : lb + 1); ++li) {
         const int v = seg_list[li];
         const int64_t s0 = p.seg_start[v];
         const int S = (int)(p.seg_start[v + 1] - s0);
+        if (batched && S <= 64) continue;  // done above
         if (S == 0) {
             if (t == 0) p.vbest[q * p.nseg + v] = ~0ull;
             continue;
@@ -134,25 +230,6 @@ __global__ void __launch_bounds__(256, NT == 32 ? 4 : 1) moment_nms_kernel(const
             for (int j = 16; j > 0; j >>= 1) {
                 cx(k0, j, true);
                 cx(k1, j, true);
-            }
-            if (p.sup) {
-                // greedy NMS as bit arithmetic on the precomputed suppression masks (uniform across the warp): walk the
-                // ranks, a moment that is still alive is kept and kills what it overlaps
-                const unsigned long long m0 = t < S ? p.sup[s0 + t] : 0ull, m1 = t + 32 < S ? p.sup[s0 + t + 32] : 0ull;
-                const uint32_t i0 = (uint32_t)k0, i1 = (uint32_t)k1;  // moment (index inside the video) at ranks t, t + 32
-                unsigned long long dead = 0ull, keep = 0ull;
-                for (int r = 0; r < S; ++r) {
-                    const uint32_t a = r < 32 ? __shfl_sync(0xffffffffu, i0, r) : __shfl_sync(0xffffffffu, i1, r - 32);
-                    if (!((dead >> a) & 1ull)) {  // uniform
-                        keep |= 1ull << a;
-                        dead |= a < 32 ? __shfl_sync(0xffffffffu, m0, a) : __shfl_sync(0xffffffffu, m1, a - 32);
-                    }
-                }
-                if (t < S) kept[s0 + t] = (uint8_t)((keep >> t) & 1ull);
-                if (t + 32 < S) kept[s0 + t + 32] = (uint8_t)((keep >> (t + 32)) & 1ull);
-                const uint64_t kb = __shfl_sync(0xffffffffu, k0, 0);
-                if (t == 0) p.vbest[q * p.nseg + v] = (kb & 0xffffffff00000000ull) | (uint64_t)(s0 + (uint32_t)kb);
-                continue;
             }
             keys[t] = k0;
             keys[t + 32] = k1;
@@ -234,6 +311,7 @@ __global__ void __launch_bounds__(256, NT == 32 ? 4 : 1) moment_nms_kernel(const
         }
         for (int i = t; i < S; i += NT) kept[s0 + (uint32_t)keys[i]] = dead[i] ? 0 : 1;
         if (t == 0) p.vbest[q * p.nseg + v] = (keys[0] & 0xffffffff00000000ull) | (uint64_t)(s0 + (uint32_t)keys[0]);
+      }
     }
 }
 
@@ -241,7 +319,8 @@ int launch_moment_nms(const MomentNmsParams &p, const int32_t *small_list, int n
                       int n_large, cudaStream_t st) {
     if (p.nq_tile == 0) return VQ_OK;
     if (n_small > 0) {
-        constexpr int CAP = kMomentWarpCap, GB = CAP * 17, PER = 4;
+        constexpr int CAP = kMomentWarpCap, GB = CAP * 17;
+        const int PER = p.sup ? 32 : 4;  // with suppression masks a warp takes its videos in batches of 32
         const int blocks = (n_small + 8 * PER - 1) / (8 * PER);
         moment_nms_kernel<32, CAP><<<dim3((unsigned)blocks, (unsigned)p.nq_tile), 256, 8 * GB, st>>>(p, small_list, n_small, PER);
         VQ_CUDA(cudaGetLastError());
