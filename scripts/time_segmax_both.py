@@ -12,15 +12,18 @@ g = bench.gen_rows(torch, "g", 0, n, d, dev)
 for name, gg, qq in (("bf16", g, xq), ("f32", g.float(), xq.float())):
     ix = vq.IndexFlatL2(d); ix.add(gg); ix.set_segments(np.arange(0, n + 1, S, dtype=np.int64))
     ref = None
-    for hook in (0, 1):
-        L.debug_set("NO_VMAJOR", hook)
+    for label, hooks in (("unique arg-max: one score", {}), ("video-major re-scoring", {"NO_SEG_UNIQUE": 1}),
+                         ("per-query re-scoring", {"NO_VMAJOR": 1})):
+        for h in ("NO_SEG_UNIQUE", "NO_VMAJOR"):
+            L.debug_set(h, hooks.get(h, 0))
         for _ in range(3):
             Vv, R, D = ix.search_segmax(qq, 100)
         torch.cuda.synchronize()
         t = ix.last_timing()
-        cs = int(R.sum().item())
+        cs = (int(R.sum().item()), int(Vv.sum().item()), int(D.view(torch.int32).long().sum().item()))
         ref = cs if ref is None else ref
-        print("%-5s %-22s %s rows checksum %s" % (name, "per-query re-scoring" if hook else "video-major re-scoring",
-                                                  {k: round(v, 2) for k, v in t.items()}, "same" if cs == ref else "DIFFERENT"), flush=True)
-    L.debug_set("NO_VMAJOR", 0)
+        print("%-5s %-26s %s checksums %s fallback %d" % (name, label, {k: round(v, 2) for k, v in t.items()},
+                                                        "same" if cs == ref else "DIFFERENT", ix.last_stats()["fallback_queries"]), flush=True)
+    for h in ("NO_SEG_UNIQUE", "NO_VMAJOR"):
+        L.debug_set(h, 0)
     del ix

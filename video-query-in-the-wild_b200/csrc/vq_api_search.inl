@@ -233,6 +233,26 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     gp.dense_rows = 4;  // measured: scripts/ab_gemm.py, profiles/r01_ab_gemm_chain_dense.txt
     if (g_hooks.dense_rows >= 0) gp.dense_rows = g_hooks.dense_rows;  // A/B hook (33 = never)
     gp.cand = ix->cand; gp.cand_cnt = ix->cand_cnt; gp.cand_tau = ix->cand_tau; gp.cand_cum = ix->cand_cum;
+
+    SelectParams sp{};
+    sp.nq = nq; sp.n = ix->n; sp.d = ix->d; sp.dtype = dtype; sp.q = xq; sp.g = ix->raw;
+    error_model(prec, ix->dtype, ix->dp, &sp.eps_rel, &sp.eps_abs);
+    sp.gmax_norm2_bits = ix->gmax_bits;
+    // SEGMAX: the GEMM marks the (query, video) candidates whose coarse arg-max is not provably the exact best moment;
+    // all others are settled by one canonical score instead of the whole video (vq_select.cu)
+    Tmp amb, reps;
+    const bool seg_unique = segmax && !g_hooks.no_vmajor && !g_hooks.no_seg_unique && ix->n < (1ll << 31);
+    if (seg_unique) {
+        const int64_t nseg = (int64_t)ix->seg_start.size() - 1;
+        const int words = (int)((nseg + 31) / 32);
+        VQ_TRY(amb.alloc((size_t)nq * words * 4, st));
+        VQ_TRY(reps.alloc((size_t)nq * 4, st));
+        VQ_CUDA(cudaMemsetAsync(amb.p, 0, (size_t)nq * words * 4, st));
+        VQ_TRY(launch_segmax_row_eps(sp, (float *)reps.p, st));
+        ++launches;
+        gp.seg_amb = (uint32_t *)amb.p; gp.amb_words = words; gp.row_eps = (const float *)reps.p;
+        sp.seg_amb = (const uint32_t *)amb.p; sp.amb_words = words;
+    }
     VQ_CUDA(cudaEventRecord(ix->ev[1], st));
     if (pair) {
         VQ_TRY(launch_gemm_topk_pair(maps, gp, segmax, pl.n_cta, st));
@@ -242,13 +262,9 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     VQ_CUDA(cudaEventRecord(ix->ev[2], st));
     ++launches;
 
-    SelectParams sp{};
-    sp.nq = nq; sp.n = ix->n; sp.d = ix->d; sp.dtype = dtype; sp.q = xq; sp.g = ix->raw;
     sp.group_size = group_size; sp.group_segs = ix->plan_ints_dev + 2 * pl.nseg + pl.n_cta + 1;
     sp.segs_per_group = pl.n_chunks; sp.cand = ix->cand; sp.cand_cnt = ix->cand_cnt;
     sp.cand_tau = ix->cand_tau; sp.cand_cum = ix->cand_cum; sp.kprime = kprime; sp.k = k;
-    error_model(prec, ix->dtype, ix->dp, &sp.eps_rel, &sp.eps_abs);
-    sp.gmax_norm2_bits = ix->gmax_bits;
     sp.seg_of_row = segmax ? ix->seg_of_row : nullptr;
     sp.seg_start = segmax ? ix->seg_start_dev : nullptr;
     sp.out_d2 = D; sp.out_idx = I; sp.out_seg = seg_out;
@@ -258,7 +274,7 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
         const int64_t nseg = (int64_t)ix->seg_start.size() - 1;
         VQ_TRY(vm.alloc(select_vmajor_scratch_bytes(nq, kprime, nseg), st));
         VQ_TRY(launch_select_segmax_vmajor(sp, nseg, vm.p, st));
-        launches += 4;
+        launches += seg_unique ? 5 : 4;
     } else {
         VQ_TRY(launch_select(sp, st));
     }

@@ -227,8 +227,10 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
         // group-max state (SEGMAX), in accumulator (half-score) units
         int cur_seg = -2;
         float cur_maxh = -INFINITY;
+        float cur_sech = -INFINITY;  // runner-up of the current video among the elements looked at (p.seg_amb)
         uint32_t cur_arg = 0;
         bool grp_masked = false;
+        const float band = (SEGMAX && p.seg_amb && qvalid) ? p.row_eps[q] : 0.f;  // accumulator units: acc1 - acc2 > eps proves the order
         __syncwarp();
         if (p.n_ign > 0) {
             for (int t = 0; t < p.n_ign; ++t) ign[row * kMaxIgnore + t] = qvalid ? p.q_ignore[q * p.n_ign + t] : -1;
@@ -330,9 +332,20 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                     const int last = min(31, ncols - 1 - ch * 32);
                     const int seg_first = __shfl_sync(0xffffffffu, sgL, 0), seg_last = __shfl_sync(0xffffffffu, sgL, last);
                     auto flush_to = [&](int sg, int col) {
-                        if (cur_maxh > tauh && !grp_masked) append(2.0f * cur_maxh, cur_arg);
+                        if (cur_maxh > tauh && !grp_masked) {
+                            append(2.0f * cur_maxh, cur_arg);
+                            // The arg-max is the video's exact best moment if nothing else can reach it: the runner-up
+                            // of the inspected elements and every skipped element (all <= tau at the time, tau only
+                            // grows) lie more than the error band below.  Otherwise the video is marked.
+                            if (p.seg_amb && qvalid) {
+                                const float lim = cur_maxh - band;
+                                if (!(cur_sech < lim && tauh < lim))
+                                    atomicOr(p.seg_amb + q * p.amb_words + (cur_seg >> 5), 1u << (cur_seg & 31));
+                            }
+                        }
                         cur_seg = sg;
                         cur_maxh = -INFINITY;
+                        cur_sech = -INFINITY;
                         grp_masked = p.n_ign > 0 ? is_ignored(row, __ldg(p.col_video + j0 + col)) : false;
                     };
                     if ((bnd & ~1u) == 0u) {  // warp-uniform: the 32 columns belong to one video
@@ -341,8 +354,16 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                             int arg = 31;
 #pragma unroll
                             for (int i = 30; i >= 0; --i) arg = v[i] == m32 ? i : arg;
+                            if (p.seg_amb) {  // runner-up: the old maximum or the step's second (a duplicate of m32 counts)
+                                float t2 = -INFINITY;
+#pragma unroll
+                                for (int i = 0; i < 32; ++i) t2 = fmaxf(t2, i == arg ? -INFINITY : v[i]);
+                                cur_sech = fmaxf(fmaxf(cur_sech, cur_maxh), t2);
+                            }
                             cur_maxh = m32;
                             cur_arg = jbase + (uint32_t)(ch * 32 + arg);
+                        } else if (m32 > tauh) {
+                            cur_sech = fmaxf(cur_sech, m32);
                         }
                     } else if (m32 > tauh) {
 #pragma unroll
@@ -351,8 +372,11 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                             if (col < ncols) {  // warp-uniform
                                 if ((bnd >> i) & 1u) flush_to(__ldg(p.col_seg + j0 + col), col);
                                 if (v[i] > tauh && v[i] > cur_maxh) {
+                                    cur_sech = fmaxf(cur_sech, cur_maxh);
                                     cur_maxh = v[i];
                                     cur_arg = jbase + col;
+                                } else {
+                                    cur_sech = fmaxf(cur_sech, v[i]);
                                 }
                             }
                         }
@@ -407,7 +431,13 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
             }
         }
         if (SEGMAX) {
-            if (cur_maxh > tauh && !grp_masked) append(2.0f * cur_maxh, cur_arg);
+            if (cur_maxh > tauh && !grp_masked) {
+                append(2.0f * cur_maxh, cur_arg);
+                if (p.seg_amb && qvalid) {
+                    const float lim = cur_maxh - band;
+                    if (!(cur_sech < lim && tauh < lim)) atomicOr(p.seg_amb + q * p.amb_words + (cur_seg >> 5), 1u << (cur_seg & 31));
+                }
+            }
         }
         __syncwarp();
         // final compaction of this unit to exactly <= k' entries per row

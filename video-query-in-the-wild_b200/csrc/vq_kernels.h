@@ -10,7 +10,7 @@ namespace vq {
 // loaded and changed afterwards only through vq_debug_set() -- never getenv() on a search path.
 struct DebugHooks {
     int force_fallback = 0, no_pair = 0, no_chain = 0, dense_rows = -1, no_tc_triplet = 0, triplet_clocks = 0,
-        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0, no_vmajor = 0, no_nms_masks = 0;
+        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0, no_vmajor = 0, no_nms_masks = 0, no_seg_unique = 0;
 };
 extern DebugHooks g_hooks;
 
@@ -57,6 +57,12 @@ struct GemmTopkParams {
     int32_t *cand_cnt;  // [units][kTileM]
     float *cand_tau;    // [units][kTileM] everything not listed has coarse score <= tau (NaN until the unit is done)
     int32_t *cand_cum;  // [units][kTileM] 1: the list continues the predecessor's (it covers all earlier chunks of the row)
+    // SEGMAX, optional: which (query, video) candidates have a best moment that is NOT alone at the top -- some other
+    // moment of the video may lie within the error band of the coarse maximum (or could not be ruled out).  Every other
+    // candidate's exact best moment is the coarse arg-max and needs ONE canonical score instead of the whole video.
+    uint32_t *seg_amb;      // [nq][amb_words] bit v: video v is ambiguous for this query (zeroed by the caller) or null
+    int amb_words;
+    const float *row_eps;   // [nq] proven |coarse - (|q|^2 - d2)| bound of the row's scores
 };
 
 int launch_gemm_topk(const CUtensorMap *maps4, const GemmTopkParams &p, int npass, bool segmax,
@@ -110,7 +116,11 @@ struct SelectParams {
     int32_t *pair_m;         // [nq]
     float *pair_tau;         // [nq]
     int32_t *vcount;         // [nseg] pairs per video
+    const uint32_t *seg_amb; // [nq][amb_words] from the GEMM (GemmTopkParams::seg_amb) or null: every pair is re-scored in full
+    int amb_words;
+    int32_t *pair_one;       // [nq, kprime] arg-max row of a pair whose best moment is proven unique (-1 otherwise)
 };
+int launch_segmax_row_eps(const SelectParams &p, float *row_eps, cudaStream_t st);
 int launch_select(const SelectParams &p, cudaStream_t st);
 size_t select_vmajor_scratch_bytes(int64_t nq, int kprime, int64_t nseg);
 int launch_select_segmax_vmajor(SelectParams p, int64_t nseg, void *scratch, cudaStream_t st);

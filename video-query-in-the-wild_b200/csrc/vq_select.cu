@@ -134,12 +134,20 @@ __global__ void __launch_bounds__(kSelThreads) select_kernel(const SelectParams 
     if (SEGMAX && p.pair_vid) {
         // video-major re-scoring (below): hand the surviving (query, video) pairs over instead of re-scoring them here
         for (int i = tid; i < p.kprime; i += kSelThreads) {
-            int v = -1;
+            int v = -1, one = -1;
             if (i < m) {
-                v = p.seg_of_row[key_desc_idx(keys[i])];
-                atomicAdd(p.vcount + v, 1);
+                const uint32_t row = key_desc_idx(keys[i]);
+                v = p.seg_of_row[row];
+                // the GEMM proved the coarse arg-max alone at the top of its video: one canonical score settles the pair
+                if (p.seg_amb && !((p.seg_amb[q * p.amb_words + (v >> 5)] >> (v & 31)) & 1u)) {
+                    one = (int)row;
+                    v = -1;
+                } else {
+                    atomicAdd(p.vcount + v, 1);
+                }
             }
             p.pair_vid[q * p.kprime + i] = v;
+            if (p.pair_one) p.pair_one[q * p.kprime + i] = one;
         }
         if (tid == 0) {
             p.pair_m[q] = m;
@@ -385,6 +393,61 @@ __global__ void __launch_bounds__(VTHREADS) segmax_rescore_kernel(const SelectPa
     }
 }
 
+// pairs whose best moment is known (pair_one): one canonical score, a thread per pair
+template <typename T>
+__global__ void __launch_bounds__(256) segmax_single_kernel(const SelectParams p, const int32_t *__restrict__ pair_one,
+                                                            int64_t npairs, uint64_t *__restrict__ exact) {
+    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= npairs) return;
+    const int row = pair_one[i];
+    if (row < 0) return;
+    const T *qr = (const T *)p.q + (i / p.kprime) * p.d, *gr = (const T *)p.g + (int64_t)row * p.d;
+    float acc = 0.f;
+    int k = 0;
+    if (sizeof(T) == 4 && (p.d & 3) == 0) {
+        const float4 *q4 = reinterpret_cast<const float4 *>(qr), *g4 = reinterpret_cast<const float4 *>(gr);
+#pragma unroll 4
+        for (; k < p.d; k += 4) {
+            const float4 a = __ldg(q4 + (k >> 2)), b = __ldg(g4 + (k >> 2));
+            acc = canon_step(acc, a.x, b.x);
+            acc = canon_step(acc, a.y, b.y);
+            acc = canon_step(acc, a.z, b.z);
+            acc = canon_step(acc, a.w, b.w);
+        }
+    }
+    for (; k < p.d; ++k) acc = canon_step(acc, to_f32<T>(qr[k]), to_f32<T>(gr[k]));
+    exact[i] = make_key_asc(acc, (uint32_t)row);
+}
+
+// row_eps[q] = the proven bound of |coarse - (|q|^2 - d2)| for query q (error_model), a hair generous in |q|^2
+template <typename T>
+__global__ void __launch_bounds__(256) segmax_row_eps_kernel(const SelectParams p, float *__restrict__ row_eps) {
+    const int64_t q = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (q >= p.nq) return;
+    const T *qr = (const T *)p.q + q * p.d;
+    float qn = 0.f;
+    for (int i = lane; i < p.d; i += 32) {
+        const float x = to_f32<T>(qr[i]);
+        qn = fmaf(x, x, qn);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) qn += __shfl_xor_sync(0xffffffffu, qn, o);
+    qn *= 1.0001f;
+    const float gmax2 = __uint_as_float(*p.gmax_norm2_bits);
+    if (lane == 0) row_eps[q] = 1.0001f * (p.eps_rel * sqrtf(qn) * sqrtf(gmax2) + p.eps_abs * (qn + gmax2));
+}
+
+int launch_segmax_row_eps(const SelectParams &p, float *row_eps, cudaStream_t st) {
+    if (p.nq == 0) return VQ_OK;
+    if (p.dtype == VQ_F32)
+        segmax_row_eps_kernel<float><<<(unsigned)((p.nq + 7) / 8), 256, 0, st>>>(p, row_eps);
+    else
+        segmax_row_eps_kernel<__nv_bfloat16><<<(unsigned)((p.nq + 7) / 8), 256, 0, st>>>(p, row_eps);
+    VQ_CUDA(cudaGetLastError());
+    return VQ_OK;
+}
+
 __global__ void __launch_bounds__(kSelThreads) segmax_finish_kernel(const SelectParams p, const uint64_t *__restrict__ exact) {
     extern __shared__ __align__(16) uint8_t sm[];
     const int ksort = next_pow2(p.kprime);
@@ -456,8 +519,8 @@ static int launch_sel(const SelectParams &p, cudaStream_t st) {
 }
 
 size_t select_vmajor_scratch_bytes(int64_t nq, int kprime, int64_t nseg) {
-    // pair_vid i32 | plist i32 | exact u64 (per pair)   pair_m i32 | pair_tau f32 (per query)   vcount | vfill | voff (per video)
-    return (size_t)nq * kprime * 16 + (size_t)nq * 8 + (size_t)(nseg + 1) * 12 + 64;
+    // exact u64 | pair_vid i32 | plist i32 | pair_one i32 (per pair)   pair_m i32 | pair_tau f32 (per query)   vcount | vfill | voff (per video)
+    return (size_t)nq * kprime * 20 + (size_t)nq * 8 + (size_t)(nseg + 1) * 12 + 64;
 }
 
 // SEGMAX with the video-major re-scoring; scratch: select_vmajor_scratch_bytes(), device memory
@@ -467,14 +530,22 @@ int launch_select_segmax_vmajor(SelectParams p, int64_t nseg, void *scratch, cud
     uint64_t *exact = (uint64_t *)scratch;
     int32_t *pair_vid = (int32_t *)(exact + npairs);
     int32_t *plist = pair_vid + npairs;
-    int32_t *pair_m = plist + npairs;
+    int32_t *pair_one = plist + npairs;
+    int32_t *pair_m = pair_one + npairs;
     float *pair_tau = (float *)(pair_m + p.nq);
     int32_t *vcount = (int32_t *)(pair_tau + p.nq);
     int32_t *vfill = vcount + (nseg + 1);
     int32_t *voff = vfill + (nseg + 1);
     VQ_CUDA(cudaMemsetAsync(vcount, 0, (size_t)(nseg + 1) * 8, st));  // vcount and vfill
     p.pair_vid = pair_vid; p.pair_m = pair_m; p.pair_tau = pair_tau; p.vcount = vcount;
+    p.pair_one = p.seg_amb ? pair_one : nullptr;
     VQ_TRY(launch_select(p, st));  // phase A: the k' surviving videos of every query -> pairs
+    if (p.seg_amb) {  // pairs with a proven-unique best moment: one canonical score each
+        if (p.dtype == VQ_F32)
+            segmax_single_kernel<float><<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(p, pair_one, npairs, exact);
+        else
+            segmax_single_kernel<__nv_bfloat16><<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(p, pair_one, npairs, exact);
+    }
     scan_i32_kernel<<<1, 1024, 0, st>>>(vcount, voff, nseg);
     segmax_fill_kernel<<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(pair_vid, npairs, voff, vfill, plist);
     if (p.dtype == VQ_F32)
