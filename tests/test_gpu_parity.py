@@ -209,6 +209,57 @@ def test_segmax_topk(vq, ragged):
     assert np.array_equal(D.view(np.uint32), Do.view(np.uint32))
 
 
+@pytest.mark.parametrize("bf16", [False, True])
+def test_segmax_best_moment_ties_and_near_ties(vq, bf16):
+    """The GEMM marks a (query, video) candidate when its coarse arg-max is not provably the exact best moment; unmarked
+    pairs are settled by ONE canonical score.  Adversarial videos: the best moment duplicated (exact tie: the lowest row
+    must be reported), duplicated up to one ulp in one coordinate (inside the error band, either order), duplicated
+    across the 32-column steps of the epilogue, and more videos than k' so that thresholds skip most steps.  Must equal
+    the oracle and the result with the marking switched off, bit for bit."""
+    import torch
+    from vqwild_b200 import _lib as L
+    rng = np.random.default_rng(31)
+    nseg, d, nq, k = 2500, 128, 96, 20
+    lens = rng.integers(40, 90, nseg)
+    seg_start = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    n = int(seg_start[-1])
+    g, q = _emb(rng, n, d), _emb(rng, nq, d)
+    # every query gets a few videos that hold near copies of it -> those videos are its top candidates
+    for qi in range(nq):
+        for t, v in enumerate(rng.choice(nseg, 6, replace=False)):
+            s0, S = int(seg_start[v]), int(lens[v])
+            a, b = s0 + int(rng.integers(0, S)), s0 + int(rng.integers(0, S))
+            base = q[qi] + 0.05 * rng.standard_normal(d).astype(np.float32)
+            g[a] = base
+            g[b] = base                                      # t % 3 == 0: exact duplicate (a != b mostly, any distance apart)
+            if t % 3 == 1:
+                g[b, 7] = np.nextafter(g[b, 7], np.float32(10))   # one ulp: canonical may or may not differ, coarse cannot tell
+            if t % 3 == 2:
+                g[b] = base + np.float32(3e-4) * rng.standard_normal(d).astype(np.float32)  # inside / around the band
+    if bf16:
+        g_t = torch.from_numpy(g).cuda().to(torch.bfloat16)
+        q_t = torch.from_numpy(q).cuda().to(torch.bfloat16)
+        g, q = g_t.float().cpu().numpy(), q_t.float().cpu().numpy()
+    else:
+        g_t, q_t = torch.from_numpy(g).cuda(), torch.from_numpy(q).cuda()
+    ix = vq.IndexFlatL2(d)
+    ix.add(g_t)
+    ix.set_segments(seg_start)
+    Vo, Ro, Do = orc.segmax_topk(q, g, seg_start, k)
+    outs = []
+    for off in (0, 1):
+        L.debug_set("NO_SEG_UNIQUE", off)
+        try:
+            V, R, D = ix.search_segmax(q_t, k)
+        finally:
+            L.debug_set("NO_SEG_UNIQUE", 0)
+        V, R, D = V.cpu().numpy(), R.cpu().numpy(), D.cpu().numpy()
+        assert np.array_equal(V, Vo) and np.array_equal(R, Ro), "marking %s" % ("off" if off else "on")
+        assert np.array_equal(D.view(np.uint32), Do.view(np.uint32))
+        outs.append(ix.last_stats()["fallback_queries"])
+    assert outs[0] == outs[1]
+
+
 def _seg_of(video):
     chg = np.flatnonzero(np.diff(video)) + 1
     return np.concatenate([[0], chg, [len(video)]]).astype(np.int64)

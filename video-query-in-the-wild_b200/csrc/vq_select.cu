@@ -393,29 +393,51 @@ __global__ void __launch_bounds__(VTHREADS) segmax_rescore_kernel(const SelectPa
     }
 }
 
-// pairs whose best moment is known (pair_one): one canonical score, a thread per pair
+// pairs whose best moment is known (pair_one): one canonical score, a thread per pair; one block per query, whose row
+// is staged once in shared memory (fp32) and read by broadcast -- the kernel is bound by the L2 -> SM traffic of the
+// uncoalesced gallery rows, and the query row was half of it
 template <typename T>
-__global__ void __launch_bounds__(256) segmax_single_kernel(const SelectParams p, const int32_t *__restrict__ pair_one,
-                                                            int64_t npairs, uint64_t *__restrict__ exact) {
-    const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= npairs) return;
+__global__ void __launch_bounds__(512) segmax_single_kernel(const SelectParams p, const int32_t *__restrict__ pair_one,
+                                                            uint64_t *__restrict__ exact) {
+    extern __shared__ __align__(16) float s_q[];
+    const int64_t q = blockIdx.x;
+    const T *qr = (const T *)p.q + q * p.d;
+    for (int k = threadIdx.x; k < p.d; k += blockDim.x) s_q[k] = to_f32<T>(qr[k]);
+    __syncthreads();
+    if ((int)threadIdx.x >= p.kprime) return;
+    const int64_t i = q * p.kprime + threadIdx.x;
     const int row = pair_one[i];
     if (row < 0) return;
-    const T *qr = (const T *)p.q + (i / p.kprime) * p.d, *gr = (const T *)p.g + (int64_t)row * p.d;
+    const T *gr = (const T *)p.g + (int64_t)row * p.d;
     float acc = 0.f;
     int k = 0;
     if (sizeof(T) == 4 && (p.d & 3) == 0) {
-        const float4 *q4 = reinterpret_cast<const float4 *>(qr), *g4 = reinterpret_cast<const float4 *>(gr);
+        const float4 *g4 = reinterpret_cast<const float4 *>(gr);
 #pragma unroll 4
         for (; k < p.d; k += 4) {
-            const float4 a = __ldg(q4 + (k >> 2)), b = __ldg(g4 + (k >> 2));
+            const float4 b = __ldg(g4 + (k >> 2)), a = *reinterpret_cast<const float4 *>(s_q + k);
             acc = canon_step(acc, a.x, b.x);
             acc = canon_step(acc, a.y, b.y);
             acc = canon_step(acc, a.z, b.z);
             acc = canon_step(acc, a.w, b.w);
         }
+    } else if (sizeof(T) == 2 && (p.d & 7) == 0) {  // bf16 rows: 16 bytes = 8 elements per load (a bf16 is the top half of its f32)
+        const uint4 *g8 = reinterpret_cast<const uint4 *>(gr);
+#pragma unroll 4
+        for (; k < p.d; k += 8) {
+            const uint4 b = __ldg(g8 + (k >> 3));
+            const float4 a0 = *reinterpret_cast<const float4 *>(s_q + k), a1 = *reinterpret_cast<const float4 *>(s_q + k + 4);
+            acc = canon_step(acc, a0.x, __uint_as_float(b.x << 16));
+            acc = canon_step(acc, a0.y, __uint_as_float(b.x & 0xffff0000u));
+            acc = canon_step(acc, a0.z, __uint_as_float(b.y << 16));
+            acc = canon_step(acc, a0.w, __uint_as_float(b.y & 0xffff0000u));
+            acc = canon_step(acc, a1.x, __uint_as_float(b.z << 16));
+            acc = canon_step(acc, a1.y, __uint_as_float(b.z & 0xffff0000u));
+            acc = canon_step(acc, a1.z, __uint_as_float(b.w << 16));
+            acc = canon_step(acc, a1.w, __uint_as_float(b.w & 0xffff0000u));
+        }
     }
-    for (; k < p.d; ++k) acc = canon_step(acc, to_f32<T>(qr[k]), to_f32<T>(gr[k]));
+    for (; k < p.d; ++k) acc = canon_step(acc, s_q[k], to_f32<T>(gr[k]));
     exact[i] = make_key_asc(acc, (uint32_t)row);
 }
 
@@ -541,10 +563,13 @@ int launch_select_segmax_vmajor(SelectParams p, int64_t nseg, void *scratch, cud
     p.pair_one = p.seg_amb ? pair_one : nullptr;
     VQ_TRY(launch_select(p, st));  // phase A: the k' surviving videos of every query -> pairs
     if (p.seg_amb) {  // pairs with a proven-unique best moment: one canonical score each
+        const int threads = (p.kprime + 31) / 32 * 32;  // <= kMaxKPrime = 512
+        const size_t qsm = (size_t)((p.d + 3) / 4 * 4) * 4;
+        VQ_CHECK(qsm <= 48 * 1024, VQ_ERR_CAPACITY, "segmax: dimension %d exceeds the staged query row", p.d);
         if (p.dtype == VQ_F32)
-            segmax_single_kernel<float><<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(p, pair_one, npairs, exact);
+            segmax_single_kernel<float><<<(unsigned)p.nq, threads, qsm, st>>>(p, pair_one, exact);
         else
-            segmax_single_kernel<__nv_bfloat16><<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(p, pair_one, npairs, exact);
+            segmax_single_kernel<__nv_bfloat16><<<(unsigned)p.nq, threads, qsm, st>>>(p, pair_one, exact);
     }
     scan_i32_kernel<<<1, 1024, 0, st>>>(vcount, voff, nseg);
     segmax_fill_kernel<<<(unsigned)((npairs + 255) / 256), 256, 0, st>>>(pair_vid, npairs, voff, vfill, plist);
