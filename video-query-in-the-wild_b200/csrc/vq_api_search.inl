@@ -40,7 +40,7 @@ struct SegPlan {
     int nseg = 0, n_cta = 0, n_chunks = 0;
 };
 
-static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int kprime, bool segmax, SegPlan *pl) {
+static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int kprime, bool segmax, bool split, SegPlan *pl) {
     const int64_t n = ix->n;
     const int64_t ntiles = (n + kTileN - 1) / kTileN;
     int64_t max_chunks = std::min<int64_t>(ntiles, (int64_t)(128 * 64) / kprime);  // select's gather capacity
@@ -56,6 +56,22 @@ static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int k
     int64_t best = 1;
     double best_eff = -1.0;
     if (walkers) best = std::min<int64_t>(slots / n_groups, max_chunks);
+    if (walkers && split) {
+        // Three MMA passes per tile: a part's cold start weighs a third as much against its sweep, and filling the
+        // last round of CTAs pays -- configs[2] f32: 32 groups x 4 parts on 148 CTAs (86 %) 13.65 ms, x 9 parts (two
+        // full rounds, 97 %) 12.29 ms; with one pass (CTA pairs) the extra cold starts cancel the gain (6.93 / 6.91 ms).
+        const int64_t w0 = slots / n_groups;
+        double e_best = -1.0;
+        for (int64_t w = w0; w <= std::min<int64_t>(max_chunks, 3 * w0) && ntiles >= 8 * w; ++w) {
+            const int64_t units = n_groups * w;
+            const double eff = (double)units / (double)(((units + slots - 1) / slots) * slots);
+            if (eff > e_best + 0.02) {
+                e_best = eff;
+                best = w;
+            }
+        }
+    }
+    if (walkers && g_hooks.walkers > 0) best = std::min<int64_t>(g_hooks.walkers, max_chunks);  // A/B hook: parts per group
     for (int64_t c = 1; c <= max_chunks && !walkers; ++c) {
         const int64_t units = n_groups * c;
         const double eff = (double)units / (double)(((units + slots - 1) / slots) * slots);
@@ -154,7 +170,7 @@ static void make_search_plan(const vq_index *ix, int64_t nq, int dtype, int k, b
     sp->group_size = sp->pair ? 2 : 1;
     sp->n_groups = sp->n_qblocks / sp->group_size;
     sp->slots = sp->pair ? gemm_topk_pair_slots() : sm_count();
-    plan_segments(ix, sp->n_groups, sp->slots, sp->kprime, segmax, &sp->pl);
+    plan_segments(ix, sp->n_groups, sp->slots, sp->kprime, segmax, sp->split, &sp->pl);
     sp->units = (size_t)sp->pl.nseg * sp->group_size;
 }
 
