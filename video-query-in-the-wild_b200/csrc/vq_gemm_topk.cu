@@ -267,12 +267,21 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
         const int trigger = p.trigger > 0 ? min(p.trigger, kCandCap - 64) : min(2 * p.kprime, kCandCap - 64);
         const int keep_max = min(p.kprime + p.kprime / 2, trigger - 32);
         for (int t = 0; t < ntiles; ++t) {
-            mbar_wait(&tfull_bar[as], aphase);
-            tc_fence_after();
-            const uint32_t tacc = tmem_base + lane_addr + (uint32_t)(as * BN);
             const int64_t j0 = cs + (int64_t)t * BN;
             const uint32_t jbase = (uint32_t)j0;
             const int ncols = (int)min((int64_t)BN, ce - j0);  // < BN only in the last tile of a chunk
+            // SEGMAX: the video ids of the tile's columns (lane = column inside a 32-column step), fetched BEFORE the wait
+            // for the accumulator -- inside the step the load's L2 latency sat on the critical path of every step (ncu:
+            // 19 % of the kernel's stall samples on the shuffle that consumes it)
+            int sg_pre[SEGMAX ? BN / 32 : 1];
+            if (SEGMAX) {
+#pragma unroll
+                for (int ch = 0; ch < BN / 32; ++ch)
+                    sg_pre[ch] = ch * 32 + lane < ncols ? __ldg(p.col_seg + j0 + ch * 32 + lane) : 0x7fffffff;
+            }
+            mbar_wait(&tfull_bar[as], aphase);
+            tc_fence_after();
+            const uint32_t tacc = tmem_base + lane_addr + (uint32_t)(as * BN);
 #pragma unroll 1
             for (int ch = 0; ch < BN / 32; ++ch) {
                 uint32_t r[32];
@@ -325,7 +334,9 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                     // Video boundaries inside these 32 columns are common to all rows: one coalesced load of the
                     // columns' video ids and a ballot give them as a bit mask (bit i: column i opens a new video).
                     const int colL = ch * 32 + lane;
-                    const int sgL = colL < ncols ? __ldg(p.col_seg + j0 + colL) : 0x7fffffff;
+                    int sgL = sg_pre[0];  // (the step loop is not unrolled: pick the register by a select chain)
+#pragma unroll
+                    for (int c2 = 1; c2 < BN / 32; ++c2) sgL = ch == c2 ? sg_pre[c2] : sgL;
                     int sgP = __shfl_up_sync(0xffffffffu, sgL, 1);
                     if (lane == 0) sgP = cur_seg;
                     const uint32_t bnd = __ballot_sync(0xffffffffu, colL < ncols && sgL != sgP);
@@ -351,17 +362,31 @@ __device__ __forceinline__ void epilogue_role(const GemmTopkParams &p, float *sc
                     if ((bnd & ~1u) == 0u) {  // warp-uniform: the 32 columns belong to one video
                         if (bnd & 1u) flush_to(seg_first, ch * 32);
                         if (m32 > tauh && m32 > cur_maxh) {  // the step's maximum, first column that attains it
-                            int arg = 31;
+                            // Through the max tree instead of a pass over the 32 values (the branch runs for the whole warp
+                            // whenever one row qualifies -- about every second step; ncu: 38 % of the kernel's
+                            // instructions were the two 32-element passes): first group of three that attains m32, first
+                            // element inside it; runner-up = best of the other groups and the group's other elements (a
+                            // duplicate of m32 counts).
+                            int gsel = 10;
 #pragma unroll
-                            for (int i = 30; i >= 0; --i) arg = v[i] == m32 ? i : arg;
-                            if (p.seg_amb) {  // runner-up: the old maximum or the step's second (a duplicate of m32 counts)
-                                float t2 = -INFINITY;
+                            for (int gi = 9; gi >= 0; --gi) gsel = m[gi] == m32 ? gi : gsel;
+                            float e0 = v[30], e1 = v[31], e2 = -INFINITY, others = -INFINITY;
 #pragma unroll
-                                for (int i = 0; i < 32; ++i) t2 = fmaxf(t2, i == arg ? -INFINITY : v[i]);
-                                cur_sech = fmaxf(fmaxf(cur_sech, cur_maxh), t2);
+                            for (int gi = 0; gi < 10; ++gi) {
+                                const bool me = gi == gsel;
+                                e0 = me ? v[3 * gi] : e0;
+                                e1 = me ? v[3 * gi + 1] : e1;
+                                e2 = me ? v[3 * gi + 2] : e2;
+                                others = fmaxf(others, me ? -INFINITY : m[gi]);
+                            }
+                            others = fmaxf(others, gsel == 10 ? -INFINITY : m[10]);
+                            const int sub = e0 == m32 ? 0 : (e1 == m32 ? 1 : 2);
+                            if (p.seg_amb) {
+                                const float r2 = sub == 0 ? fmaxf(e1, e2) : (sub == 1 ? fmaxf(e0, e2) : fmaxf(e0, e1));
+                                cur_sech = fmaxf(fmaxf(cur_sech, cur_maxh), fmaxf(others, r2));
                             }
                             cur_maxh = m32;
-                            cur_arg = jbase + (uint32_t)(ch * 32 + arg);
+                            cur_arg = jbase + (uint32_t)(ch * 32 + 3 * gsel + sub);
                         } else if (m32 > tauh) {
                             cur_sech = fmaxf(cur_sech, m32);
                         }
