@@ -18,6 +18,7 @@
 namespace vq {
 
 static constexpr int kApThreads = 256;
+static constexpr int kApTab = 1024;  // buckets of the positives' key range (ap_rows_kernel, pass 2)
 
 // exclusive prefix sum of a[0..n) in shared memory, in place; returns the total.  part: int[kApThreads+1]
 __device__ __forceinline__ int block_exclusive_scan(int *a, int n, int *part) {
@@ -75,6 +76,7 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     int *topn = (int *)(res + 1);            // [3] true positives within rank 30/50/100
     uint64_t *tv = (uint64_t *)(topn + 4);   // MOMENT: [128] best-moment keys of the first videos
     int *tcnt = (int *)(tv + 128);           // MOMENT: [128] kept moments per such video, then their offsets
+    int *tab = tcnt + 128;                   // [kApTab + 1] bucket table of pass 2
     const int tid = threadIdx.x;
     const int64_t q = blockIdx.x;
     const float *row = p.d2 + q * p.n;
@@ -101,6 +103,18 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     __syncthreads();
     const int *ign = misc + 8;
     const int n_ign = p.q_ignore ? p.n_ign : 0;
+    // the ignore list in registers for the two passes over the row (unused slots hold INT_MIN, never a video id): v is
+    // ignored iff min over z of (v ^ ig[z]) == 0 -- no shared-memory read per element (ncu: the loop over the list in
+    // shared memory was a quarter of the kernel's instructions and a third of its shared-memory wavefronts)
+    uint32_t ig[kMaxIgnore];
+#pragma unroll
+    for (int z = 0; z < kMaxIgnore; ++z) ig[z] = z < n_ign ? (uint32_t)ign[z] : 0x80000000u;
+    auto ignored_r = [&](int v) {
+        uint32_t m = 0xffffffffu;
+#pragma unroll
+        for (int z = 0; z < kMaxIgnore; ++z) m = min(m, (uint32_t)v ^ ig[z]);
+        return m == 0u;
+    };
 
     // ---- pass 1: positives, survivor count, last-ranked survivor ----
     int nvalid_t = 0, nkept_t = 0;
@@ -135,7 +149,7 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
             if (!kp) return;
             ++nkept_t;
         }
-        if (n_ign && is_ignored(vid, ign, n_ign)) return;
+        if (n_ign && ignored_r(vid)) return;
         ++nvalid_t;
         const unsigned long long key = make_key_asc(d2v, (uint32_t)j);
         lk = key > lk ? key : lk;
@@ -210,11 +224,35 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
     block_bitonic_sort(pos, n2);  // ascending (d2, row): best first
 
     // ---- pass 2: bucket every survivor against the sorted positive d2 values ----
+    // A table over the positives' key range (kApTab buckets, tab[b] = lower bound of the bucket's first key) cuts the
+    // bisection from log2(npos) dependent shared-memory reads to the few entries of one bucket.
+    const uint32_t kmin = (uint32_t)(pos[0] >> 32), kmax = (uint32_t)(pos[npos - 1] >> 32);
+    int tshift = 0;
+    while (((kmax - kmin) >> tshift) >= (uint32_t)kApTab) ++tshift;
+    for (int b = tid; b <= kApTab; b += kApThreads) {
+        const uint64_t first = (uint64_t)kmin + ((uint64_t)b << tshift);  // (may pass 2^32 in the last buckets)
+        int lo = 0, hi = npos;
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if ((uint64_t)(uint32_t)(pos[mid] >> 32) < first) lo = mid + 1; else hi = mid;
+        }
+        tab[b] = lo;
+    }
+    __syncthreads();
     scan_row([&](int64_t, uint8_t kp, float d2v, int vid, int, float) {
         if (MOMENT && !kp) return;
-        if (n_ign && is_ignored(vid, ign, n_ign)) return;
+        if (n_ign && ignored_r(vid)) return;
         const uint32_t s = f32_to_ordered(d2v);
         int lo = 0, hi = npos;  // lower bound: first i with pos_d2[i] >= s
+        if (s > kmax) {
+            lo = npos;
+        } else if (s >= kmin) {
+            const uint32_t b = (s - kmin) >> tshift;
+            lo = tab[b];
+            hi = tab[b + 1];
+        } else {
+            hi = 0;
+        }
         while (lo < hi) {
             const int mid = (lo + hi) >> 1;
             if ((uint32_t)(pos[mid] >> 32) < s) lo = mid + 1; else hi = mid;
@@ -653,7 +691,7 @@ int launch_ap_rows_tc(const ApTcParams &p, cudaStream_t st) {
 
 static size_t ap_rows_smem(int pcap2) {
     return (size_t)pcap2 * 8 + (size_t)(pcap2 + 1) * 4 + (size_t)pcap2 * 4 * 2 + (kApThreads + 1) * 4 + 16 * 4 + 16 +
-           8 + 16 + 128 * 8 + 128 * 4 + 64;
+           8 + 16 + 128 * 8 + 128 * 4 + (kApTab + 1) * 4 + 64;
 }
 
 int launch_ap_rows(const ApRowsParams &p, int pcap2, cudaStream_t st) {
