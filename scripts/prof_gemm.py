@@ -18,7 +18,7 @@ g = bench.gen_rows(torch, "g", 0, n, 512, dev)
 ix = vq.IndexFlatL2(512)
 ix.add(g)
 for _ in range(reps):
-    D, I = ix.search(xq, 100)
+    D, I = ix.search(xq, int(os.environ.get("PROF_K", "100")))
 torch.cuda.synchronize()
 t = ix.last_timing()
 print("nq=%d n=%d" % (nq, n), ix.last_stats(), t, "TFLOP/s=%.1f" % (2.0 * nq * n * 512 / t["gemm_topk_ms"] / 1e9))
