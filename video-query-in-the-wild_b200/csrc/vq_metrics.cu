@@ -425,9 +425,9 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
     unsigned long long *lastp = (unsigned long long *)(ambk + kTcAmb);  // [2] key of the canonically last survivor (+ pad)
     float *qs = (float *)(lastp + 2);                     // [d rounded up to 4] 16-byte aligned: read as float4
     uint32_t *ambr = (uint32_t *)(qs + ((p.d + 3) & ~3)); // [kTcAmb] rows of the queued survivors
-    uint32_t *posr = ambr + kTcAmb;                       // [kTcPos] rows of the positives (before their keys exist)
-    int *gap = (int *)(posr + kTcPos);                    // [kTcPos + 2] non-positive survivors between positives i-1 and i (by d2)
+    int *gap = (int *)(ambr + kTcAmb);                    // [kTcPos + 2] non-positive survivors between positives i-1 and i (by d2)
     int *eqc = gap + kTcPos + 2;                          // [kTcPos + 1] ... of which with d2 equal to positive i's
+    uint32_t *posr = (uint32_t *)eqc;                     // [kTcPos] rows of the positives until their keys exist (eqc is zeroed after)
     int *part = eqc + kTcPos + 1;                         // [40]
     int *misc = part + 40;                                // [0] npos [1] nvalid [2] namb [3] bad [4] cmin bits [5..7] topn  [8..16) ignore
     uint8_t *tile = (uint8_t *)((((uintptr_t)(misc + 16)) + 127) & ~(uintptr_t)127);  // [warps][kRescoreTileBytes]
@@ -441,7 +441,6 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
     if (tid < kMaxIgnore) misc[8 + tid] = tid < n_ign ? p.q_ignore[q * p.n_ign + tid] : -1;
     if (tid < 8) misc[tid] = tid == 4 ? -1 : 0;  // [4]: ordered-uint image of the smallest coarse score, starts at the maximum
     for (int i = tid; i < kTcPos + 2; i += kTcThreads) gap[i] = 0;
-    for (int i = tid; i < kTcPos + 1; i += kTcThreads) eqc[i] = 0;
     __syncthreads();
     const int *ign = misc + 8;
     float qn = 0.f;
@@ -483,11 +482,22 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
         }
         for (int64_t j = n4 + tid; j < p.n; j += kTcThreads) body(j, row[j], n_ign ? p.g_video[j] : 0, p.g_label[j]);
     };
+    // the ignore list in registers (as in ap_rows_kernel: min of xors, no shared-memory read per element -- the loop over
+    // the shared list was a third of this kernel's stall samples and a quarter of its instructions)
+    uint32_t ig[kMaxIgnore];
+#pragma unroll
+    for (int z = 0; z < kMaxIgnore; ++z) ig[z] = z < n_ign ? (uint32_t)ign[z] : 0x80000000u;
+    auto ignored_r = [&](int v) {
+        uint32_t m = 0xffffffffu;
+#pragma unroll
+        for (int z = 0; z < kMaxIgnore; ++z) m = min(m, (uint32_t)v ^ ig[z]);
+        return m == 0u;
+    };
     // ---- pass 1: survivors, positives, smallest coarse score ----
     int nvalid_t = 0;
     float cmin_t = INFINITY;
     scan_row([&](int64_t j, float c, int vid, int lab) {
-        if (n_ign && is_ignored(vid, ign, n_ign)) return;
+        if (n_ign && ignored_r(vid)) return;
         ++nvalid_t;
         cmin_t = fminf(cmin_t, c);
         if (lab == ql) {
@@ -533,6 +543,7 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
     for (int i = ntrue + tid; i < n2p; i += kTcThreads) pos[i] = ~0ull;
     rescore(posr, pos, ntrue);
     __syncthreads();
+    for (int i = tid; i < kTcPos + 1; i += kTcThreads) eqc[i] = 0;  // (posr's storage)
     block_bitonic_sort(pos, n2p);
     auto posd = [&](int i) { return (uint32_t)(pos[i] >> 32); };  // ordered image of positive i's d2
 
@@ -541,7 +552,7 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
     const uint32_t last_pos_o = ntrue > 0 ? posd(ntrue - 1) : 0u;
     scan_row([&](int64_t j, float c, int vid, int lab) {
         if (lab == ql) return;
-        if (n_ign && is_ignored(vid, ign, n_ign)) return;
+        if (n_ign && ignored_r(vid)) return;
         const float e = qn - c;
         bool queue = e >= emax - 2.0f * eps;  // could be the canonically last survivor
         int lb = 0;
@@ -670,7 +681,7 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
 }
 
 size_t ap_rows_tc_smem(int d) {
-    return (size_t)kTcPos * 8 + (size_t)kTcAmb * 8 + 16 + (size_t)kTcAmb * 4 + (size_t)kTcPos * 4 + (size_t)(kTcPos + 2) * 4 +
+    return (size_t)kTcPos * 8 + (size_t)kTcAmb * 8 + 16 + (size_t)kTcAmb * 4 + (size_t)(kTcPos + 2) * 4 +
            (size_t)(kTcPos + 1) * 4 + (size_t)((d + 3) & ~3) * 4 + 40 * 4 + 16 * 4 + 128 + (size_t)(kTcThreads / 32) * kRescoreTileBytes + 64;
 }
 
