@@ -15,6 +15,8 @@ namespace vq {
 // staged coalesced, each lane sums its contiguous slice, a shuffle scan gives the slice offsets, and the slice is
 // rewritten as running sums -- no block-wide serial step.  Windows: one thread per window, CH consecutive channels
 // (one 32-byte sector per window and tile), one reciprocal per window.
+static constexpr int kStageLoads = 8;  // (16 in flight measured the same: the staging loads are not what bounds the kernel)
+
 template <int CH>
 __global__ void __launch_bounds__(256) window_means_kernel(const float *__restrict__ feat, int C, int64_t Ttot,
                                                            const int64_t *__restrict__ vid_t0,
@@ -33,14 +35,14 @@ __global__ void __launch_bounds__(256) window_means_kernel(const float *__restri
         const int c = c0 + ch;
         double *row = P + ch * pitch;
         if (c < C) {
-            // eight independent loads in flight per lane: a 600-frame channel is three memory latencies, not nineteen
+            // kStageLoads independent loads in flight per lane: a 600-frame channel is three memory latencies, not nineteen
             const float *src = feat + (int64_t)c * Ttot + t0;
-            for (int t = lane; t < T; t += 256) {
-                float v[8];
+            for (int t = lane; t < T; t += 32 * kStageLoads) {
+                float v[kStageLoads];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) v[u] = t + 32 * u < T ? __ldg(src + t + 32 * u) : 0.f;
+                for (int u = 0; u < kStageLoads; ++u) v[u] = t + 32 * u < T ? __ldg(src + t + 32 * u) : 0.f;
 #pragma unroll
-                for (int u = 0; u < 8; ++u)
+                for (int u = 0; u < kStageLoads; ++u)
                     if (t + 32 * u < T) row[t + 32 * u + 1] = (double)v[u];
             }
         } else {
@@ -75,7 +77,14 @@ __global__ void __launch_bounds__(256) window_means_kernel(const float *__restri
 #pragma unroll
         for (int ch = 0; ch < CH; ++ch) r[ch] = (float)((P[ch * pitch + z] - P[ch * pitch + a]) * rl);
         float *dst = out + (w0 + w) * (int64_t)C + c0;
-        if (CH % 4 == 0 && c0 + CH <= C && (C & 3) == 0 && (((uintptr_t)out) & 15) == 0) {
+        if (CH == 8 && c0 + CH <= C && (C & 7) == 0 && (((uintptr_t)out) & 31) == 0) {
+            // one 256-bit store = the window's whole 32-byte sector of this channel tile (sm_100: STG.256).  As two
+            // 16-byte stores every sector went through the L1 data pipe twice (ncu: 180 M store sectors for 2.84 GB
+            // written, the pipe 90 % busy).
+            asm volatile("st.global.v8.f32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "f"(r[0]), "f"(r[1]), "f"(r[2]),
+                         "f"(r[3]), "f"(r[4 % CH]), "f"(r[5 % CH]), "f"(r[6 % CH]), "f"(r[7 % CH])
+                         : "memory");
+        } else if (CH % 4 == 0 && c0 + CH <= C && (C & 3) == 0 && (((uintptr_t)out) & 15) == 0) {
 #pragma unroll
             for (int ch = 0; ch < CH; ch += 4) *reinterpret_cast<float4 *>(dst + ch) = make_float4(r[ch], r[ch + 1], r[ch + 2], r[ch + 3]);
         } else {
