@@ -411,7 +411,33 @@ __global__ void __launch_bounds__(512) segmax_single_kernel(const SelectParams p
     const T *gr = (const T *)p.g + (int64_t)row * p.d;
     float acc = 0.f;
     int k = 0;
-    if (sizeof(T) == 4 && (p.d & 3) == 0) {
+    // 32 bytes per load (LDG.256, sm_100): the row reads are uncoalesced -- one sector per lane and request -- and what
+    // bounds the kernel is the number of such requests, so a whole sector per request halves them
+    if ((((uintptr_t)gr) & 31) == 0 && ((size_t)p.d * sizeof(T)) % 32 == 0) {
+        constexpr int E = 32 / (int)sizeof(T);  // elements per load
+#pragma unroll 2
+        for (; k < p.d; k += E) {
+            uint32_t w[8];
+            asm volatile("ld.global.nc.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                         : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+                         : "l"(gr + k));
+            if (sizeof(T) == 4) {
+                const float4 a0 = *reinterpret_cast<const float4 *>(s_q + k), a1 = *reinterpret_cast<const float4 *>(s_q + k + 4);
+                const float av[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+                for (int e = 0; e < 8; ++e) acc = canon_step(acc, av[e], __uint_as_float(w[e]));
+            } else {
+#pragma unroll
+                for (int e = 0; e < 8; e += 2) {
+                    const float4 a = *reinterpret_cast<const float4 *>(s_q + k + 2 * e);
+                    acc = canon_step(acc, a.x, __uint_as_float(w[e] << 16));
+                    acc = canon_step(acc, a.y, __uint_as_float(w[e] & 0xffff0000u));
+                    acc = canon_step(acc, a.z, __uint_as_float(w[e + 1] << 16));
+                    acc = canon_step(acc, a.w, __uint_as_float(w[e + 1] & 0xffff0000u));
+                }
+            }
+        }
+    } else if (sizeof(T) == 4 && (p.d & 3) == 0) {
         const float4 *g4 = reinterpret_cast<const float4 *>(gr);
 #pragma unroll 4
         for (; k < p.d; k += 4) {
