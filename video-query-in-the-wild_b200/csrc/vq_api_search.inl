@@ -257,7 +257,9 @@ static int search_core(vq_index *ix, const void *xq, int64_t nq, int dtype, int 
     // SEGMAX: the GEMM marks the (query, video) candidates whose coarse arg-max is not provably the exact best moment;
     // all others are settled by one canonical score instead of the whole video (vq_select.cu)
     Tmp amb, reps;
-    const bool seg_unique = segmax && !g_hooks.no_vmajor && !g_hooks.no_seg_unique && ix->n < (1ll << 31);
+    // (one bit per (query, video): not worth more than 1 GiB -- beyond that every pair takes the video-major re-scoring)
+    const bool seg_unique = segmax && !g_hooks.no_vmajor && !g_hooks.no_seg_unique && ix->n < (1ll << 31) &&
+                            (double)nq * (double)(((int64_t)ix->seg_start.size() + 30) / 32) * 4.0 <= 1073741824.0;
     if (seg_unique) {
         const int64_t nseg = (int64_t)ix->seg_start.size() - 1;
         const int words = (int)((nseg + 31) / 32);
@@ -461,6 +463,10 @@ int vq_index_search_workspace_bytes(vq_index *ix, int64_t nq, int64_t k, int seg
     make_search_plan(ix, nq, ix->dtype, (int)k, segmax != 0, &sp);
     *persistent_bytes = (int64_t)sp.persistent_bytes() + nq * 4;
     *transient_bytes = nq * ix->dpa * 2 * (sp.split ? 2 : 1);
+    if (segmax && !ix->seg_start.empty()) {  // video-major re-scoring scratch + the (query, video) ambiguity bits and row bounds
+        const int64_t nseg = (int64_t)ix->seg_start.size() - 1;
+        *transient_bytes += (int64_t)select_vmajor_scratch_bytes(nq, sp.kprime, nseg) + nq * ((nseg + 31) / 32) * 4 + nq * 4;
+    }
     return VQ_OK;
 }
 
