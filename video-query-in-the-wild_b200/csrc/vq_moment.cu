@@ -126,31 +126,77 @@ __global__ void __launch_bounds__(256, NT == 32 ? 4 : 1) moment_nms_kernel(const
                 if (S == 0 && t == 0) p.vbest[q * p.nseg + v] = ~0ull;
                 continue;
             }
-            uint64_t k0 = t < S ? make_key_asc(row[s0 + t], (uint32_t)t) : ~0ull;
-            uint64_t k1 = t + 32 < S ? make_key_asc(row[s0 + t + 32], (uint32_t)(t + 32)) : ~0ull;
-            auto cx = [&](uint64_t &x, int jj, bool asc) {
-                const uint64_t o = __shfl_xor_sync(0xffffffffu, x, jj);
+            // First on 32-bit keys: the score's ordered image with its low 6 bits replaced by the moment number -- one
+            // shuffle and one min / max per compare-exchange instead of two shuffles and a 64-bit compare.  The order is
+            // the exact (d2, moment) order unless two moments agree in the 26 score bits that were kept; such a pair ends
+            // up adjacent, is detected, and the video is sorted again on the full 64-bit keys.
+            const float d0 = t < S ? row[s0 + t] : 0.f, d1 = t + 32 < S ? row[s0 + t + 32] : 0.f;
+            uint32_t c0 = t < S ? ((f32_to_ordered(d0) & ~63u) | (uint32_t)t) : 0xffffffffu;
+            uint32_t c1 = t + 32 < S ? ((f32_to_ordered(d1) & ~63u) | (uint32_t)(t + 32)) : 0xffffffffu;
+            auto cx32 = [&](uint32_t &x, int jj, bool asc) {
+                const uint32_t o = __shfl_xor_sync(0xffffffffu, x, jj);
                 const bool takemin = ((t & jj) == 0) == asc;
-                x = ((o < x) == takemin) ? o : x;
+                x = takemin ? min(x, o) : max(x, o);
             };
 #pragma unroll
             for (int k = 2; k <= 32; k <<= 1) {
                 const bool a0 = k < 32 ? (t & k) == 0 : true, a1 = k < 32 ? a0 : false;
 #pragma unroll
                 for (int jj = k >> 1; jj > 0; jj >>= 1) {
-                    cx(k0, jj, a0);
-                    cx(k1, jj, a1);
+                    cx32(c0, jj, a0);
+                    cx32(c1, jj, a1);
                 }
             }
-            if (k1 < k0) {
-                const uint64_t tmp = k0;
-                k0 = k1;
-                k1 = tmp;
+            if (c1 < c0) {
+                const uint32_t tmp = c0;
+                c0 = c1;
+                c1 = tmp;
             }
 #pragma unroll
             for (int jj = 16; jj > 0; jj >>= 1) {
-                cx(k0, jj, true);
-                cx(k1, jj, true);
+                cx32(c0, jj, true);
+                cx32(c1, jj, true);
+            }
+            // rank r and r + 1 with equal kept score bits?  (ranks t / t + 1 and t + 32 / t + 33; pads are all ones)
+            uint32_t n0 = __shfl_down_sync(0xffffffffu, c0, 1), n1 = __shfl_down_sync(0xffffffffu, c1, 1);
+            const uint32_t c1_first = __shfl_sync(0xffffffffu, c1, 0);
+            if (t == 31) {
+                n0 = c1_first;
+                n1 = 0xffffffffu;
+            }
+            const bool clash = (t + 1 < S && ((c0 ^ n0) & ~63u) == 0u) || (t + 33 < S && ((c1 ^ n1) & ~63u) == 0u);
+            uint64_t k0, k1;
+            if (__any_sync(0xffffffffu, clash)) {  // uniform, rare: the exact sort on (d2, moment)
+                k0 = t < S ? make_key_asc(d0, (uint32_t)t) : ~0ull;
+                k1 = t + 32 < S ? make_key_asc(d1, (uint32_t)(t + 32)) : ~0ull;
+                auto cx = [&](uint64_t &x, int jj, bool asc) {
+                    const uint64_t o = __shfl_xor_sync(0xffffffffu, x, jj);
+                    const bool takemin = ((t & jj) == 0) == asc;
+                    x = ((o < x) == takemin) ? o : x;
+                };
+#pragma unroll 1
+                for (int k = 2; k <= 32; k <<= 1) {
+                    const bool a0 = k < 32 ? (t & k) == 0 : true, a1 = k < 32 ? a0 : false;
+#pragma unroll 1
+                    for (int jj = k >> 1; jj > 0; jj >>= 1) {
+                        cx(k0, jj, a0);
+                        cx(k1, jj, a1);
+                    }
+                }
+                if (k1 < k0) {
+                    const uint64_t tmp = k0;
+                    k0 = k1;
+                    k1 = tmp;
+                }
+#pragma unroll 1
+                for (int jj = 16; jj > 0; jj >>= 1) {
+                    cx(k0, jj, true);
+                    cx(k1, jj, true);
+                }
+            } else {  // moment numbers in the low bytes; the exact key of the best moment for vbest
+                k0 = (uint64_t)(c0 & 63u);
+                k1 = (uint64_t)(c1 & 63u);
+                if (t == 0) k0 = make_key_asc(row[s0 + (c0 & 63u)], c0 & 63u);
             }
             b_rank[j * kNmsRankPitch + t] = (uint8_t)k0;        // moment (index inside the video) at ranks t, t + 32;
             b_rank[j * kNmsRankPitch + t + 32] = (uint8_t)k1;   // ranks >= S hold the pad key's low byte, never read
