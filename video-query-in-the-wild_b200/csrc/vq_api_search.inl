@@ -62,7 +62,9 @@ static void plan_segments(const vq_index *ix, int64_t n_groups, int slots, int k
         // full rounds, 97 %) 12.29 ms; with one pass (CTA pairs) the extra cold starts cancel the gain (6.93 / 6.91 ms).
         const int64_t w0 = slots / n_groups;
         double e_best = -1.0;
-        for (int64_t w = w0; w <= std::min<int64_t>(max_chunks, 3 * w0) && ntiles >= 8 * w; ++w) {
+        // (only where a part still sweeps >= 64 tiles: on a 20 480-row gallery nine parts of nine tiles each lose to
+        // four of twenty, 1.51 against 1.12 ms, scripts/ab_walkers_small.py)
+        for (int64_t w = w0; w <= std::min<int64_t>(max_chunks, 3 * w0) && (w == w0 || ntiles >= 64 * w); ++w) {
             const int64_t units = n_groups * w;
             const double eff = (double)units / (double)(((units + slots - 1) / slots) * slots);
             if (eff > e_best + 0.02) {
