@@ -13,17 +13,24 @@ namespace vq {
 // ---------------------------------------------------------------------------------------
 // all-pairs: 64 x 64 output tile per 256-thread block, 4 x 4 per thread, k staged 32 at a time
 // ---------------------------------------------------------------------------------------
-static constexpr int AT = 64, AQ = 128, AK = 32, APAD = 4;  // gallery rows / query rows / k per block tile
+// k-block depth: 64 (half the barriers, but 124 registers and 51 KB of shared memory -> two blocks per SM instead of three)
+// measured 4.98 ms against 3.48 ms at 4096 x 20480 x 512 -- occupancy matters more than the barrier count.
+#ifndef VQ_L2SQ_AK
+#define VQ_L2SQ_AK 32
+#endif
+static constexpr int AT = 64, AQ = 128, AK = VQ_L2SQ_AK, APAD = 4;
+static constexpr size_t kL2Smem = sizeof(float) * AK * (AQ + APAD + AT + APAD);  // gallery rows / query rows / k per block tile
 
 template <typename T>
-__global__ void __launch_bounds__(256, 3) l2sq_all_kernel(const T *__restrict__ q, const T *__restrict__ g,
+__global__ void __launch_bounds__(256, AK == 64 ? 2 : 3) l2sq_all_kernel(const T *__restrict__ q, const T *__restrict__ g,
                                                           int64_t nq, int64_t n, int d, float *__restrict__ out) {
     // 128 queries x 64 gallery rows per block, 8 x 4 per thread: per k one thread reads 8 query and 4 gallery values
     // (three LDS.128) for 32 packed steps.  The {q, q} operand of a packed step is the scalar-broadcast form of FADD2
     // (R.F32): nothing is duplicated in shared memory -- with a 4 x 4 tile and duplicated queries the shared-memory
     // pipe was the limiter (ncu: l1tex 95 %, fma pipe 58 %).
-    __shared__ __align__(16) float sQ[AK][AQ + APAD];
-    __shared__ __align__(16) float sG[AK][AT + APAD];
+    extern __shared__ __align__(16) uint8_t l2_sm[];  // dynamic: sQ[AK][AQ + APAD] | sG[AK][AT + APAD]
+    float(*sQ)[AQ + APAD] = reinterpret_cast<float(*)[AQ + APAD]>(l2_sm);
+    float(*sG)[AT + APAD] = reinterpret_cast<float(*)[AT + APAD]>(l2_sm + sizeof(float) * AK * (AQ + APAD));
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
     const int64_t q0 = (int64_t)blockIdx.y * AQ, g0 = (int64_t)blockIdx.x * AT;
     unsigned long long acc[8][2];  // [query a][gallery pair]: {acc(a, 2p), acc(a, 2p+1)}
@@ -32,17 +39,20 @@ __global__ void __launch_bounds__(256, 3) l2sq_all_kernel(const T *__restrict__ 
     // loaders: query row qr = tid / 2, 16 consecutive k; gallery row gr = tid / 4, 8 consecutive k.  The next k-block's
     // values are fetched into registers while this one is being multiplied; tile columns are XOR-swizzled by the k-group
     // so that the loader lanes of one row do not land in one bank.
-    const int qr = tid >> 1, qk = (tid & 1) * 16, q_sw = (tid & 1) << 4;
-    const int gr = tid >> 2, gk = (tid & 3) * 8, g_sw = (tid & 3) << 3;
-    float rq[16], rg[8];
+    constexpr int QE = AK / 2, GE = AK / 4;            // k values a loader thread carries per k-block
+    constexpr int QSH = AK == 64 ? 5 : 4, GSH = AK == 64 ? 4 : 3;
+    static_assert(AK == 32 || AK == 64, "loader layout");
+    const int qr = tid >> 1, qk = (tid & 1) * QE, q_sw = (tid & 1) << 4;
+    const int gr = tid >> 2, gk = (tid & 3) * GE, g_sw = (tid & 3) << 3;
+    float rq[QE], rg[GE];
     auto fetch = [&](int k0) {
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
+        for (int e = 0; e < QE; ++e) {
             const int k = k0 + qk + e;
             rq[e] = (k < d && q0 + qr < nq) ? to_f32<T>(q[(q0 + qr) * d + k]) : 0.f;
         }
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
+        for (int e = 0; e < GE; ++e) {
             const int k = k0 + gk + e;
             rg[e] = (k < d && g0 + gr < n) ? to_f32<T>(g[(g0 + gr) * d + k]) : 0.f;
         }
@@ -51,14 +61,14 @@ __global__ void __launch_bounds__(256, 3) l2sq_all_kernel(const T *__restrict__ 
     for (int k0 = 0; k0 < d; k0 += AK) {
         __syncthreads();
 #pragma unroll
-        for (int e = 0; e < 16; ++e) sQ[qk + e][qr ^ q_sw] = rq[e];
+        for (int e = 0; e < QE; ++e) sQ[qk + e][qr ^ q_sw] = rq[e];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) sG[gk + e][gr ^ g_sw] = rg[e];
+        for (int e = 0; e < GE; ++e) sG[gk + e][gr ^ g_sw] = rg[e];
         __syncthreads();
         if (k0 + AK < d) fetch(k0 + AK);
 #pragma unroll
         for (int kk = 0; kk < AK; ++kk) {
-            const int swq = (kk >> 4) << 4, swg = (kk >> 3) << 3;
+            const int swq = (kk >> QSH) << 4, swg = (kk >> GSH) << 3;
             const float4 a0 = *reinterpret_cast<const float4 *>(&sQ[kk][(ty * 8) ^ swq]);
             const float4 a1 = *reinterpret_cast<const float4 *>(&sQ[kk][((ty * 8) ^ swq) + 4]);
             const ulonglong2 b2 = *reinterpret_cast<const ulonglong2 *>(&sG[kk][(tx * 4) ^ swg]);
@@ -94,11 +104,14 @@ int launch_l2sq_all(const void *q, const void *g, int dtype, int64_t nq, int64_t
     if (nq == 0 || n == 0) return VQ_OK;
     dim3 grid((unsigned)((n + AT - 1) / AT), (unsigned)((nq + AQ - 1) / AQ));
     VQ_CHECK(grid.y <= 65535, VQ_ERR_INVALID, "l2sq_all: too many query tiles in one launch");
-    if (dtype == VQ_F32)
-        l2sq_all_kernel<float><<<grid, 256, 0, st>>>((const float *)q, (const float *)g, nq, n, d, out);
-    else
-        l2sq_all_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16 *)q, (const __nv_bfloat16 *)g,
+    if (dtype == VQ_F32) {
+        VQ_CUDA(cudaFuncSetAttribute(l2sq_all_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kL2Smem));
+        l2sq_all_kernel<float><<<grid, 256, kL2Smem, st>>>((const float *)q, (const float *)g, nq, n, d, out);
+    } else {
+        VQ_CUDA(cudaFuncSetAttribute(l2sq_all_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kL2Smem));
+        l2sq_all_kernel<__nv_bfloat16><<<grid, 256, kL2Smem, st>>>((const __nv_bfloat16 *)q, (const __nv_bfloat16 *)g,
                                                               nq, n, d, out);
+    }
     VQ_CUDA(cudaGetLastError());
     return VQ_OK;
 }
