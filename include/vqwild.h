@@ -58,7 +58,7 @@ typedef enum {
 VQ_API int vq_version(void);
 VQ_API const char *vq_last_error(void);
 /* Test / A-B hooks ("FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS",
- * "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER", "NO_VMAJOR", "NO_NMS_MASKS", "NO_SEG_UNIQUE", "WALKERS").  Their initial values come from the VQ_DEBUG_<NAME> environment variables, read once when the
+ * "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER", "NO_VMAJOR", "NO_NMS_MASKS", "NO_SEG_UNIQUE", "WALKERS", "NO_L2SQ_WIDE").  Their initial values come from the VQ_DEBUG_<NAME> environment variables, read once when the
  * library is loaded; no entry point reads the environment afterwards. */
 VQ_API int vq_debug_set(const char *hook, int value);
 /* 0 if device `dev` exists and is sm_100; else VQ_ERR_NO_DEVICE / VQ_ERR_ARCH. */

@@ -45,7 +45,7 @@ def lib():
 
 def debug_set(hook, value):
     """Test / A-B hooks (FORCE_FALLBACK, NO_PAIR, NO_CHAIN, DENSE_ROWS, NO_TC_TRIPLET, TRIPLET_CLOCKS, NO_TC_EVAL, NO_INSERT,
-    KPRIME, TRIGGER, NO_VMAJOR, NO_NMS_MASKS, NO_SEG_UNIQUE, WALKERS); see include/vqwild.h."""
+    KPRIME, TRIGGER, NO_VMAJOR, NO_NMS_MASKS, NO_SEG_UNIQUE, WALKERS, NO_L2SQ_WIDE); see include/vqwild.h."""
     check(lib().vq_debug_set(hook.encode(), C.c_int(int(value))))
 
 

@@ -21,13 +21,14 @@ static int *hook_slot(const char *name) {
         {"TRIPLET_CLOCKS", &g_hooks.triplet_clocks}, {"NO_TC_EVAL", &g_hooks.no_tc_eval},
         {"NO_INSERT", &g_hooks.no_insert}, {"KPRIME", &g_hooks.kprime}, {"TRIGGER", &g_hooks.trigger},
         {"NO_VMAJOR", &g_hooks.no_vmajor}, {"NO_NMS_MASKS", &g_hooks.no_nms_masks},
-        {"NO_SEG_UNIQUE", &g_hooks.no_seg_unique}, {"WALKERS", &g_hooks.walkers}};
+        {"NO_SEG_UNIQUE", &g_hooks.no_seg_unique}, {"WALKERS", &g_hooks.walkers},
+        {"NO_L2SQ_WIDE", &g_hooks.no_l2sq_wide}};
     for (auto &t : tab)
         if (!strcmp(name, t.n)) return t.p;
     return nullptr;
 }
 static const bool g_hooks_from_env = [] {
-    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER", "NO_VMAJOR", "NO_NMS_MASKS", "NO_SEG_UNIQUE", "WALKERS"}) {
+    for (const char *n : {"FORCE_FALLBACK", "NO_PAIR", "NO_CHAIN", "DENSE_ROWS", "NO_TC_TRIPLET", "TRIPLET_CLOCKS", "NO_TC_EVAL", "NO_INSERT", "KPRIME", "TRIGGER", "NO_VMAJOR", "NO_NMS_MASKS", "NO_SEG_UNIQUE", "WALKERS", "NO_L2SQ_WIDE"}) {
         char env[64];
         snprintf(env, sizeof(env), "VQ_DEBUG_%s", n);
         if (const char *e = getenv(env)) *hook_slot(n) = atoi(e);

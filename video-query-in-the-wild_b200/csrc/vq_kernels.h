@@ -10,7 +10,7 @@ namespace vq {
 // loaded and changed afterwards only through vq_debug_set() -- never getenv() on a search path.
 struct DebugHooks {
     int force_fallback = 0, no_pair = 0, no_chain = 0, dense_rows = -1, no_tc_triplet = 0, triplet_clocks = 0,
-        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0, no_vmajor = 0, no_nms_masks = 0, no_seg_unique = 0, walkers = 0;
+        no_tc_eval = 0, no_insert = 0, kprime = 0, trigger = 0, no_vmajor = 0, no_nms_masks = 0, no_seg_unique = 0, walkers = 0, no_l2sq_wide = 0;
 };
 extern DebugHooks g_hooks;
 
