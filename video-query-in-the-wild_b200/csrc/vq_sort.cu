@@ -20,6 +20,21 @@ static constexpr int kRsPerThread = 16;
 static constexpr int kRsChunk = kRsThreads * kRsPerThread;  // elements per block
 static constexpr uint32_t kRsNoDigit = 0x100u;              // lanes past the end of the row
 
+// Lanes of the warp that hold the same digit (0 .. 256; 256 = "past the end of the row"), as a bit mask: nine ballots,
+// one per digit bit.  __match_any_sync gives the same mask but its cost grows with the number of DISTINCT digits in the
+// warp -- the passes over the low, random bytes of the scores ran 4x slower than the pass over the top byte (ncu: 1.61 /
+// 1.22 / 0.84 / 0.43 ms for the four scatter passes over identical volumes).
+__device__ __forceinline__ uint32_t rs_match(uint32_t dg) {
+    uint32_t peers = 0xffffffffu;
+#pragma unroll
+    for (int b = 0; b < 9; ++b) {
+        const bool bit = (dg >> b) & 1u;
+        const uint32_t vote = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? vote : ~vote;
+    }
+    return peers;
+}
+
 template <bool FIRST>
 __device__ __forceinline__ uint64_t rs_load(const RowSortParams &p, int64_t q, int64_t i, const int *ign, int n_ign) {
     if (FIRST) {
@@ -52,7 +67,7 @@ __global__ void __launch_bounds__(kRsThreads) rowsort_hist_kernel(const RowSortP
         const int64_t i = base + r * 32 + lane;
         uint32_t dg = kRsNoDigit;
         if (i < p.n) dg = (uint32_t)(rs_load<FIRST>(p, q, i, ign, n_ign) >> (32 + shift)) & 255u;
-        const uint32_t m = __match_any_sync(0xffffffffu, dg);
+        const uint32_t m = rs_match(dg);
         if (dg != kRsNoDigit && lane == __ffs(m) - 1) atomicAdd(&h[dg], __popc(m));
     }
     __syncthreads();
@@ -116,11 +131,13 @@ __global__ void __launch_bounds__(kRsThreads) rowsort_scatter_kernel(const RowSo
         const int64_t i = base + r * 32 + lane;
         e[r] = i < p.n ? rs_load<FIRST>(p, q, i, ign, n_ign) : 0ull;
     }
+    uint32_t mk[kRsPerThread];  // the peers of every element: formed once, used for the counts and for the ranks
 #pragma unroll
     for (int r = 0; r < kRsPerThread; ++r) {
         const int64_t i = base + r * 32 + lane;
         const uint32_t dg = i < p.n ? (uint32_t)(e[r] >> (32 + shift)) & 255u : kRsNoDigit;
-        const uint32_t m = __match_any_sync(0xffffffffu, dg);
+        const uint32_t m = rs_match(dg);
+        mk[r] = m;
         if (dg != kRsNoDigit && lane == __ffs(m) - 1) mine[dg] += __popc(m);
         __syncwarp();
     }
@@ -140,7 +157,7 @@ __global__ void __launch_bounds__(kRsThreads) rowsort_scatter_kernel(const RowSo
     for (int r = 0; r < kRsPerThread; ++r) {
         const int64_t i = base + r * 32 + lane;
         const uint32_t dg = i < p.n ? (uint32_t)(e[r] >> (32 + shift)) & 255u : kRsNoDigit;
-        const uint32_t m = __match_any_sync(0xffffffffu, dg);
+        const uint32_t m = mk[r];
         if (dg != kRsNoDigit) {
             const int64_t slot = mine[dg] + __popc(m & lt);
             if (LAST) {
