@@ -113,7 +113,7 @@ __global__ void __launch_bounds__(256) rowsort_scan_kernel(int32_t *__restrict__
 }
 
 template <bool FIRST, bool LAST>
-__global__ void __launch_bounds__(kRsThreads) rowsort_scatter_kernel(const RowSortParams p, int shift, int nblk) {
+__global__ void __launch_bounds__(kRsThreads, 3) rowsort_scatter_kernel(const RowSortParams p, int shift, int nblk) {
     __shared__ int cnt[kRsWarps][256];  // per-warp digit counts, then each warp's running output slot per digit
     __shared__ int ign[kMaxIgnore];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
