@@ -415,10 +415,14 @@ __global__ void __launch_bounds__(kApThreads) ap_rows_kernel(const ApRowsParams 
 // With class-structured features the queue holds ~1 % of the gallery; a query whose queue or positive list overflows
 // is reported in `redo` and evaluated by the canonical all-pairs path.  Results are the same numbers as ap_rows_kernel.
 // ---------------------------------------------------------------------------------------------------------------
-static constexpr int kTcThreads = 128, kTcPos = 512, kTcAmb = 1024;  // 56 KB of shared memory per block: four blocks per SM
+#ifndef VQ_TC_THREADS
+#define VQ_TC_THREADS 256
+#endif
+static constexpr int kTcThreads = VQ_TC_THREADS, kTcPos = 512, kTcAmb = 1024;  // 256 threads, 80 registers, 56 KB: three blocks = 24 warps per SM (128 threads x four blocks = 16 warps measured 1.24 ms against 1.15 ms at configs[0])
+static constexpr int kTcRescoreWarps = 4;  // warps that own a re-scoring tile (the row scans use every warp)
 
 template <typename T>
-__global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams p) {
+__global__ void __launch_bounds__(kTcThreads, kTcThreads == 256 ? 3 : 4) ap_rows_tc_kernel(const ApTcParams p) {
     extern __shared__ __align__(16) uint8_t sm[];
     uint64_t *pos = (uint64_t *)sm;                       // [kTcPos] exact keys of the positives (sorted), then + forced last
     uint64_t *ambk = pos + kTcPos;                        // [kTcAmb] exact keys of the queued survivors
@@ -524,10 +528,10 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
     const float cmin = ordered_to_f32((unsigned int)misc[4]);
     const float emax = qn - cmin;  // largest coarse distance of a survivor
     const bool tiled = ((size_t)p.d * sizeof(T)) % 128 == 0 && (((uintptr_t)p.g) & 15) == 0;
-    uint8_t *wtile = tile + warp * kRescoreTileBytes;
+    uint8_t *wtile = tile + (warp % kTcRescoreWarps) * kRescoreTileBytes;
     auto rescore = [&](const uint32_t *rows, uint64_t *keys, int cnt) {  // canonical (d2, row) keys of gathered rows
         if (tiled) {
-            for (int i0 = warp * 32; i0 < cnt; i0 += kTcThreads) {
+            for (int i0 = warp * 32; warp < kTcRescoreWarps && i0 < cnt; i0 += 32 * kTcRescoreWarps) {
                 const int i = i0 + lane;
                 const uint32_t r = rows[i < cnt ? i : i0];
                 const float d2 = warp_canon_d2_rows<T>(qs, (const T *)p.g + (int64_t)r * p.d, p.d, wtile, lane);
@@ -682,7 +686,7 @@ __global__ void __launch_bounds__(kTcThreads) ap_rows_tc_kernel(const ApTcParams
 
 size_t ap_rows_tc_smem(int d) {
     return (size_t)kTcPos * 8 + (size_t)kTcAmb * 8 + 16 + (size_t)kTcAmb * 4 + (size_t)(kTcPos + 2) * 4 +
-           (size_t)(kTcPos + 1) * 4 + (size_t)((d + 3) & ~3) * 4 + 40 * 4 + 16 * 4 + 128 + (size_t)(kTcThreads / 32) * kRescoreTileBytes + 64;
+           (size_t)(kTcPos + 1) * 4 + (size_t)((d + 3) & ~3) * 4 + 40 * 4 + 16 * 4 + 128 + (size_t)kTcRescoreWarps * kRescoreTileBytes + 64;
 }
 
 int launch_ap_rows_tc(const ApTcParams &p, cudaStream_t st) {
