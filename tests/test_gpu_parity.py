@@ -719,12 +719,12 @@ def test_triplet_fused_shapes(vq, G, B, d, ncls):
 def test_triplet_fused_adversarial(vq):
     """Ties and degenerate groups: duplicate rows (exact distance ties -> lowest index), an anchor
     identical to all its positives (pdist's clamp region), a singleton class, a single-class group
-    (no negatives: every anchor skipped), near-duplicates inside the TF32 error band, and a group
-    whose ambiguity overflows the fused kernel's candidate capacity (handed to the CUDA-core path)."""
+    (no negatives: every anchor skipped), near-duplicates inside the TF32 error band (20 of them: over the
+    capacity; 12 of them: within it), and a group whose ambiguity overflows the fused kernel's candidate capacity (handed to the CUDA-core path)."""
     rng = np.random.default_rng(5)
     B, d, ncls = 128, 64, 16
-    labs = np.stack([np.arange(B) % ncls for _ in range(6)]).astype(np.int64)
-    embs = np.stack([_emb(rng, B, d, ncls, labs[g]) for g in range(6)])
+    labs = np.stack([np.arange(B) % ncls for _ in range(7)]).astype(np.int64)
+    embs = np.stack([_emb(rng, B, d, ncls, labs[g]) for g in range(7)])
     embs[0, 16] = embs[0, 0]           # same class (0 and 16): d = clamp floor
     embs[0, 33] = embs[0, 1]           # 33 % 16 == 1: same class duplicate
     embs[0, 50] = embs[0, 3]           # 50 % 16 == 2: duplicate in ANOTHER class -> hardest negative ties
@@ -737,7 +737,14 @@ def test_triplet_fused_adversarial(vq):
     for j in range(20, 40):
         embs[4, j] = base + rng.standard_normal(d).astype(np.float32) * 1e-5
     embs[5, :] = embs[5, 0] + rng.standard_normal((B, d)).astype(np.float32) * 1e-6  # everything ambiguous
+    base = embs[6, 5].copy()           # group 6: 10 such rows, all of different classes and spread over the warps, so
+    for j in (5, 38, 71, 104, 9, 42, 75, 108, 13, 46):  # that each has 9 tied negatives (more than 8, at most 16: the
+        embs[6, j] = base + rng.standard_normal(d).astype(np.float32) * 1e-5  # second candidate word) and stays fused
     _check_groups(vq, embs, labs, 1.0)
+    from vqwild_b200 import _lib as L
+    assert L.lib().vq_triplet_last_handed_back() >= 2       # groups 4 and 5 at least
+    _check_groups(vq, embs[6:7], labs[6:7], 1.0)
+    assert L.lib().vq_triplet_last_handed_back() == 0       # 9-10 negative candidates are within the capacity
 
 
 def test_triplet_simt_path_matches(vq):

@@ -85,8 +85,32 @@ __global__ void __launch_bounds__(MT) bh_mine_kernel(const float *__restrict__ e
     const float *E = emb + (int64_t)g * B * d;
     const int32_t *L = labels ? labels + (int64_t)g * B : nullptr;
     const int a0 = blockIdx.x * MA;
-    // row norms = diagonal of the Gram matrix, canonical chain (prod.diag(), :286)
-    for (int r = tid; r < B; r += MT) nrm[r] = dot_chain(E + (int64_t)r * d, E + (int64_t)r * d, d);
+    // row norms = diagonal of the Gram matrix, canonical chain (prod.diag(), :286).  Eight lanes per row, lane c =
+    // chunk c of every 32-k block (dot_chain's t[c]); the xor-4 / 2 / 1 exchange is tree8 (fadd commutes, so every
+    // lane of the eight ends up with the same bits), and a warp reads 4 x 128 contiguous bytes per step instead of
+    // 32 rows at a 4*d-byte stride.
+    {
+        const int lane = tid & 31, c = lane & 7;
+        for (int r0 = (tid >> 5) * 4; r0 < B; r0 += (MT / 32) * 4) {  // warp-uniform
+            const int r = r0 + (lane >> 3);
+            const float *row = E + (int64_t)min(r, B - 1) * d;
+            float acc = 0.f;
+            for (int k0 = 0; k0 < d; k0 += 32) {
+                float t = 0.f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int k = k0 + c * 4 + i;
+                    const float v = k < d ? row[k] : 0.f;  // fmaf(0, 0, t) == t: same as dot_chain's skip
+                    t = __fmaf_rn(v, v, t);
+                }
+                t = __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, 4));
+                t = __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, 2));
+                t = __fadd_rn(t, __shfl_xor_sync(0xffffffffu, t, 1));
+                acc = __fadd_rn(acc, t);
+            }
+            if (c == 0 && r < B) nrm[r] = acc;
+        }
+    }
     const int al = tid >> 3, cg = tid & 7;  // anchor (local), column group
     const int ncol = (B + 7) / 8;           // columns per thread: cg, cg+8, ...
     float acc[NCMAX];

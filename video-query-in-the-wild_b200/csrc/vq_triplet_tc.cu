@@ -18,8 +18,8 @@
 //           it (in triplet order), acc = fmaf(2/T, x_u - x_v, acc); written once, coalesced.
 //
 // Results are bit-identical to the CUDA-core path (vq_triplet.cu) and to the oracle whatever the
-// tensor cores rounded.  Groups that exceed a fixed capacity (more than 8 candidates for a role,
-// more than 64 extra candidate pairs in a warp) are handed back through `bad_list` and recomputed
+// tensor cores rounded.  Groups that exceed a fixed capacity (more than 8 positive or 16 negative
+// candidates of an anchor, more than 64 extra candidate pairs in a warp) are handed back through `bad_list` and recomputed
 // by the CUDA-core path.
 #include <stdlib.h>
 
@@ -36,7 +36,10 @@ static constexpr int TSTAGE = TB * TKB * 4;       // 32 KB
 static constexpr int TSTAGES = 5;
 static constexpr int TROWT = 256;                 // row threads (warps 2..9)
 static constexpr int TTHREADS = 64 + TROWT;
-static constexpr int TCAND = 8;                   // candidates kept per role and anchor
+static constexpr int TCAND = 8;                   // positive candidates kept per anchor
+// negative candidates kept per anchor: with 8, about 1 anchor in 400 000 of random unit rows (252 negatives,
+// band 2 eps = 0.0084) overflowed, i.e. ~3 of 4096 groups went to the CUDA-core path, 0.3 ms after the kernel
+static constexpr int TCANDN = 16;
 static constexpr uint32_t kTcSleepNs = 20000;   // suspend-time hint of the waits of the producer / MMA warp
 static constexpr int TEXTRA = 64;                 // candidate pairs beyond the first of a role, per warp
 
@@ -358,7 +361,8 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             const float qnan = __int_as_float(0x7fc00000);
             const float thr_p = !avalid ? qnan : (maxp < 1e-4f + 2.0f * eps ? -INFINITY : maxp - 2.0f * eps);  // clamp region: every positive ties
             const float thr_n = !avalid ? qnan : fmaxf(minn, 1e-4f) + 2.0f * eps;
-            uint64_t cpw = 0, cnw = 0;  // up to 8 candidate rows per role, one byte each, ascending row order
+            // candidate rows, one byte each, ascending row order: up to TCAND positives, up to TCANDN negatives
+            uint64_t cpw = 0, cnw = 0, cnw2 = 0;
             int ncp = 0, ncn = 0;
             if (__any_sync(0xffffffffu, avalid)) {
 #pragma unroll 1
@@ -389,7 +393,8 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                     while (mn) {
                         const int j = ch * 32 + __ffs(mn) - 1;
                         mn &= mn - 1;
-                        if (ncn < TCAND) cnw |= (uint64_t)j << (8 * ncn);
+                        if (ncn < 8) cnw |= (uint64_t)j << (8 * ncn);
+                        else if (ncn < TCANDN) cnw2 |= (uint64_t)j << (8 * (ncn - 8));
                         ++ncn;
                     }
                 }
@@ -398,9 +403,10 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty_bar);  // TMEM may take the next group's Gram
             tk[3] = clock64();
-            bool bad = ncp > TCAND || ncn > TCAND;
+            bool bad = ncp > TCAND || ncn > TCANDN;
             ncp = min(ncp, TCAND);
-            ncn = min(ncn, TCAND);
+            ncn = min(ncn, TCANDN);
+            auto neg_at = [&](int t) { return (uint32_t)(((t < 8 ? cnw : cnw2) >> (8 * (t & 7))) & 255u); };
 
             // ---------------- work items of pass 2 ----------------
             // primary triple of every anchor (row, first positive candidate, first negative candidate): kept in
@@ -428,7 +434,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                 for (int t = 1; t < ncp; ++t)
                     s_tl[rw * TEXTRA + w++] = base_of((uint32_t)row) | (base_of((uint32_t)((cpw >> (8 * t)) & 255u)) << 16);
                 for (int t = 1; t < ncn; ++t)
-                    s_tl[rw * TEXTRA + w++] = base_of((uint32_t)row) | (base_of((uint32_t)((cnw >> (8 * t)) & 255u)) << 16);
+                    s_tl[rw * TEXTRA + w++] = base_of((uint32_t)row) | (base_of(neg_at(t)) << 16);
             }
             const bool wvalid = __any_sync(0xffffffffu, avalid);
             __syncwarp();
@@ -569,7 +575,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                     const float2 *rn = rx + (ncp - 1);
                     float bd = tc_pdist(na, s_nrm[cnw & 255u], pr.w, 1e-4f);
                     for (int t = 1; t < ncn; ++t) {
-                        const float dist = tc_pdist(na, s_nrm[(cnw >> (8 * t)) & 255u], rn[t - 1].y, 1e-4f);
+                        const float dist = tc_pdist(na, s_nrm[neg_at(t)], rn[t - 1].y, 1e-4f);
                         if (dist < bd) {
                             bd = dist;
                             bq = t;
@@ -577,7 +583,7 @@ triplet_tc_kernel(const __grid_constant__ CUtensorMap tm_e, const TripletTcParam
                         }
                     }
                 }
-                fn = (int)((cnw >> (8 * bq)) & 255u);
+                fn = (int)neg_at(bq);
                 const float v = __fadd_rn(__fsub_rn(d2p, d2n), p.margin);
                 lterm = v > 0.f ? v : 0.f;
             }
