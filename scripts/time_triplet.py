@@ -12,7 +12,7 @@ from vqwild_b200 import _lib as L
 
 dev = "cuda"
 lib = vq.lib()
-for G in (1, 148, 4096):
+for G in [int(x) for x in os.environ.get("TT_G", "1,148,4096").split(",")]:  # TT_G=4096: that case only
     emb = torch.randn(G, 256, 512, device=dev)
     emb = emb / emb.norm(dim=2, keepdim=True)
     lab = torch.arange(256, device=dev).div(4, rounding_mode="floor").to(torch.int32).repeat(G, 1).contiguous()

@@ -39,7 +39,11 @@ static constexpr int TTHREADS = 64 + TROWT;
 static constexpr int TCAND = 8;                   // positive candidates kept per anchor
 // negative candidates kept per anchor: with 8, about 1 anchor in 400 000 of random unit rows (252 negatives,
 // band 2 eps = 0.0084) overflowed, i.e. ~3 of 4096 groups went to the CUDA-core path, 0.3 ms after the kernel
-static constexpr int TCANDN = 16;
+#ifndef VQ_TCANDN
+#define VQ_TCANDN 16  // 9 .. 16; -DVQ_TCANDN=8 rebuilds the former capacity for an A/B
+#endif
+static constexpr int TCANDN = VQ_TCANDN;
+static_assert(TCANDN >= 8 && TCANDN <= 16, "two candidate words");
 static constexpr uint32_t kTcSleepNs = 20000;   // suspend-time hint of the waits of the producer / MMA warp
 static constexpr int TEXTRA = 64;                 // candidate pairs beyond the first of a role, per warp
 
