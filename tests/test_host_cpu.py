@@ -40,6 +40,41 @@ def test_abi_exports_nothing_but_vq_symbols():
     assert set(_declared_symbols()) <= set(syms)
 
 
+def test_hot_kernels_are_tcgen05_and_tma():
+    """The built library is the sm_100a product, not a recompiled SIMT baseline: the search GEMMs and the fused triplet
+    kernel hold tcgen05 MMAs (SASS UTCHMMA, `.2CTA` for the CTA-pair kernel), TMA loads (UTMALDG), TMEM loads (LDTM)
+    and mbarrier waits (SYNCS); the canonical scorers hold the packed fp32 forms.  Same table as
+    profiles/r02_sass_mnemonics.txt (scripts/sass_mnemonics.py)."""
+    import shutil
+    import subprocess
+    import vqwild_b200 as vq
+    if not shutil.which("cuobjdump"):
+        pytest.skip("cuobjdump not on PATH")
+    sass = subprocess.run(["cuobjdump", "-sass", vq.SO_PATH], capture_output=True, text=True, check=True).stdout
+    assert "sm_100a" in sass
+    body = {}
+    cur = None
+    for ln in sass.split("\n"):
+        m = re.search(r"Function : (\S+)", ln)
+        if m:
+            cur = m.group(1)
+            body[cur] = []
+        elif cur:
+            body[cur].append(ln)
+
+    def kernels(tag):
+        ks = {k: "\n".join(v) for k, v in body.items() if tag in k}
+        assert ks, tag
+        return ks
+    for k, txt in kernels("gemm_topk_pair_kernel").items():
+        assert re.search(r"UTC[HQ]MMA\.2CTA", txt) and "UTMALDG" in txt and "LDTM" in txt and "SYNCS" in txt, k
+    for k, txt in list(kernels("16gemm_topk_kernel").items()) + list(kernels("triplet_tc_kernel").items()):
+        assert re.search(r"UTC[HQ]MMA", txt) and "UTMALDG" in txt and "LDTM" in txt and "SYNCS" in txt, k
+    for k, txt in kernels("segmax_rescore_kernel").items():
+        assert "FFMA2" in txt and "FADD2" in txt, k
+    assert any("STG.E.ENL2.256" in t or re.search(r"STG\.[A-Z0-9.]*256", t) for t in kernels("window_means_kernel").values())
+
+
 def test_no_cpu_fallback_without_device():
     import torch
     if torch.cuda.is_available():
